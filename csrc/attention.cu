@@ -1,0 +1,390 @@
+// Fused multi-head self-attention for sequences of up to 128 tokens (the reference truncates/pads every flow
+// sentence to max_len=128, client1.py:27,38-45), head_dim 64: one CTA per (batch, head), the whole sequence is a
+// single 128-row tile, so there is no online-softmax loop and the backward needs no atomics.
+//
+// forward : S = Q K^T (tcgen05, TMEM) -> masked softmax + dropout in registers -> P (bf16, smem) -> O = P V (tcgen05)
+// backward: S = Q K^T, dP = dO V^T -> P, dS in registers -> dV = P^T dO, dK = dS^T Q, dQ = dS K (three more MMAs)
+//
+// Replaces HF DistilBERT's attention core (transformers modeling_distilbert.py:126-151 eager /
+// F.scaled_dot_product_attention) reached from reference client1.py:61, incl. attention dropout 0.1 and the
+// key-padding mask (here: per-sample valid length instead of a [B,1,S,S] mask tensor).
+//
+// Layout: qkv is [B*S, 3*H*64] bf16 (Q | K | V column blocks, head-major inside each), ctx is [B*S, H*64].
+#include <mutex>
+
+#include "common.cuh"
+#include "../include/dcad_b200.h"
+
+namespace dcad {
+
+int make_tensor_map_bf16_3d(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t ld1,
+                            uint64_t ld2, uint32_t b0, uint32_t b1);
+
+constexpr int AT_S = 128;        // tile rows (max sequence length)
+constexpr int AT_D = 64;         // head dim
+constexpr int TILE_BYTES = AT_S * AT_D * 2;  // 16 KB: [128][64] bf16, 128-byte rows, SW128
+constexpr float LOG2E = 1.4426950408889634f;
+
+__device__ __forceinline__ uint64_t attn_seed(const uint64_t* rng) {
+    return rng ? rng[0] + rng[1] * 0xD1B54A32D192ED03ULL : 0ULL;
+}
+
+// write 8 consecutive bf16 (keys j0..j0+7 of row `row`) into a K-major SW128 [128][128] tile made of two
+// [128][64] slabs
+__device__ __forceinline__ void st_tile8(uint8_t* tile, int row, int j0, const float* v) {
+    uint4 o;
+    o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
+    o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+    uint8_t* p = tile + (j0 >> 6) * TILE_BYTES + sw128_offset(row, (j0 & 63) >> 3);
+    *reinterpret_cast<uint4*>(p) = o;
+}
+
+// ------------------------------------------------------------------------------------------------
+// forward
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128, 2)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __restrict__ ctx,
+                float* __restrict__ lse2_out, const int32_t* __restrict__ lens, int S, int H, float scale,
+                uint32_t thresh, float keep_scale, const uint64_t* __restrict__ rng, uint32_t stream_id) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t bar_load, bar_mma1, bar_mma2;
+    __shared__ uint32_t tmem_base_smem;
+
+    const int bh = blockIdx.x, b = bh / H, h = bh % H;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    uint8_t* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw));
+    uint8_t* sQ = smem; uint8_t* sK = smem + TILE_BYTES; uint8_t* sV = smem + 2 * TILE_BYTES;
+    uint8_t* sP = smem + 3 * TILE_BYTES;  // 2 slabs
+    const int HD = H * AT_D;
+
+    if (tid == 0) {
+        tma_prefetch_desc(&tm_qkv);
+        mbar_init(smem_u32(&bar_load), 1);
+        mbar_init(smem_u32(&bar_mma1), 1);
+        mbar_init(smem_u32(&bar_mma2), 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) { tmem_alloc(smem_u32(&tmem_base_smem), 256); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base_smem;
+    const uint32_t tS = tmem, tO = tmem + 128;
+
+    if (tid == 0) {
+        const uint32_t bar = smem_u32(&bar_load);
+        mbar_arrive_expect_tx(bar, 3 * TILE_BYTES);
+        tma_load_3d(smem_u32(sQ), &tm_qkv, bar, h * AT_D, 0, b);
+        tma_load_3d(smem_u32(sK), &tm_qkv, bar, HD + h * AT_D, 0, b);
+        tma_load_3d(smem_u32(sV), &tm_qkv, bar, 2 * HD + h * AT_D, 0, b);
+    }
+    mbar_wait(smem_u32(&bar_load), 0);
+    if (tid == 0) {
+        tc_fence_after();
+        constexpr uint32_t idesc = make_idesc_bf16(128, 128, kMajorK, kMajorK);
+#pragma unroll
+        for (int k = 0; k < AT_D / 16; ++k)
+            umma_bf16_ss(tS, make_smem_desc_sw128(smem_u32(sQ) + k * 32, 16, 1024),
+                         make_smem_desc_sw128(smem_u32(sK) + k * 32, 16, 1024), idesc, k != 0);
+        umma_commit(smem_u32(&bar_mma1));
+    }
+    const int len = min(lens ? lens[b] : S, S);
+    const uint64_t seed = attn_seed(rng);
+    const float sc2 = scale * LOG2E;
+    mbar_wait(smem_u32(&bar_mma1), 0);
+    tc_fence_after();
+
+    const int row = tid;
+    const uint32_t t_lane = (static_cast<uint32_t>(warp) * 32u) << 16;
+    // pass 1: row max over valid keys
+    float mx = -INFINITY;
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tS + t_lane + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            if (c * 32 + j < len) mx = fmaxf(mx, __uint_as_float(r[j]));
+    }
+    const float m2 = mx * sc2;
+    // pass 2: p = exp2(s*sc2 - m2), row sum, dropout, write bf16 P (unnormalised) to smem
+    float sum = 0.f;
+    const uint32_t drop_base = (static_cast<uint32_t>(bh) * AT_S + row) * AT_S;
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tS + t_lane + c * 32, r);
+        tmem_ld_wait();
+        float p[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const int key = c * 32 + j;
+            float e = key < len ? exp2f(__uint_as_float(r[j]) * sc2 - m2) : 0.f;
+            sum += e;
+            if (thresh) e = dropout_keep(seed, stream_id, drop_base + key, thresh) ? e * keep_scale : 0.f;
+            p[j] = e;
+        }
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) st_tile8(sP, row, c * 32 + j, p + j);
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+        tc_fence_after();
+        constexpr uint32_t idesc = make_idesc_bf16(128, 64, kMajorK, kMajorMN);
+#pragma unroll
+        for (int k = 0; k < AT_S / 16; ++k)
+            umma_bf16_ss(tO, make_smem_desc_sw128(smem_u32(sP) + (k >> 2) * TILE_BYTES + (k & 3) * 32, 16, 1024),
+                         make_smem_desc_sw128(smem_u32(sV) + k * 2048, TILE_BYTES, 1024), idesc, k != 0);
+        umma_commit(smem_u32(&bar_mma2));
+    }
+    if (lse2_out && row < S) lse2_out[static_cast<size_t>(bh) * AT_S + row] = m2 + log2f(sum);
+    const float inv = 1.0f / sum;
+    mbar_wait(smem_u32(&bar_mma2), 0);
+    tc_fence_after();
+#pragma unroll 1
+    for (int c = 0; c < 2; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tO + t_lane + c * 32, r);
+        tmem_ld_wait();
+        if (row < S) {
+            __nv_bfloat16* dst = ctx + (static_cast<size_t>(b) * S + row) * HD + h * AT_D + c * 32;
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+                uint4 o;
+                o.x = pack_bf16x2(__uint_as_float(r[j]) * inv, __uint_as_float(r[j + 1]) * inv);
+                o.y = pack_bf16x2(__uint_as_float(r[j + 2]) * inv, __uint_as_float(r[j + 3]) * inv);
+                o.z = pack_bf16x2(__uint_as_float(r[j + 4]) * inv, __uint_as_float(r[j + 5]) * inv);
+                o.w = pack_bf16x2(__uint_as_float(r[j + 6]) * inv, __uint_as_float(r[j + 7]) * inv);
+                *reinterpret_cast<uint4*>(dst + j) = o;
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem, 256); }
+}
+
+// ------------------------------------------------------------------------------------------------
+// backward
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128, 1)
+attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_dctx,
+                const __nv_bfloat16* __restrict__ ctx, const __nv_bfloat16* __restrict__ dctx,
+                const float* __restrict__ lse2, __nv_bfloat16* __restrict__ dqkv, const int32_t* __restrict__ lens,
+                int S, int H, float scale, uint32_t thresh, float keep_scale, const uint64_t* __restrict__ rng,
+                uint32_t stream_id) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t bar_load, bar_mma1, bar_mma2;
+    __shared__ uint32_t tmem_base_smem;
+
+    const int bh = blockIdx.x, b = bh / H, h = bh % H;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    uint8_t* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw));
+    uint8_t* sQ = smem; uint8_t* sK = smem + TILE_BYTES; uint8_t* sV = smem + 2 * TILE_BYTES;
+    uint8_t* sdO = smem + 3 * TILE_BYTES;
+    uint8_t* sP = smem + 4 * TILE_BYTES;   // 2 slabs: P (dropped, normalised)
+    uint8_t* sdS = smem + 6 * TILE_BYTES;  // 2 slabs: dS (scaled)
+    const int HD = H * AT_D;
+
+    if (tid == 0) {
+        tma_prefetch_desc(&tm_qkv);
+        tma_prefetch_desc(&tm_dctx);
+        mbar_init(smem_u32(&bar_load), 1);
+        mbar_init(smem_u32(&bar_mma1), 1);
+        mbar_init(smem_u32(&bar_mma2), 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) { tmem_alloc(smem_u32(&tmem_base_smem), 512); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base_smem;
+    const uint32_t tS = tmem, tdP = tmem + 128, tdV = tmem + 256, tdK = tmem + 320, tdQ = tmem + 384;
+
+    if (tid == 0) {
+        const uint32_t bar = smem_u32(&bar_load);
+        mbar_arrive_expect_tx(bar, 4 * TILE_BYTES);
+        tma_load_3d(smem_u32(sQ), &tm_qkv, bar, h * AT_D, 0, b);
+        tma_load_3d(smem_u32(sK), &tm_qkv, bar, HD + h * AT_D, 0, b);
+        tma_load_3d(smem_u32(sV), &tm_qkv, bar, 2 * HD + h * AT_D, 0, b);
+        tma_load_3d(smem_u32(sdO), &tm_dctx, bar, h * AT_D, 0, b);
+    }
+    const int row = tid;
+    // delta = rowsum(dO * O), from global while the TMA loads fly
+    float delta = 0.f;
+    if (row < S) {
+        const uint4* po = reinterpret_cast<const uint4*>(ctx + (static_cast<size_t>(b) * S + row) * HD + h * AT_D);
+        const uint4* pd = reinterpret_cast<const uint4*>(dctx + (static_cast<size_t>(b) * S + row) * HD + h * AT_D);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint4 o = __ldg(po + i), d = __ldg(pd + i);
+            const float2 o0 = unpack_bf16x2(o.x), o1 = unpack_bf16x2(o.y), o2 = unpack_bf16x2(o.z), o3 = unpack_bf16x2(o.w);
+            const float2 d0 = unpack_bf16x2(d.x), d1 = unpack_bf16x2(d.y), d2 = unpack_bf16x2(d.z), d3 = unpack_bf16x2(d.w);
+            delta += o0.x * d0.x + o0.y * d0.y + o1.x * d1.x + o1.y * d1.y + o2.x * d2.x + o2.y * d2.y +
+                     o3.x * d3.x + o3.y * d3.y;
+        }
+    }
+    mbar_wait(smem_u32(&bar_load), 0);
+    if (tid == 0) {
+        tc_fence_after();
+        constexpr uint32_t idesc = make_idesc_bf16(128, 128, kMajorK, kMajorK);
+#pragma unroll
+        for (int k = 0; k < AT_D / 16; ++k)  // S = Q K^T
+            umma_bf16_ss(tS, make_smem_desc_sw128(smem_u32(sQ) + k * 32, 16, 1024),
+                         make_smem_desc_sw128(smem_u32(sK) + k * 32, 16, 1024), idesc, k != 0);
+#pragma unroll
+        for (int k = 0; k < AT_D / 16; ++k)  // dP = dO V^T
+            umma_bf16_ss(tdP, make_smem_desc_sw128(smem_u32(sdO) + k * 32, 16, 1024),
+                         make_smem_desc_sw128(smem_u32(sV) + k * 32, 16, 1024), idesc, k != 0);
+        umma_commit(smem_u32(&bar_mma1));
+    }
+    const int len = min(lens ? lens[b] : S, S);
+    const uint64_t seed = attn_seed(rng);
+    const float sc2 = scale * LOG2E;
+    const float l2 = (row < S) ? lse2[static_cast<size_t>(bh) * AT_S + row] : 0.f;
+    const uint32_t t_lane = (static_cast<uint32_t>(warp) * 32u) << 16;
+    const uint32_t drop_base = (static_cast<uint32_t>(bh) * AT_S + row) * AT_S;
+    mbar_wait(smem_u32(&bar_mma1), 0);
+    tc_fence_after();
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+        uint32_t rs[32], rp[32];
+        tmem_ld_32x32b_x32(tS + t_lane + c * 32, rs);
+        tmem_ld_32x32b_x32(tdP + t_lane + c * 32, rp);
+        tmem_ld_wait();
+        float pd[32], ds[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const int key = c * 32 + j;
+            const bool valid = key < len && row < S;
+            const float p = valid ? exp2f(__uint_as_float(rs[j]) * sc2 - l2) : 0.f;
+            float dp = __uint_as_float(rp[j]);
+            float pk = p;
+            if (thresh) {
+                const bool keep = dropout_keep(seed, stream_id, drop_base + key, thresh);
+                pk = keep ? p * keep_scale : 0.f;
+                dp = keep ? dp * keep_scale : 0.f;
+            }
+            pd[j] = pk;
+            ds[j] = valid ? p * (dp - delta) * scale : 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+            st_tile8(sP, row, c * 32 + j, pd + j);
+            st_tile8(sdS, row, c * 32 + j, ds + j);
+        }
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+        tc_fence_after();
+        constexpr uint32_t idesc_t = make_idesc_bf16(128, 64, kMajorMN, kMajorMN);
+        constexpr uint32_t idesc_n = make_idesc_bf16(128, 64, kMajorK, kMajorMN);
+#pragma unroll
+        for (int k = 0; k < AT_S / 16; ++k)  // dV[key, d] = sum_q P[q, key] dO[q, d]
+            umma_bf16_ss(tdV, make_smem_desc_sw128(smem_u32(sP) + k * 2048, TILE_BYTES, 1024),
+                         make_smem_desc_sw128(smem_u32(sdO) + k * 2048, TILE_BYTES, 1024), idesc_t, k != 0);
+#pragma unroll
+        for (int k = 0; k < AT_S / 16; ++k)  // dK[key, d] = sum_q dS[q, key] Q[q, d]
+            umma_bf16_ss(tdK, make_smem_desc_sw128(smem_u32(sdS) + k * 2048, TILE_BYTES, 1024),
+                         make_smem_desc_sw128(smem_u32(sQ) + k * 2048, TILE_BYTES, 1024), idesc_t, k != 0);
+#pragma unroll
+        for (int k = 0; k < AT_S / 16; ++k)  // dQ[q, d] = sum_key dS[q, key] K[key, d]
+            umma_bf16_ss(tdQ, make_smem_desc_sw128(smem_u32(sdS) + (k >> 2) * TILE_BYTES + (k & 3) * 32, 16, 1024),
+                         make_smem_desc_sw128(smem_u32(sK) + k * 2048, TILE_BYTES, 1024), idesc_n, k != 0);
+        umma_commit(smem_u32(&bar_mma2));
+    }
+    mbar_wait(smem_u32(&bar_mma2), 0);
+    tc_fence_after();
+    // rows of dQ are queries, rows of dK/dV are keys: thread `row` writes token `row` of all three
+#pragma unroll 1
+    for (int which = 0; which < 3; ++which) {
+        const uint32_t tsrc = which == 0 ? tdQ : (which == 1 ? tdK : tdV);
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+            uint32_t r[32];
+            tmem_ld_32x32b_x32(tsrc + t_lane + c * 32, r);
+            tmem_ld_wait();
+            if (row < S) {
+                __nv_bfloat16* dst =
+                    dqkv + (static_cast<size_t>(b) * S + row) * (3 * HD) + which * HD + h * AT_D + c * 32;
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) {
+                    uint4 o;
+                    o.x = pack_bf16x2(__uint_as_float(r[j]), __uint_as_float(r[j + 1]));
+                    o.y = pack_bf16x2(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+                    o.z = pack_bf16x2(__uint_as_float(r[j + 4]), __uint_as_float(r[j + 5]));
+                    o.w = pack_bf16x2(__uint_as_float(r[j + 6]), __uint_as_float(r[j + 7]));
+                    *reinterpret_cast<uint4*>(dst + j) = o;
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+}
+
+static inline uint32_t drop_thresh_attn(float p) {
+    if (p <= 0.f) return 0u;
+    double t = static_cast<double>(p) * 4294967296.0;
+    if (t > 4294967295.0) t = 4294967295.0;
+    return static_cast<uint32_t>(t);
+}
+
+}  // namespace dcad
+
+using namespace dcad;
+
+// qkv: [B*S, 3*H*64] bf16; ctx: [B*S, H*64] bf16; lse2: [B*H*128] fp32 (log2-domain logsumexp, for backward)
+extern "C" int dcad_attn_fwd(const void* qkv, void* ctx, float* lse2, const int32_t* lens, int B, int S, int H,
+                             float p_drop, const uint64_t* rng, uint32_t stream_id, void* stream) {
+    if (B <= 0) return 0;
+    if (S <= 0 || S > AT_S || H <= 0) return DCAD_ERR_BAD_SHAPE;
+    if (p_drop > 0.f && rng == nullptr) return DCAD_ERR_BAD_ARGUMENT;
+    const int HD = H * AT_D;
+    CUtensorMap tm;
+    int rc = make_tensor_map_bf16_3d(&tm, qkv, 3 * HD, S, B, 3 * HD, static_cast<uint64_t>(S) * 3 * HD, AT_D, AT_S);
+    if (rc) return rc;
+    constexpr int SMEM = 5 * TILE_BYTES + 1024;
+    static bool attr = false;
+    if (!attr) {
+        DCAD_CUDA_TRY(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        attr = true;
+    }
+    const float ks = p_drop > 0.f ? 1.0f / (1.0f - p_drop) : 1.0f;
+    attn_fwd_kernel<<<B * H, 128, SMEM, reinterpret_cast<cudaStream_t>(stream)>>>(
+        tm, reinterpret_cast<__nv_bfloat16*>(ctx), lse2, lens, S, H, 0.125f, drop_thresh_attn(p_drop), ks, rng,
+        stream_id);
+    return (int)cudaGetLastError();
+}
+
+// dctx: [B*S, H*64] bf16 gradient of ctx; dqkv: [B*S, 3*H*64] bf16 output
+extern "C" int dcad_attn_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse2, void* dqkv,
+                             const int32_t* lens, int B, int S, int H, float p_drop, const uint64_t* rng,
+                             uint32_t stream_id, void* stream) {
+    if (B <= 0) return 0;
+    if (S <= 0 || S > AT_S || H <= 0) return DCAD_ERR_BAD_SHAPE;
+    if (p_drop > 0.f && rng == nullptr) return DCAD_ERR_BAD_ARGUMENT;
+    const int HD = H * AT_D;
+    CUtensorMap tq, td;
+    int rc = make_tensor_map_bf16_3d(&tq, qkv, 3 * HD, S, B, 3 * HD, static_cast<uint64_t>(S) * 3 * HD, AT_D, AT_S);
+    if (rc) return rc;
+    rc = make_tensor_map_bf16_3d(&td, dctx, HD, S, B, HD, static_cast<uint64_t>(S) * HD, AT_D, AT_S);
+    if (rc) return rc;
+    constexpr int SMEM = 8 * TILE_BYTES + 1024;
+    static bool attr = false;
+    if (!attr) {
+        DCAD_CUDA_TRY(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        attr = true;
+    }
+    const float ks = p_drop > 0.f ? 1.0f / (1.0f - p_drop) : 1.0f;
+    attn_bwd_kernel<<<B * H, 128, SMEM, reinterpret_cast<cudaStream_t>(stream)>>>(
+        tq, td, reinterpret_cast<const __nv_bfloat16*>(ctx), reinterpret_cast<const __nv_bfloat16*>(dctx), lse2,
+        reinterpret_cast<__nv_bfloat16*>(dqkv), lens, S, H, 0.125f, drop_thresh_attn(p_drop), ks, rng, stream_id);
+    return (int)cudaGetLastError();
+}

@@ -1,0 +1,287 @@
+// FedAvg aggregation kernels and the peer-memory runtime they need.
+//
+// The reference's server averages the clients' state_dicts key by key in Python after shipping them through
+// pickle + gzip + TCP (server.py:67-79 aggregate_models; transport server.py:29-65, client1.py:228-336).  Here every
+// client keeps its parameters in one contiguous arena in peer-mappable GPU memory and the aggregation is ONE kernel
+// per GPU that reads the peers' arenas over NVLink/NVSwitch, accumulates in fp32 in client order (bit parity with the
+// reference's `+=` loop), divides by N, and stores the result -- plus the bf16 compute copy of the GEMM weights --
+// straight into every client's buffers.  No NCCL on this path.
+//
+//   two-shot (default): rank r reduces shard r from all N arenas and pushes the averaged shard to all N arenas
+//                       (in place; ingress (N-1)/N*S + egress (N-1)/N*S per GPU, both link directions busy)
+//   one-shot          : every rank reduces the whole arena from all peers into its own separate output buffer
+//   local             : all sources reachable from one GPU, no cross-GPU handshake (server-side socket fallback,
+//                       single-process tests)
+//
+// Cross-GPU handshake: per-rank signal pad in peer memory, flags written with st.release.sys and polled with
+// ld.acquire.sys; bounded spins set an error flag instead of hanging.
+#include <string.h>
+
+#include "common.cuh"
+#include "../include/dcad_b200.h"
+
+namespace dcad {
+
+constexpr int FED_MAX = DCAD_FED_MAX_CLIENTS;
+constexpr int PAD_READY = 0;     // [0,16)  : ready flags, slot k written by rank k
+constexpr int PAD_DONE = 16;     // [16,32) : done flags
+constexpr int PAD_COUNTER = 32;  // local block-completion counter
+constexpr int PAD_ERROR = 33;    // set to 1 when a bounded spin expired
+
+struct FedArgs {
+    void* arena[FED_MAX];
+    void* out[FED_MAX];
+    void* mirror[FED_MAX];
+    uint32_t* pad[FED_MAX];
+    float weight[FED_MAX];
+    int use_weights;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ bool spin_until_ge(const uint32_t* p, uint32_t target) {
+    for (uint32_t i = 0; i < (1u << 24); ++i) {
+        if (static_cast<int32_t>(ld_acquire_sys(p) - target) >= 0) return true;
+        __nanosleep(64);
+    }
+    return false;
+}
+
+template <bool IN_BF16>
+struct VecIO;
+template <>
+struct VecIO<false> {  // fp32 arena, 4 elements per 16-byte access
+    static constexpr int ELEMS = 4;
+    __device__ static void load(const void* base, int64_t vec, float (&v)[4]) {
+        const float4 t = *(reinterpret_cast<const float4*>(base) + vec);
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    }
+    __device__ static void store(void* base, int64_t vec, const float (&v)[4]) {
+        *(reinterpret_cast<float4*>(base) + vec) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+};
+template <>
+struct VecIO<true> {  // bf16 arena, 8 elements per 16-byte access
+    static constexpr int ELEMS = 8;
+    __device__ static void load(const void* base, int64_t vec, float (&v)[8]) {
+        const uint4 t = *(reinterpret_cast<const uint4*>(base) + vec);
+        const float2 a = unpack_bf16x2(t.x), b = unpack_bf16x2(t.y), c = unpack_bf16x2(t.z), d = unpack_bf16x2(t.w);
+        v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
+    }
+    __device__ static void store(void* base, int64_t vec, const float (&v)[8]) {
+        uint4 o;
+        o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
+        o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+        *(reinterpret_cast<uint4*>(base) + vec) = o;
+    }
+};
+
+// average one 16-byte vector position across n clients, in client order.  Loads are issued in batches of 8
+// clients before any arithmetic so that up to 8 peer reads per thread are in flight (NVLink latency ~2 us).
+template <bool IN_BF16>
+__device__ __forceinline__ void reduce_vec(const FedArgs& a, int n, int64_t vec, float (&acc)[VecIO<IN_BF16>::ELEMS]) {
+    constexpr int E = VecIO<IN_BF16>::ELEMS;
+#pragma unroll
+    for (int j = 0; j < E; ++j) acc[j] = 0.f;
+    for (int k0 = 0; k0 < n; k0 += 8) {
+        float t[8][E];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+            if (k0 + u < n) VecIO<IN_BF16>::load(a.arena[k0 + u], vec, t[u]);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            if (k0 + u < n) {
+                if (a.use_weights) {
+                    const float w = a.weight[k0 + u];
+#pragma unroll
+                    for (int j = 0; j < E; ++j) acc[j] = (k0 + u == 0) ? w * t[u][j] : fmaf(w, t[u][j], acc[j]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < E; ++j) acc[j] = (k0 + u == 0) ? t[u][j] : acc[j] + t[u][j];
+                }
+            }
+        }
+    }
+    if (!a.use_weights) {
+        const float nf = static_cast<float>(n);
+#pragma unroll
+        for (int j = 0; j < E; ++j) acc[j] = __fdiv_rn(acc[j], nf);  // reference: base[key] /= len(models)
+    }
+}
+
+template <bool IN_BF16>
+__device__ __forceinline__ void store_mirror(void* mirror, int64_t elem0, int64_t bf16_begin, int64_t bf16_end,
+                                             const float (&v)[VecIO<IN_BF16>::ELEMS]) {
+    if constexpr (!IN_BF16) {
+        if (mirror && elem0 >= bf16_begin && elem0 < bf16_end) {
+            uint2 o;
+            o.x = pack_bf16x2(v[0], v[1]);
+            o.y = pack_bf16x2(v[2], v[3]);
+            *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(mirror) + (elem0 - bf16_begin)) = o;
+        }
+    }
+}
+
+// ---- local: sources readable from this GPU, single destination ----
+template <bool IN_BF16>
+__global__ void __launch_bounds__(512)
+fedavg_local_kernel(const FedArgs a, int n, int64_t num_vecs, int64_t bf16_begin, int64_t bf16_end) {
+    constexpr int E = VecIO<IN_BF16>::ELEMS;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t vec = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; vec < num_vecs; vec += stride) {
+        float acc[E];
+        reduce_vec<IN_BF16>(a, n, vec, acc);
+        VecIO<IN_BF16>::store(a.out[0], vec, acc);
+        store_mirror<IN_BF16>(a.mirror[0], vec * E, bf16_begin, bf16_end, acc);
+    }
+}
+
+// ---- peer-to-peer: one launch per rank, kernels on different GPUs handshake through the signal pads ----
+template <bool IN_BF16>
+__global__ void __launch_bounds__(512)
+fedavg_p2p_kernel(const FedArgs a, int rank, int n, int64_t num_vecs, int mode, int64_t bf16_begin, int64_t bf16_end,
+                  uint32_t epoch) {
+    constexpr int E = VecIO<IN_BF16>::ELEMS;
+    uint32_t* my_pad = a.pad[rank];
+    // start barrier: every peer's arena is final (their launch is stream-ordered after their local training)
+    if (blockIdx.x == 0 && threadIdx.x < n) st_release_sys(a.pad[threadIdx.x] + PAD_READY + rank, epoch);
+    if (threadIdx.x < n) {
+        if (!spin_until_ge(my_pad + PAD_READY + threadIdx.x, epoch)) my_pad[PAD_ERROR] = 1;
+    }
+    __syncthreads();
+
+    int64_t lo = 0, hi = num_vecs;
+    if (mode == DCAD_FED_TWO_SHOT) {
+        lo = num_vecs * rank / n;
+        hi = num_vecs * (rank + 1) / n;
+    }
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t vec = lo + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; vec < hi; vec += stride) {
+        float acc[E];
+        reduce_vec<IN_BF16>(a, n, vec, acc);
+        if (mode == DCAD_FED_TWO_SHOT) {
+            for (int k = 0; k < n; ++k) {
+                VecIO<IN_BF16>::store(a.arena[k], vec, acc);
+                store_mirror<IN_BF16>(a.mirror[k], vec * E, bf16_begin, bf16_end, acc);
+            }
+        } else {
+            VecIO<IN_BF16>::store(a.out[rank], vec, acc);
+            store_mirror<IN_BF16>(a.mirror[rank], vec * E, bf16_begin, bf16_end, acc);
+        }
+    }
+    // end barrier: the last block of this rank tells every peer its pushes are visible, then waits for theirs
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const uint32_t prev = atomicAdd(my_pad + PAD_COUNTER, 1u);
+        if (prev == gridDim.x - 1) {
+            my_pad[PAD_COUNTER] = 0;
+            __threadfence_system();
+            for (int k = 0; k < n; ++k) st_release_sys(a.pad[k] + PAD_DONE + rank, epoch);
+            for (int k = 0; k < n; ++k)
+                if (!spin_until_ge(my_pad + PAD_DONE + k, epoch)) my_pad[PAD_ERROR] = 1;
+        }
+    }
+}
+
+static int fill_args(FedArgs& fa, const void* const* arenas, const void* const* outs, const void* const* mirrors,
+                     const void* const* pads, const float* weights, int n) {
+    if (n < 1 || n > FED_MAX) return DCAD_ERR_TOO_LARGE;
+    for (int k = 0; k < FED_MAX; ++k) {
+        fa.arena[k] = k < n ? const_cast<void*>(arenas[k]) : nullptr;
+        fa.out[k] = (outs && k < n) ? const_cast<void*>(outs[k]) : nullptr;
+        fa.mirror[k] = (mirrors && k < n) ? const_cast<void*>(mirrors[k]) : nullptr;
+        fa.pad[k] = (pads && k < n) ? reinterpret_cast<uint32_t*>(const_cast<void*>(pads[k])) : nullptr;
+        fa.weight[k] = (weights && k < n) ? weights[k] : 0.f;
+    }
+    fa.use_weights = weights ? 1 : 0;
+    return 0;
+}
+
+}  // namespace dcad
+
+using namespace dcad;
+
+extern "C" int dcad_fedavg_local(const void* const* srcs, void* dst, void* dst_bf16, int n_clients, int64_t count,
+                                 int in_bf16, const float* weights, int64_t bf16_begin, int64_t bf16_end,
+                                 int max_ctas, void* stream) {
+    if (count <= 0) return 0;
+    const int E = in_bf16 ? 8 : 4;
+    if (count % E || (bf16_begin & 3) || (bf16_end & 3)) return DCAD_ERR_BAD_ALIGNMENT;
+    FedArgs fa;
+    int rc = fill_args(fa, srcs, nullptr, nullptr, nullptr, weights, n_clients);
+    if (rc) return rc;
+    fa.out[0] = dst;
+    fa.mirror[0] = dst_bf16;
+    const int64_t num_vecs = count / E;
+    int64_t blocks = (num_vecs + 511) / 512;
+    const int64_t cap = max_ctas > 0 ? max_ctas : 148 * 2;
+    if (blocks > cap) blocks = cap;
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (in_bf16) fedavg_local_kernel<true><<<(int)blocks, 512, 0, s>>>(fa, n_clients, num_vecs, bf16_begin, bf16_end);
+    else fedavg_local_kernel<false><<<(int)blocks, 512, 0, s>>>(fa, n_clients, num_vecs, bf16_begin, bf16_end);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dcad_fedavg_p2p(const void* const* arenas, const void* const* outs, const void* const* mirrors,
+                               const void* const* pads, const float* weights, int rank, int n_clients, int64_t count,
+                               int in_bf16, int mode, int64_t bf16_begin, int64_t bf16_end, uint32_t epoch,
+                               int max_ctas, void* stream) {
+    if (count <= 0) return 0;
+    const int E = in_bf16 ? 8 : 4;
+    if (count % E || (bf16_begin & 3) || (bf16_end & 3)) return DCAD_ERR_BAD_ALIGNMENT;
+    if (rank < 0 || rank >= n_clients || pads == nullptr) return DCAD_ERR_BAD_ARGUMENT;
+    if (mode == DCAD_FED_ONE_SHOT && outs == nullptr) return DCAD_ERR_BAD_ARGUMENT;
+    FedArgs fa;
+    int rc = fill_args(fa, arenas, outs, mirrors, pads, weights, n_clients);
+    if (rc) return rc;
+    const int64_t num_vecs = count / E;
+    const int64_t work = mode == DCAD_FED_TWO_SHOT ? (num_vecs + n_clients - 1) / n_clients : num_vecs;
+    int64_t blocks = (work + 511) / 512;
+    const int64_t cap = max_ctas > 0 ? max_ctas : 148;  // one co-resident wave: the end barrier needs all blocks to run
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (in_bf16)
+        fedavg_p2p_kernel<true><<<(int)blocks, 512, 0, s>>>(fa, rank, n_clients, num_vecs, mode, bf16_begin, bf16_end, epoch);
+    else
+        fedavg_p2p_kernel<false><<<(int)blocks, 512, 0, s>>>(fa, rank, n_clients, num_vecs, mode, bf16_begin, bf16_end, epoch);
+    return (int)cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// peer-memory runtime (these DO allocate / map memory; they are set-up calls, not hot-path calls)
+// ------------------------------------------------------------------------------------------------
+extern "C" int dcad_p2p_alloc(void** ptr, size_t bytes) {
+    DCAD_CUDA_TRY(cudaMalloc(ptr, bytes));
+    DCAD_CUDA_TRY(cudaMemset(*ptr, 0, bytes));
+    return 0;
+}
+extern "C" int dcad_p2p_free(void* ptr) { return (int)cudaFree(ptr); }
+extern "C" int dcad_p2p_ipc_get(void* ptr, void* handle64) {
+    cudaIpcMemHandle_t h;
+    DCAD_CUDA_TRY(cudaIpcGetMemHandle(&h, ptr));
+    memcpy(handle64, &h, sizeof(h));
+    return 0;
+}
+extern "C" int dcad_p2p_ipc_open(const void* handle64, void** ptr) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, sizeof(h));
+    DCAD_CUDA_TRY(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+extern "C" int dcad_p2p_ipc_close(void* ptr) { return (int)cudaIpcCloseMemHandle(ptr); }
+extern "C" int dcad_p2p_enable_peer_access(int peer_device) {
+    cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return 0; }
+    return (int)e;
+}
+extern "C" int dcad_p2p_can_access(int device, int peer, int* out) {
+    return (int)cudaDeviceCanAccessPeer(out, device, peer);
+}

@@ -336,6 +336,24 @@ int make_tensor_map_bf16_2d(CUtensorMap* out, const void* ptr, uint64_t rows, ui
     return 0;
 }
 
+// 3D bf16 tensor [d2][d1][d0] (d0 contiguous), box = 1 x b1 x b0; used by the attention kernels so that rows past the
+// end of a sequence are zero-filled instead of spilling into the next sample.
+int make_tensor_map_bf16_3d(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t ld1,
+                            uint64_t ld2, uint32_t b0, uint32_t b1) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) return DCAD_ERR_NO_DRIVER_ENTRY;
+    if ((reinterpret_cast<uintptr_t>(ptr) & 15u) || (ld1 * 2) % 16 != 0 || (ld2 * 2) % 16 != 0)
+        return DCAD_ERR_BAD_ALIGNMENT;
+    cuuint64_t gdim[3] = {d0, d1, d2};
+    cuuint64_t gstride[2] = {ld1 * 2, ld2 * 2};
+    cuuint32_t box[3] = {b0, b1, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : DCAD_ERR_TENSOR_MAP;
+}
+
 static int num_sms() {
     static int n = 0;
     if (n == 0) {

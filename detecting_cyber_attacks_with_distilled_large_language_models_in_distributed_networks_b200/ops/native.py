@@ -73,28 +73,34 @@ def ptr(t: Optional[torch.Tensor]) -> int:
 
 def _declare(L: ctypes.CDLL) -> None:
     def sig(name, argtypes, restype=c_int):
-        if hasattr(L, name):
-            f = getattr(L, name)
-            f.argtypes = argtypes
-            f.restype = restype
+        f = getattr(L, name)
+        f.argtypes = argtypes
+        f.restype = restype
 
-    P, I, F = c_void_p, c_int, c_float
+    P, I, F, L64, U32 = c_void_p, c_int, c_float, c_int64, c_uint32
     sig("dcad_version", [])
     sig("dcad_gemm_bf16", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, I, I, P])
-    sig("dcad_add_ln_fwd", [P, P, P, P, P, P, I, I, F, F, P, c_uint32, P])
-    sig("dcad_add_ln_bwd", [P, P, P, P, P, P, P, P, P, P, P, I, I, F, P, c_uint32, P])
-    sig("dcad_embed_ln_fwd", [P, P, P, P, P, P, P, P, I, I, I, F, F, P, c_uint32, P])
-    sig("dcad_embed_ln_bwd", [P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, F, P, c_uint32, P])
+    sig("dcad_add_ln_fwd", [P, P, P, P, P, P, I, I, F, F, P, U32, P])
+    sig("dcad_add_ln_bwd", [P, P, P, P, P, P, P, P, P, P, P, I, I, F, P, U32, P])
+    sig("dcad_embed_ln_fwd", [P, P, P, P, P, P, P, P, I, I, I, F, F, P, U32, P])
+    sig("dcad_embed_ln_bwd", [P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, F, P, U32, P])
     sig("dcad_colsum_bf16", [P, P, I, I, I, P])
-    sig("dcad_cls_head_train", [P, I, P, P, P, I, F, P, c_uint32, P, P, P, P, P, I, P])
-    sig("dcad_cls_head_eval", [P, I, P, P, P, I, P, P, P, P])
-    sig("dcad_adam_step", [P, P, P, P, P, c_int64, c_int64, c_int64, F, F, F, F, P, P])
+    sig("dcad_cls_head_train", [P, I, P, P, P, I, F, P, U32, P, P, P, P, P, I, P])
+    sig("dcad_cls_head_eval", [P, I, P, P, P, I, I, P, P, P, P, P])
+    sig("dcad_adam_step", [P, P, P, P, P, L64, L64, L64, L64, L64, F, F, F, F, P, P])
     sig("dcad_step_advance", [P, P])
-    sig("dcad_cast_f32_bf16", [P, P, c_int64, P])
-    sig("dcad_attn_fwd", [P, P, P, P, I, I, I, F, P, c_uint32, P])
-    sig("dcad_attn_bwd", [P, P, P, P, P, P, I, I, I, F, P, c_uint32, P])
-    sig("dcad_fedavg_local", [P, P, I, c_int64, I, F, P])
-    sig("dcad_fedavg_p2p", [P, P, P, I, I, c_int64, I, I, c_uint32, P])
+    sig("dcad_attn_fwd", [P, P, P, P, I, I, I, F, P, U32, P])
+    sig("dcad_attn_bwd", [P, P, P, P, P, P, I, I, I, F, P, U32, P])
+    sig("dcad_fedavg_local", [P, P, P, I, L64, I, P, L64, L64, I, P])
+    sig("dcad_fedavg_p2p", [P, P, P, P, P, I, I, L64, I, I, L64, L64, U32, I, P])
+    sig("dcad_p2p_alloc", [P, ctypes.c_size_t])
+    sig("dcad_p2p_free", [P])
+    sig("dcad_p2p_ipc_get", [P, P])
+    sig("dcad_p2p_ipc_open", [P, P])
+    sig("dcad_p2p_ipc_close", [P])
+    sig("dcad_p2p_enable_peer_access", [I])
+    sig("dcad_p2p_can_access", [I, I, P])
+    sig("dcad_cast_f32_bf16", [P, P, L64, P])
     sig("dcad_gather_rows_bf16", [P, P, I, I, I, I, P])
     sig("dcad_scatter_rows_bf16", [P, P, I, I, I, I, P])
 
@@ -141,3 +147,219 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_major: i
                               1 if accumulate else 0, block_n, max_ctas, stream_ptr(stream))
     check(rc, "dcad_gemm_bf16")
     return out
+
+
+# --------------------------------------------------------------------------------------------------------------
+# LayerNorm family
+# --------------------------------------------------------------------------------------------------------------
+def add_ln_fwd(a, res, gamma, beta, out, rstd, *, eps=1e-12, p_drop=0.0, rng=None, stream_id=0, stream=None):
+    rows, cols = a.shape
+    check(lib().dcad_add_ln_fwd(ptr(a), ptr(res), ptr(gamma), ptr(beta), ptr(out), ptr(rstd), rows, cols, eps,
+                                p_drop, ptr(rng), stream_id, stream_ptr(stream)), "dcad_add_ln_fwd")
+    return out
+
+
+def add_ln_bwd(dy1, dy2, y, gamma, beta, rstd, dz, da, dgamma, dbeta, dbias, *, p_drop=0.0, rng=None, stream_id=0,
+               stream=None):
+    rows, cols = y.shape
+    check(lib().dcad_add_ln_bwd(ptr(dy1), ptr(dy2), ptr(y), ptr(gamma), ptr(beta), ptr(rstd), ptr(dz), ptr(da),
+                                ptr(dgamma), ptr(dbeta), ptr(dbias), rows, cols, p_drop, ptr(rng), stream_id,
+                                stream_ptr(stream)), "dcad_add_ln_bwd")
+
+
+def embed_ln_fwd(ids, word, pos, gamma, beta, out, mean, rstd, seq, *, eps=1e-12, p_drop=0.0, rng=None, stream_id=0,
+                 stream=None):
+    rows, cols = out.shape
+    assert ids.dtype == torch.int32
+    check(lib().dcad_embed_ln_fwd(ptr(ids), ptr(word), ptr(pos), ptr(gamma), ptr(beta), ptr(out), ptr(mean),
+                                  ptr(rstd), rows, seq, cols, eps, p_drop, ptr(rng), stream_id, stream_ptr(stream)),
+          "dcad_embed_ln_fwd")
+    return out
+
+
+def embed_ln_bwd(dy1, dy2, ids, word, pos, gamma, mean, rstd, dword, dpos, dgamma, dbeta, seq, *, p_drop=0.0,
+                 rng=None, stream_id=0, stream=None):
+    rows, cols = dy1.shape
+    check(lib().dcad_embed_ln_bwd(ptr(dy1), ptr(dy2), ptr(ids), ptr(word), ptr(pos), ptr(gamma), ptr(mean),
+                                  ptr(rstd), ptr(dword), ptr(dpos), ptr(dgamma), ptr(dbeta), rows, seq, cols, p_drop,
+                                  ptr(rng), stream_id, stream_ptr(stream)), "dcad_embed_ln_bwd")
+
+
+def colsum_bf16(x, out, stream=None):
+    rows, cols = x.shape
+    check(lib().dcad_colsum_bf16(ptr(x), ptr(out), rows, cols, x.stride(0), stream_ptr(stream)), "dcad_colsum_bf16")
+    return out
+
+
+# --------------------------------------------------------------------------------------------------------------
+# classifier head
+# --------------------------------------------------------------------------------------------------------------
+def cls_head_train(h, sample_stride, W, bias, labels, batch, loss_accum, logits, dW, db, dcls, *, cols=768,
+                   p_drop=0.0, rng=None, stream_id=0, stream=None):
+    assert labels.dtype == torch.int32
+    check(lib().dcad_cls_head_train(ptr(h), sample_stride, ptr(W), ptr(bias), ptr(labels), batch, p_drop, ptr(rng),
+                                    stream_id, ptr(loss_accum), ptr(logits), ptr(dW), ptr(db), ptr(dcls), cols,
+                                    stream_ptr(stream)), "dcad_cls_head_train")
+
+
+def cls_head_eval(h, sample_stride, W, bias, labels, batch, loss_accum, confusion, probs=None, preds=None, *,
+                  cols=768, stream=None):
+    assert labels.dtype == torch.int32
+    check(lib().dcad_cls_head_eval(ptr(h), sample_stride, ptr(W), ptr(bias), ptr(labels), batch, cols,
+                                   ptr(loss_accum), ptr(confusion), ptr(probs), ptr(preds), stream_ptr(stream)),
+          "dcad_cls_head_eval")
+
+
+# --------------------------------------------------------------------------------------------------------------
+# optimizer
+# --------------------------------------------------------------------------------------------------------------
+def adam_step(p, g, m, v, p_bf16, n, bf16_begin, bf16_end, zero_begin, zero_end, lr, beta1, beta2, eps, state,
+              stream=None):
+    check(lib().dcad_adam_step(ptr(p), ptr(g), ptr(m), ptr(v), ptr(p_bf16), n, bf16_begin, bf16_end, zero_begin,
+                               zero_end, lr, beta1, beta2, eps, ptr(state), stream_ptr(stream)), "dcad_adam_step")
+
+
+def step_advance(state, stream=None):
+    check(lib().dcad_step_advance(ptr(state), stream_ptr(stream)), "dcad_step_advance")
+
+
+# --------------------------------------------------------------------------------------------------------------
+# attention
+# --------------------------------------------------------------------------------------------------------------
+def attn_fwd(qkv, ctx, lse2, lens, B, S, H, *, p_drop=0.0, rng=None, stream_id=0, stream=None):
+    check(lib().dcad_attn_fwd(ptr(qkv), ptr(ctx), ptr(lse2), ptr(lens), B, S, H, p_drop, ptr(rng), stream_id,
+                              stream_ptr(stream)), "dcad_attn_fwd")
+    return ctx
+
+
+def attn_bwd(qkv, ctx, dctx, lse2, dqkv, lens, B, S, H, *, p_drop=0.0, rng=None, stream_id=0, stream=None):
+    check(lib().dcad_attn_bwd(ptr(qkv), ptr(ctx), ptr(dctx), ptr(lse2), ptr(dqkv), ptr(lens), B, S, H, p_drop,
+                              ptr(rng), stream_id, stream_ptr(stream)), "dcad_attn_bwd")
+    return dqkv
+
+
+# --------------------------------------------------------------------------------------------------------------
+# FedAvg + peer runtime
+# --------------------------------------------------------------------------------------------------------------
+def _ptr_array(ptrs):
+    if ptrs is None:
+        return None
+    arr = (c_void_p * len(ptrs))()
+    for i, p_ in enumerate(ptrs):
+        arr[i] = p_
+    return arr
+
+
+def _float_array(vals):
+    if vals is None:
+        return None
+    arr = (c_float * len(vals))()
+    for i, v_ in enumerate(vals):
+        arr[i] = float(v_)
+    return arr
+
+
+def fedavg_local(src_ptrs, dst_ptr, count, *, dst_bf16_ptr=0, in_bf16=False, weights=None, bf16_begin=0, bf16_end=0,
+                 max_ctas=0, stream=None):
+    """dst = mean_k src_k over raw device pointers (all reachable from the current device)."""
+    check(lib().dcad_fedavg_local(_ptr_array(src_ptrs), dst_ptr, dst_bf16_ptr, len(src_ptrs), count,
+                                  1 if in_bf16 else 0, _float_array(weights), bf16_begin, bf16_end, max_ctas,
+                                  stream_ptr(stream)), "dcad_fedavg_local")
+
+
+def fedavg_p2p(arena_ptrs, pad_ptrs, rank, count, epoch, *, out_ptrs=None, mirror_ptrs=None, weights=None,
+               in_bf16=False, mode=0, bf16_begin=0, bf16_end=0, max_ctas=0, stream=None):
+    check(lib().dcad_fedavg_p2p(_ptr_array(arena_ptrs), _ptr_array(out_ptrs), _ptr_array(mirror_ptrs),
+                                _ptr_array(pad_ptrs), _float_array(weights), rank, len(arena_ptrs), count,
+                                1 if in_bf16 else 0, mode, bf16_begin, bf16_end, epoch, max_ctas,
+                                stream_ptr(stream)), "dcad_fedavg_p2p")
+
+
+def p2p_alloc(nbytes: int) -> int:
+    out = c_void_p()
+    check(lib().dcad_p2p_alloc(ctypes.byref(out), nbytes), "dcad_p2p_alloc")
+    return out.value
+
+
+def p2p_free(p: int) -> None:
+    check(lib().dcad_p2p_free(p), "dcad_p2p_free")
+
+
+def p2p_ipc_get(p: int) -> bytes:
+    buf = ctypes.create_string_buffer(64)
+    check(lib().dcad_p2p_ipc_get(p, buf), "dcad_p2p_ipc_get")
+    return buf.raw
+
+
+def p2p_ipc_open(handle: bytes) -> int:
+    out = c_void_p()
+    buf = ctypes.create_string_buffer(handle, 64)
+    check(lib().dcad_p2p_ipc_open(buf, ctypes.byref(out)), "dcad_p2p_ipc_open")
+    return out.value
+
+
+def p2p_ipc_close(p: int) -> None:
+    check(lib().dcad_p2p_ipc_close(p), "dcad_p2p_ipc_close")
+
+
+def p2p_enable_peer_access(peer: int) -> None:
+    check(lib().dcad_p2p_enable_peer_access(peer), "dcad_p2p_enable_peer_access")
+
+
+def p2p_can_access(dev: int, peer: int) -> bool:
+    out = c_int(0)
+    check(lib().dcad_p2p_can_access(dev, peer, ctypes.byref(out)), "dcad_p2p_can_access")
+    return bool(out.value)
+
+
+class RawDeviceBuffer:
+    """A device allocation made by the native runtime, viewable as torch tensors (no copy) through
+    ``__cuda_array_interface__``.  Used for peer-mappable arenas and signal pads."""
+
+    def __init__(self, ptr_: int, nbytes: int, owner: bool = True, ipc: bool = False):
+        self.ptr, self.nbytes, self.owner, self.ipc = ptr_, nbytes, owner, ipc
+
+    def view(self, dtype: torch.dtype, offset_bytes: int = 0, numel: Optional[int] = None) -> torch.Tensor:
+        itemsize = torch.empty((), dtype=dtype).element_size()
+        if numel is None:
+            numel = (self.nbytes - offset_bytes) // itemsize
+        typestr = {torch.float32: "<f4", torch.bfloat16: "<u2", torch.int32: "<i4", torch.uint8: "|u1",
+                   torch.int64: "<i8", torch.uint32: "<u4"}[dtype]
+
+        class _Iface:
+            pass
+
+        o = _Iface()
+        o.__cuda_array_interface__ = {"shape": (numel,), "typestr": typestr, "data": (self.ptr + offset_bytes, False),
+                                      "version": 3, "strides": None}
+        o._keepalive = self
+        t = torch.as_tensor(o, device=torch.device("cuda", torch.cuda.current_device()))
+        if dtype == torch.bfloat16:
+            t = t.view(torch.bfloat16)
+        t._dcad_owner = self  # keep the allocation alive as long as any view lives
+        return t
+
+    def free(self) -> None:
+        if self.ptr:
+            if self.ipc:
+                p2p_ipc_close(self.ptr)
+            elif self.owner:
+                p2p_free(self.ptr)
+            self.ptr = 0
+
+
+def cast_f32_bf16(src, dst, stream=None):
+    check(lib().dcad_cast_f32_bf16(ptr(src), ptr(dst), src.numel(), stream_ptr(stream)), "dcad_cast_f32_bf16")
+    return dst
+
+
+def gather_rows_bf16(src, dst, rows, cols, every, stream=None):
+    check(lib().dcad_gather_rows_bf16(ptr(src), ptr(dst), rows, cols, every, src.stride(0), stream_ptr(stream)),
+          "dcad_gather_rows_bf16")
+    return dst
+
+
+def scatter_rows_bf16(src, dst, rows, cols, every, stream=None):
+    check(lib().dcad_scatter_rows_bf16(ptr(src), ptr(dst), rows, cols, every, dst.stride(0), stream_ptr(stream)),
+          "dcad_scatter_rows_bf16")
+    return dst

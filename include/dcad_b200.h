@@ -9,6 +9,7 @@
 #ifndef DCAD_B200_H_
 #define DCAD_B200_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -47,6 +48,92 @@ int dcad_version(void);
 int dcad_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major, int lda,
                    int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
                    int out_fp32, int accumulate, int block_n, int max_ctas, void* stream);
+
+/* ---- LayerNorm family (warp per row; cols must be 256/512/768/1024) ----
+ * rng points at two uint64 in device memory: {seed, step}; dropout masks are a pure function of
+ * (seed, step, stream_id, element index), so backward regenerates them and CUDA-graph replays get fresh masks.
+ */
+/* out = LayerNorm(dropout_p(a) + res) * gamma + beta; rstd[rows] saved for backward.  res may be NULL.
+ * Replaces HF sa_layer_norm / output_layer_norm + FFN dropout (modeling_distilbert.py:227,257,261). */
+int dcad_add_ln_fwd(const void* a, const void* res, const float* gamma, const float* beta, void* out, float* rstd,
+                    int rows, int cols, float eps, float p_drop, const uint64_t* rng, uint32_t stream_id,
+                    void* stream);
+/* backward of dcad_add_ln_fwd.  dy = dy1 (+ dy2 when non-NULL).  dz = grad wrt res (and wrt the pre-dropout sum);
+ * da = grad wrt a (only written when p_drop > 0, otherwise it equals dz).  dgamma/dbeta/dbias (dbias may be NULL;
+ * it is colsum(da), the bias gradient of the Linear that produced a) are ACCUMULATED into zero-initialised buffers. */
+int dcad_add_ln_bwd(const void* dy1, const void* dy2, const void* y, const float* gamma, const float* beta,
+                    const float* rstd, void* dz, void* da, float* dgamma, float* dbeta, float* dbias, int rows,
+                    int cols, float p_drop, const uint64_t* rng, uint32_t stream_id, void* stream);
+/* out = dropout_p(LayerNorm(word[ids[r]] + pos[r % seq])).  Replaces HF Embeddings (modeling_distilbert.py:96-122). */
+int dcad_embed_ln_fwd(const int32_t* ids, const float* word, const float* pos, const float* gamma, const float* beta,
+                      void* out, float* mean, float* rstd, int rows, int seq, int cols, float eps, float p_drop,
+                      const uint64_t* rng, uint32_t stream_id, void* stream);
+/* backward: scatter-adds into dword [vocab, cols] / dpos [max_pos, cols] and accumulates dgamma / dbeta. */
+int dcad_embed_ln_bwd(const void* dy1, const void* dy2, const int32_t* ids, const float* word, const float* pos,
+                      const float* gamma, const float* mean, const float* rstd, float* dword, float* dpos,
+                      float* dgamma, float* dbeta, int rows, int seq, int cols, float p_drop, const uint64_t* rng,
+                      uint32_t stream_id, void* stream);
+/* out[c] += sum_r x[r, c]  (bf16 in, fp32 accumulate): bias gradients (autograd of nn.Linear bias). */
+int dcad_colsum_bf16(const void* x, float* out, int rows, int cols, int ld, void* stream);
+
+/* ---- classifier head + cross-entropy (reference client1.py:62-64,108 and, for eval, :134-142) ----
+ * h: bf16, CLS vector of sample s starts at h + s * sample_stride.  loss_accum[0] += batch-mean loss,
+ * loss_accum[1] += 1.  dW [2, cols] / db [2] are accumulated; dcls [batch, cols] bf16 is written. */
+int dcad_cls_head_train(const void* h, int sample_stride, const float* W, const float* bias, const int32_t* labels,
+                        int batch, float p_drop, const uint64_t* rng, uint32_t stream_id, float* loss_accum,
+                        float* logits, float* dW, float* db, void* dcls, int cols, void* stream);
+/* confusion[true * 2 + pred] += 1; probs[s] = softmax(logits)[1]; preds[s] = argmax (any output may be NULL). */
+int dcad_cls_head_eval(const void* h, int sample_stride, const float* W, const float* bias, const int32_t* labels,
+                       int batch, int cols, float* loss_accum, int32_t* confusion, float* probs, int32_t* preds,
+                       void* stream);
+
+/* ---- optimizer (reference client1.py:106,110,380: Adam(lr=2e-5) + zero_grad) ----
+ * One launch over the flat arena.  Elements in [bf16_begin, bf16_end) are also written as bf16 to
+ * p_bf16[i - bf16_begin]; gradients in [zero_begin, zero_end) are cleared after use.  The step number is
+ * state[1] + 1 (device memory), advanced by dcad_step_advance at the end of each training step. */
+int dcad_adam_step(float* p, float* g, float* m, float* v, void* p_bf16, int64_t n, int64_t bf16_begin,
+                   int64_t bf16_end, int64_t zero_begin, int64_t zero_end, float lr, float beta1, float beta2,
+                   float eps, const uint64_t* state, void* stream);
+int dcad_step_advance(uint64_t* state, void* stream);
+
+/* ---- fused attention, seq <= 128, head_dim 64 (HF modeling_distilbert.py:126-151 + attention dropout) ----
+ * qkv [B*S, 3*H*64] bf16 (Q | K | V), ctx [B*S, H*64] bf16, lse2 [B*H*128] fp32, lens [B] valid key counts or NULL. */
+int dcad_attn_fwd(const void* qkv, void* ctx, float* lse2, const int32_t* lens, int B, int S, int H, float p_drop,
+                  const uint64_t* rng, uint32_t stream_id, void* stream);
+int dcad_attn_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse2, void* dqkv,
+                  const int32_t* lens, int B, int S, int H, float p_drop, const uint64_t* rng, uint32_t stream_id,
+                  void* stream);
+
+/* ---- FedAvg (reference server.py:67-79) ---- */
+#define DCAD_FED_MAX_CLIENTS 16
+#define DCAD_FED_TWO_SHOT 0
+#define DCAD_FED_ONE_SHOT 1
+#define DCAD_FED_PAD_WORDS 64 /* uint32 words per signal pad */
+/* dst = mean over clients of srcs[k] (fp32 accumulate, client order, then / N; or sum_k weights[k]*srcs[k]).
+ * srcs / weights are HOST arrays.  Optional bf16 mirror of elements [bf16_begin, bf16_end). */
+int dcad_fedavg_local(const void* const* srcs, void* dst, void* dst_bf16, int n_clients, int64_t count, int in_bf16,
+                      const float* weights, int64_t bf16_begin, int64_t bf16_end, int max_ctas, void* stream);
+/* One launch per rank; the N kernels (one per GPU) handshake through `pads` (peer-mapped, DCAD_FED_PAD_WORDS uint32
+ * each, zero-initialised, epoch strictly increasing per call).  Two-shot works in place on `arenas`; one-shot writes
+ * outs[rank].  mirrors[k] (may be NULL) receive the bf16 copy.  All pointer arrays are HOST arrays of N entries. */
+int dcad_fedavg_p2p(const void* const* arenas, const void* const* outs, const void* const* mirrors,
+                    const void* const* pads, const float* weights, int rank, int n_clients, int64_t count,
+                    int in_bf16, int mode, int64_t bf16_begin, int64_t bf16_end, uint32_t epoch, int max_ctas,
+                    void* stream);
+
+/* ---- peer-memory runtime (set-up calls; these allocate / map) ---- */
+int dcad_p2p_alloc(void** ptr, size_t bytes);
+int dcad_p2p_free(void* ptr);
+int dcad_p2p_ipc_get(void* ptr, void* handle64);
+int dcad_p2p_ipc_open(const void* handle64, void** ptr);
+int dcad_p2p_ipc_close(void* ptr);
+int dcad_p2p_enable_peer_access(int peer_device);
+int dcad_p2p_can_access(int device, int peer, int* out);
+
+/* ---- misc ---- */
+int dcad_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
+int dcad_gather_rows_bf16(const void* src, void* dst, int rows, int cols, int every, int ld_src, void* stream);
+int dcad_scatter_rows_bf16(const void* src, void* dst, int rows, int cols, int every, int ld_dst, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,321 @@
+"""GPU numerics tests: every hand-written sm_100a kernel against a plain PyTorch fp32 reference of the same op."""
+from __future__ import annotations
+
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+PKG = "detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200"
+
+
+@pytest.fixture(scope="module")
+def nv():
+    import importlib
+
+    mod = importlib.import_module(f"{PKG}.ops.native")
+    assert mod.lib().dcad_version() >= 100
+    return mod
+
+
+def _rng_state(seed=1234, step=0):
+    return torch.tensor([seed, step], dtype=torch.int64, device="cuda")
+
+
+def _rel(a, b):
+    return ((a.float() - b.float()).abs().max() / (b.float().abs().max() + 1e-6)).item()
+
+
+# ---------------------------------------------------------------- GEMM
+@pytest.mark.parametrize("a_major,b_major,bn", [(0, 0, 96), (0, 0, 256), (0, 1, 128), (1, 1, 128), (1, 1, 64)])
+def test_gemm_matches_matmul(nv, a_major, b_major, bn):
+    torch.manual_seed(0)
+    M, N, K = 384, 768, 320
+    a = torch.randn((M, K) if a_major == 0 else (K, M), device="cuda").bfloat16()
+    b = torch.randn((N, K) if b_major == 0 else (K, N), device="cuda").bfloat16()
+    out = torch.empty(M, N, device="cuda", dtype=torch.float32)
+    nv.gemm_bf16(a, b, out, a_major=a_major, b_major=b_major, block_n=bn)
+    A = a.float() if a_major == 0 else a.float().t()
+    B = b.float() if b_major == 0 else b.float().t()
+    ref = A @ B.t()
+    assert _rel(out, ref) < 1e-3
+
+
+def test_gemm_epilogues(nv):
+    torch.manual_seed(1)
+    M, N, K = 256, 512, 256
+    a = torch.randn(M, K, device="cuda").bfloat16()
+    w = (torch.randn(N, K, device="cuda") * 0.05).bfloat16()
+    bias = torch.randn(N, device="cuda")
+    pre_ref = a.float() @ w.float().t() + bias
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    pre = torch.empty_like(out)
+    nv.gemm_bf16(a, w, out, bias=bias, aux_out=pre, epi=nv.EPI_BIAS_GELU)
+    assert _rel(pre, pre_ref) < 1e-2
+    assert _rel(out, F.gelu(pre_ref)) < 1e-2
+    # dgelu: D = (dY @ W) * gelu'(pre)
+    dy = torch.randn(M, N, device="cuda").bfloat16()
+    w2 = (torch.randn(N, K, device="cuda") * 0.05).bfloat16()  # [N,K] row-major == B[K_red=N][N_out=K] MN-major
+    pre2 = torch.randn(M, K, device="cuda").bfloat16()
+    d = torch.empty(M, K, device="cuda", dtype=torch.bfloat16)
+    nv.gemm_bf16(dy, w2, d, b_major=nv.MAJOR_MN, aux=pre2, epi=nv.EPI_DGELU, block_n=128)
+    x = pre2.float().requires_grad_(True)
+    F.gelu(x).backward(torch.ones_like(x))
+    ref = (dy.float() @ w2.float()) * x.grad
+    assert _rel(d, ref) < 1e-2
+
+
+# ---------------------------------------------------------------- LayerNorm
+def test_add_ln_fwd_bwd(nv):
+    torch.manual_seed(2)
+    rows, cols = 300, 768
+    a = torch.randn(rows, cols, device="cuda").bfloat16()
+    res = torch.randn(rows, cols, device="cuda").bfloat16()
+    gamma = torch.rand(cols, device="cuda") + 0.5
+    beta = torch.randn(cols, device="cuda") * 0.1
+    out = torch.empty_like(a)
+    rstd = torch.empty(rows, device="cuda")
+    nv.add_ln_fwd(a, res, gamma, beta, out, rstd, eps=1e-12)
+    z = (a.float() + res.float()).requires_grad_(True)
+    g_ = gamma.clone().requires_grad_(True)
+    b_ = beta.clone().requires_grad_(True)
+    ref = F.layer_norm(z, (cols,), g_, b_, 1e-12)
+    assert _rel(out, ref) < 1e-2
+    dy1 = torch.randn(rows, cols, device="cuda").bfloat16()
+    dy2 = torch.randn(rows, cols, device="cuda").bfloat16()
+    ref.backward(dy1.float() + dy2.float())
+    dz = torch.empty_like(a)
+    dgamma = torch.zeros(cols, device="cuda")
+    dbeta = torch.zeros(cols, device="cuda")
+    dbias = torch.zeros(cols, device="cuda")
+    nv.add_ln_bwd(dy1, dy2, out, gamma, beta, rstd, dz, None, dgamma, dbeta, dbias)
+    assert _rel(dz, z.grad) < 2e-2
+    assert _rel(dgamma, g_.grad) < 2e-2
+    assert _rel(dbeta, b_.grad) < 1e-2
+    assert _rel(dbias, z.grad.sum(0)) < 3e-2
+
+
+def test_add_ln_dropout_consistency(nv):
+    """Dropout masks are regenerated in backward from (seed, step, stream, index): da must be zero exactly where the
+    forward dropped, and the keep rate must match 1-p."""
+    torch.manual_seed(3)
+    rows, cols, p = 256, 768, 0.1
+    a = torch.ones(rows, cols, device="cuda").bfloat16()
+    gamma = torch.ones(cols, device="cuda")
+    beta = torch.zeros(cols, device="cuda")
+    out = torch.empty_like(a)
+    rstd = torch.empty(rows, device="cuda")
+    rng = _rng_state()
+    nv.add_ln_fwd(a, None, gamma, beta, out, rstd, p_drop=p, rng=rng, stream_id=7)
+    # with a == 1 everywhere, dropped elements are the row minimum after LN
+    dropped = out.float() < 0
+    rate = dropped.float().mean().item()
+    assert abs(rate - p) < 0.01
+    dy = torch.ones_like(a)
+    dz = torch.empty_like(a)
+    da = torch.empty_like(a)
+    dg = torch.zeros(cols, device="cuda")
+    db = torch.zeros(cols, device="cuda")
+    nv.add_ln_bwd(torch.randn_like(a.float()).bfloat16(), None, out, gamma, beta, rstd, dz, da, dg, db, None, p_drop=p,
+                  rng=rng, stream_id=7)
+    assert torch.all(da[dropped] == 0)
+    kept = ~dropped
+    assert torch.allclose(da[kept].float(), dz[kept].float() / (1 - p), rtol=2e-2, atol=1e-3)
+    # a different step gives a different mask
+    rng2 = _rng_state(step=1)
+    out2 = torch.empty_like(a)
+    nv.add_ln_fwd(a, None, gamma, beta, out2, rstd, p_drop=p, rng=rng2, stream_id=7)
+    assert ((out2.float() < 0) != dropped).any()
+
+
+def test_embed_ln_fwd_bwd(nv):
+    torch.manual_seed(4)
+    B, S, cols, vocab = 4, 128, 768, 1000
+    ids = torch.randint(0, vocab, (B * S,), device="cuda", dtype=torch.int32)
+    word = (torch.randn(vocab, cols, device="cuda") * 0.02).requires_grad_(True)
+    pos = (torch.randn(512, cols, device="cuda") * 0.02).requires_grad_(True)
+    gamma = (torch.rand(cols, device="cuda") + 0.5).requires_grad_(True)
+    beta = (torch.randn(cols, device="cuda") * 0.1).requires_grad_(True)
+    out = torch.empty(B * S, cols, device="cuda", dtype=torch.bfloat16)
+    mean = torch.empty(B * S, device="cuda")
+    rstd = torch.empty(B * S, device="cuda")
+    nv.embed_ln_fwd(ids, word.detach(), pos.detach(), gamma.detach(), beta.detach(), out, mean, rstd, S)
+    x = word[ids.long()] + pos[torch.arange(B * S, device="cuda") % S]
+    ref = F.layer_norm(x, (cols,), gamma, beta, 1e-12)
+    assert _rel(out, ref) < 1e-2
+    dy = torch.randn(B * S, cols, device="cuda").bfloat16()
+    ref.backward(dy.float())
+    dword = torch.zeros(vocab, cols, device="cuda")
+    dpos = torch.zeros(512, cols, device="cuda")
+    dg = torch.zeros(cols, device="cuda")
+    db = torch.zeros(cols, device="cuda")
+    nv.embed_ln_bwd(dy, None, ids, word.detach(), pos.detach(), gamma.detach(), mean, rstd, dword, dpos, dg, db, S)
+    assert _rel(dword, word.grad) < 1e-2
+    assert _rel(dpos, pos.grad) < 1e-2
+    assert _rel(dg, gamma.grad) < 1e-2
+    assert _rel(db, beta.grad) < 1e-2
+
+
+def test_colsum(nv):
+    x = torch.randn(2048, 2304, device="cuda").bfloat16()
+    out = torch.zeros(2304, device="cuda")
+    nv.colsum_bf16(x, out)
+    assert _rel(out, x.float().sum(0)) < 1e-3
+
+
+# ---------------------------------------------------------------- classifier head
+def test_cls_head_train_and_eval(nv):
+    torch.manual_seed(5)
+    B, S, cols = 16, 128, 768
+    h = torch.randn(B * S, cols, device="cuda").bfloat16()
+    W = (torch.randn(2, cols, device="cuda") * 0.05).requires_grad_(True)
+    bias = torch.randn(2, device="cuda").requires_grad_(True)
+    labels = torch.randint(0, 2, (B,), device="cuda", dtype=torch.int32)
+    loss_accum = torch.zeros(2, device="cuda")
+    logits = torch.empty(B, 2, device="cuda")
+    dW = torch.zeros(2, cols, device="cuda")
+    db = torch.zeros(2, device="cuda")
+    dcls = torch.empty(B, cols, device="cuda", dtype=torch.bfloat16)
+    nv.cls_head_train(h, S * cols, W.detach(), bias.detach(), labels, B, loss_accum, logits, dW, db, dcls)
+    x = h.view(B, S, cols)[:, 0, :].float().requires_grad_(True)
+    ref_logits = x @ W.t() + bias
+    ref_loss = F.cross_entropy(ref_logits, labels.long())
+    ref_loss.backward()
+    assert torch.allclose(logits, ref_logits, rtol=1e-4, atol=1e-4)
+    assert abs(loss_accum[0].item() - ref_loss.item()) < 1e-4 and loss_accum[1].item() == 1.0
+    assert _rel(dW, W.grad) < 1e-4
+    assert _rel(db, bias.grad) < 1e-4
+    assert _rel(dcls, x.grad) < 1e-2
+    # eval variant: confusion matrix + loss + probabilities
+    la = torch.zeros(2, device="cuda")
+    conf = torch.zeros(4, device="cuda", dtype=torch.int32)
+    probs = torch.empty(B, device="cuda")
+    preds = torch.empty(B, device="cuda", dtype=torch.int32)
+    nv.cls_head_eval(h, S * cols, W.detach(), bias.detach(), labels, B, la, conf, probs, preds)
+    rp = ref_logits.argmax(1)
+    assert torch.equal(preds.long(), rp)
+    assert torch.allclose(probs, torch.softmax(ref_logits, 1)[:, 1].detach(), atol=1e-5)
+    cm = torch.zeros(2, 2, dtype=torch.int64)
+    for t, p_ in zip(labels.tolist(), rp.tolist()):
+        cm[t, p_] += 1
+    assert conf.cpu().view(2, 2).long().equal(cm)
+    assert abs(la[0].item() - ref_loss.item()) < 1e-4
+
+
+# ---------------------------------------------------------------- Adam
+def test_adam_matches_torch(nv):
+    torch.manual_seed(6)
+    n = 4096 * 3
+    p0 = torch.randn(n, device="cuda")
+    p = p0.clone()
+    m = torch.zeros(n, device="cuda")
+    v = torch.zeros(n, device="cuda")
+    pb = torch.zeros(n // 2, device="cuda", dtype=torch.bfloat16)
+    state = _rng_state(step=0)
+    ref_p = p0.clone().requires_grad_(True)
+    opt = torch.optim.Adam([ref_p], lr=2e-5)
+    for step in range(5):
+        g = torch.randn(n, device="cuda")
+        gk = g.clone()
+        ref_p.grad = g.clone()
+        opt.step()
+        nv.adam_step(p, gk, m, v, pb, n, n // 2, n, 0, n // 2, 2e-5, 0.9, 0.999, 1e-8, state)
+        nv.step_advance(state)
+        assert torch.all(gk[: n // 2] == 0) and torch.equal(gk[n // 2:], g[n // 2:])
+    assert torch.allclose(p, ref_p.detach(), rtol=1e-5, atol=1e-7)
+    assert torch.equal(pb, p[n // 2:].bfloat16())
+    assert state[1].item() == 5
+
+
+# ---------------------------------------------------------------- attention
+def _attn_ref(qkv, lens, B, S, H):
+    D = 64
+    q, k, v = qkv.float().view(B, S, 3, H, D).permute(2, 0, 3, 1, 4)
+    s = (q @ k.transpose(-1, -2)) * 0.125
+    mask = torch.arange(S, device=qkv.device)[None, :] >= lens[:, None].long()
+    s = s.masked_fill(mask[:, None, None, :], float("-inf"))
+    p = torch.softmax(s, -1)
+    o = p @ v
+    return o.permute(0, 2, 1, 3).reshape(B * S, H * D)
+
+
+@pytest.mark.parametrize("S", [128, 96])
+def test_attention_fwd_bwd(nv, S):
+    torch.manual_seed(7)
+    B, H = 3, 12
+    qkv = torch.randn(B * S, 3 * H * 64, device="cuda").bfloat16()
+    lens = torch.tensor([S, 57, 5], device="cuda", dtype=torch.int32)
+    ctx = torch.empty(B * S, H * 64, device="cuda", dtype=torch.bfloat16)
+    lse2 = torch.empty(B * H * 128, device="cuda")
+    nv.attn_fwd(qkv, ctx, lse2, lens, B, S, H)
+    q32 = qkv.float().requires_grad_(True)
+    ref = _attn_ref(q32, lens, B, S, H)
+    assert _rel(ctx, ref) < 2e-2
+    dctx = torch.randn(B * S, H * 64, device="cuda").bfloat16()
+    ref.backward(dctx.float())
+    dqkv = torch.empty_like(qkv)
+    nv.attn_bwd(qkv, ctx, dctx, lse2, dqkv, lens, B, S, H)
+    assert _rel(dqkv, q32.grad) < 3e-2
+    # padded keys receive exactly zero dK/dV
+    g = dqkv.view(B, S, 3, H * 64)
+    assert torch.all(g[1, 57:, 1:] == 0) and torch.all(g[2, 5:, 1:] == 0)
+
+
+def test_attention_dropout_statistics(nv):
+    torch.manual_seed(8)
+    B, S, H, p = 2, 128, 12, 0.1
+    qkv = torch.zeros(B * S, 3 * H * 64, device="cuda").bfloat16()
+    qkv.view(B * S, 3, H * 64)[:, 2, :] = 1.0  # V == 1, uniform attention -> ctx == sum of kept probs / (1-p)
+    ctx = torch.empty(B * S, H * 64, device="cuda", dtype=torch.bfloat16)
+    lse2 = torch.empty(B * H * 128, device="cuda")
+    rng = _rng_state()
+    nv.attn_fwd(qkv, ctx, lse2, None, B, S, H, p_drop=p, rng=rng, stream_id=3)
+    m = ctx.float().mean().item()
+    assert abs(m - 1.0) < 0.01          # unbiased
+    assert ctx.float().std().item() > 1e-3  # but actually random
+
+
+# ---------------------------------------------------------------- FedAvg (single GPU local kernel)
+@pytest.mark.parametrize("n_clients", [2, 3, 8])
+def test_fedavg_local_matches_reference_loop(nv, n_clients):
+    torch.manual_seed(9)
+    count = 1 << 20
+    srcs = [torch.randn(count, device="cuda") for _ in range(n_clients)]
+    dst = torch.empty(count, device="cuda")
+    mirror = torch.zeros(count // 2, device="cuda", dtype=torch.bfloat16)
+    nv.fedavg_local([s.data_ptr() for s in srcs], dst.data_ptr(), count, dst_bf16_ptr=mirror.data_ptr(),
+                    bf16_begin=count // 2, bf16_end=count)
+    # the reference's arithmetic (server.py:72-76): base += others in order, then true division
+    # (run on the CPU: torch's CUDA scalar division multiplies by the reciprocal, which differs by 1 ulp for N=3)
+    base = srcs[0].cpu().clone()
+    for s in srcs[1:]:
+        base += s.cpu()
+    base /= n_clients
+    assert torch.equal(dst.cpu(), base)  # bit parity
+    assert torch.equal(mirror.cpu(), base[count // 2:].bfloat16())
+
+
+def test_fedavg_local_weighted_and_bf16(nv):
+    count = 1 << 16
+    srcs = [torch.randn(count, device="cuda").bfloat16() for _ in range(4)]
+    dst = torch.empty(count, device="cuda", dtype=torch.bfloat16)
+    w = [0.1, 0.2, 0.3, 0.4]
+    nv.fedavg_local([s.data_ptr() for s in srcs], dst.data_ptr(), count, in_bf16=True, weights=w)
+    ref = sum(wi * s.float() for wi, s in zip(w, srcs))
+    assert _rel(dst, ref) < 1e-2
+
+
+def test_raw_buffer_views_and_cast(nv):
+    p = nv.p2p_alloc(4096)
+    buf = nv.RawDeviceBuffer(p, 4096)
+    t = buf.view(torch.float32)
+    assert t.numel() == 1024 and t.data_ptr() == p and torch.all(t == 0)
+    t.fill_(1.5)
+    b = torch.empty(1024, device="cuda", dtype=torch.bfloat16)
+    nv.cast_f32_bf16(t, b)
+    assert torch.all(b.float() == 1.5)
+    del t
+    buf.free()
