@@ -1,0 +1,377 @@
+"""B200 training/evaluation engine for ``DDoSClassifier``: a fixed sequence of hand-written sm_100a kernels over
+pre-allocated buffers, captured once into a CUDA graph and replayed per step.
+
+What it replaces in the reference: the body of ``train_model``'s inner loop (client1.py:102-112: H2D of the batch,
+``zero_grad``, forward through HF DistilBERT, ``CrossEntropyLoss``, ``backward``, ``Adam.step``, two ``loss.item()``
+syncs) and ``evaluate_model``'s per-batch work (client1.py:128-142).  There is no autograd here: forward and backward
+are explicit kernel sequences:
+
+    embed_ln_fwd -> 6 x [QKV GEMM(+bias) -> attn_fwd -> out GEMM(+bias) -> add_ln -> lin1 GEMM(+bias+GELU)
+                         -> lin2 GEMM(+bias) -> (dropout)+add_ln] -> cls_head(+CE, fwd+bwd)
+    backward mirrors it with dgrad (K-major x MN-major) and wgrad (MN-major x MN-major) GEMMs, fused dGELU epilogue,
+    LayerNorm backward producing the bias gradients, then ONE flat Adam launch that also refreshes the bf16 weights
+    and clears the atomically-accumulated gradients.
+
+Losses and evaluation metrics stay on the device (loss sum, batch count, 2x2 confusion matrix) and are read once
+per epoch / evaluation, not twice per step.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from ..ops import native as nv
+from .arena import ModelDims, ParamArena
+
+# dropout stream ids: one independent mask stream per dropout site
+_STREAM_EMBED = 1
+_STREAM_HEAD = 2
+
+
+def _layer_stream(layer: int, site: int) -> int:
+    return 16 + layer * 4 + site  # site 0 = attention probs, 1 = FFN output
+
+
+@dataclass
+class GemmPlan:
+    """BLOCK_N per GEMM of the step (M = tokens).  Values measured on B200 with tools/tune_gemm.py."""
+    qkv_fwd: int = 256
+    out_fwd: int = 96
+    lin1_fwd: int = 192
+    lin2_fwd: int = 96
+    lin2_dgrad: int = 192   # -> [T, 3072]
+    lin1_dgrad: int = 128   # -> [T, 768]
+    out_dgrad: int = 128
+    qkv_dgrad: int = 128
+    wgrad_wide: int = 128   # N = 768 outputs
+    wgrad_lin2: int = 256   # N = 3072 outputs
+
+
+class B200Engine:
+    def __init__(self, dims: ModelDims = ModelDims(), batch: int = 16, seq: int = 128, device: int | str = 0,
+                 lr: float = 2e-5, betas: Tuple[float, float] = (0.9, 0.999), eps: float = 1e-8, seed: int = 0,
+                 flat_params: Optional[torch.Tensor] = None, bf16_params: Optional[torch.Tensor] = None,
+                 plan: Optional[GemmPlan] = None, init_seed: Optional[int] = 0):
+        if not torch.cuda.is_available():
+            raise nv.NativeError("B200Engine needs a CUDA device; use models.distilbert.DDoSClassifier on CPU")
+        nv.lib()  # fail loudly if the native library is missing
+        if seq > 128:
+            raise ValueError("the fused attention kernel covers seq <= 128 (the reference truncates to 128)")
+        if dims.head_dim != 64 or dims.dim % 256 != 0:
+            raise ValueError("kernels are specialised for head_dim 64 and dim in {256,512,768,1024}")
+        self.dims, self.B, self.S = dims, batch, seq
+        self.device = torch.device("cuda", device) if not isinstance(device, torch.device) else device
+        torch.cuda.set_device(self.device)
+        self.lr, self.betas, self.eps = lr, betas, eps
+        self.plan = plan or GemmPlan()
+        dev = self.device
+        self.arena = ParamArena(dims, dev, flat=flat_params, with_optimizer_state=True, with_bf16=bf16_params is None)
+        if bf16_params is not None:
+            assert bf16_params.numel() == self.arena.layout.gemm_end and bf16_params.dtype == torch.bfloat16
+            self.arena.bf16 = bf16_params
+        if init_seed is not None:
+            self.arena.init_random_(init_seed)
+        self.rng = torch.tensor([seed, 0], dtype=torch.int64, device=dev)  # {seed, step}
+        T, D, Fh, H, L = batch * seq, dims.dim, dims.hidden_dim, dims.n_heads, dims.n_layers
+        self.T = T
+        bf = dict(device=dev, dtype=torch.bfloat16)
+        f32 = dict(device=dev, dtype=torch.float32)
+        # static inputs
+        self.ids = torch.zeros(T, device=dev, dtype=torch.int32)
+        self.lens = torch.full((batch,), seq, device=dev, dtype=torch.int32)
+        self.labels = torch.zeros(batch, device=dev, dtype=torch.int32)
+        # pinned staging for the end-to-end path: ids | lens | labels in one buffer -> one H2D copy per step
+        self.h_in = torch.zeros(T + 2 * batch, dtype=torch.int32).pin_memory()
+        self.d_in = torch.zeros(T + 2 * batch, device=dev, dtype=torch.int32)
+        self.h_loss = torch.zeros(2, dtype=torch.float32).pin_memory()
+        # saved activations
+        self.x = [torch.empty(T, D, **bf) for _ in range(L + 1)]
+        self.qkv = [torch.empty(T, 3 * D, **bf) for _ in range(L)]
+        self.ctx = [torch.empty(T, D, **bf) for _ in range(L)]
+        self.sa = [torch.empty(T, D, **bf) for _ in range(L)]
+        self.pre = [torch.empty(T, Fh, **bf) for _ in range(L)]
+        self.hmid = [torch.empty(T, Fh, **bf) for _ in range(L)]
+        self.rstd1 = [torch.empty(T, **f32) for _ in range(L)]
+        self.rstd2 = [torch.empty(T, **f32) for _ in range(L)]
+        self.lse2 = [torch.empty(batch * H * 128, **f32) for _ in range(L)]
+        self.emb_mean = torch.empty(T, **f32)
+        self.emb_rstd = torch.empty(T, **f32)
+        # transient forward / backward buffers
+        self.tmp_d = torch.empty(T, D, **bf)        # attn_out / ffn_out
+        self.g_a = torch.empty(T, D, **bf)          # gradient wrt a layer output, branch 1
+        self.g_b = torch.empty(T, D, **bf)          # gradient wrt a layer output, branch 2 (residual)
+        self.g_c = torch.empty(T, D, **bf)
+        self.g_d = torch.empty(T, D, **bf)
+        self.g_wide = torch.empty(T, Fh, **bf)      # dpre
+        self.g_qkv = torch.empty(T, 3 * D, **bf)
+        self.dcls = torch.empty(batch, D, **bf)
+        self.logits = torch.empty(batch, dims.n_classes, **f32)
+        # device-side accumulators
+        self.loss_accum = torch.zeros(2, **f32)                       # {sum of batch-mean losses, #batches}
+        self.eval_loss_accum = torch.zeros(2, **f32)
+        self.confusion = torch.zeros(4, device=dev, dtype=torch.int32)  # [true*2 + pred]
+        self.probs = torch.empty(batch, **f32)
+        self.preds = torch.empty(batch, device=dev, dtype=torch.int32)
+        self._graph_train: Optional[torch.cuda.CUDAGraph] = None
+        self._graph_eval: Optional[torch.cuda.CUDAGraph] = None
+        self._graph_train_e2e: Optional[torch.cuda.CUDAGraph] = None
+        self.launches_per_train_step = 0
+        self._count_launches = False
+        self._n_launch = 0
+        self._bind_params()
+
+    # ------------------------------------------------------------------------------------------------ parameters
+    def _bind_params(self) -> None:
+        a, L = self.arena, self.dims.n_layers
+        pre = "distilbert.transformer.layer.{}."
+        self.p: Dict[str, list] = {k: [] for k in (
+            "wqkv", "bqkv", "wo", "bo", "g1", "b1", "w1", "bb1", "w2", "bb2", "g2", "b2",
+            "d_wqkv", "d_bqkv", "d_wo", "d_bo", "d_g1", "d_b1", "d_w1", "d_bb1", "d_w2", "d_bb2", "d_g2", "d_b2")}
+        lay = a.layout
+        for l in range(L):
+            p = pre.format(l)
+            off = lay.qkv_weight_offset(l)
+            D = self.dims.dim
+            self.p["wqkv"].append(a.bf16[off: off + 3 * D * D].view(3 * D, D))
+            self.p["d_wqkv"].append(a.qkv_weight(l, a.grad))
+            self.p["bqkv"].append(a.qkv_bias(l))
+            self.p["d_bqkv"].append(a.qkv_bias(l, a.grad))
+            for short, key, is_w in (("wo", "attention.out_lin.weight", True), ("bo", "attention.out_lin.bias", False),
+                                     ("g1", "sa_layer_norm.weight", False), ("b1", "sa_layer_norm.bias", False),
+                                     ("w1", "ffn.lin1.weight", True), ("bb1", "ffn.lin1.bias", False),
+                                     ("w2", "ffn.lin2.weight", True), ("bb2", "ffn.lin2.bias", False),
+                                     ("g2", "output_layer_norm.weight", False), ("b2", "output_layer_norm.bias", False)):
+                self.p[short].append(a.bf16_view(p + key) if is_w else a.view(p + key))
+                self.p["d_" + short].append(a.view(p + key, a.grad))
+        e = "distilbert.embeddings."
+        self.word, self.pos = a.view(e + "word_embeddings.weight"), a.view(e + "position_embeddings.weight")
+        self.eg, self.eb = a.view(e + "LayerNorm.weight"), a.view(e + "LayerNorm.bias")
+        self.d_word, self.d_pos = a.view(e + "word_embeddings.weight", a.grad), a.view(e + "position_embeddings.weight", a.grad)
+        self.d_eg, self.d_eb = a.view(e + "LayerNorm.weight", a.grad), a.view(e + "LayerNorm.bias", a.grad)
+        self.cw, self.cb = a.view("classifier.weight"), a.view("classifier.bias")
+        self.d_cw, self.d_cb = a.view("classifier.weight", a.grad), a.view("classifier.bias", a.grad)
+
+    def state_dict(self, clone: bool = True):
+        return self.arena.state_dict(clone=clone)
+
+    def load_state_dict(self, sd) -> None:
+        self.arena.load_state_dict(sd)
+
+    def refresh_bf16(self) -> None:
+        nv.cast_f32_bf16(self.arena.flat[: self.arena.layout.gemm_end], self.arena.bf16)
+
+    def reset_optimizer(self) -> None:
+        self.arena.exp_avg.zero_()
+        self.arena.exp_avg_sq.zero_()
+        self.arena.grad.zero_()
+        self.rng[1] = 0
+
+    # ------------------------------------------------------------------------------------------------ helpers
+    def _gemm(self, *args, **kw):
+        self._n_launch += 1
+        return nv.gemm_bf16(*args, **kw)
+
+    def _k(self, fn, *args, **kw):
+        self._n_launch += 1
+        return fn(*args, **kw)
+
+    # ------------------------------------------------------------------------------------------------ forward
+    def _forward(self, rows_b: int, train: bool) -> torch.Tensor:
+        """Runs the encoder on the first ``rows_b`` samples of the static input buffers; returns the last hidden
+        states ``[rows_b * S, D]``."""
+        d, S, pl = self.dims, self.S, self.plan
+        T = rows_b * S
+        H = d.n_heads
+        p_h = d.dropout if train else 0.0
+        p_a = d.attention_dropout if train else 0.0
+        rng = self.rng if train else None
+        x0 = self.x[0][:T]
+        self._k(nv.embed_ln_fwd, self.ids[:T], self.word, self.pos, self.eg, self.eb, x0, self.emb_mean[:T],
+                self.emb_rstd[:T], S, eps=d.ln_eps, p_drop=p_h, rng=rng, stream_id=_STREAM_EMBED)
+        for l in range(d.n_layers):
+            x, qkv, ctx, sa = self.x[l][:T], self.qkv[l][:T], self.ctx[l][:T], self.sa[l][:T]
+            pre, hmid, tmp = self.pre[l][:T], self.hmid[l][:T], self.tmp_d[:T]
+            self._gemm(x, self.p["wqkv"][l], qkv, bias=self.p["bqkv"][l], epi=nv.EPI_BIAS, block_n=pl.qkv_fwd)
+            self._k(nv.attn_fwd, qkv, ctx, self.lse2[l], self.lens, rows_b, S, H, p_drop=p_a, rng=rng,
+                    stream_id=_layer_stream(l, 0))
+            self._gemm(ctx, self.p["wo"][l], tmp, bias=self.p["bo"][l], epi=nv.EPI_BIAS, block_n=pl.out_fwd)
+            self._k(nv.add_ln_fwd, tmp, x, self.p["g1"][l], self.p["b1"][l], sa, self.rstd1[l][:T], eps=d.ln_eps)
+            self._gemm(sa, self.p["w1"][l], hmid, bias=self.p["bb1"][l], aux_out=pre if train else None,
+                       epi=nv.EPI_BIAS_GELU, block_n=pl.lin1_fwd)
+            self._gemm(hmid, self.p["w2"][l], tmp, bias=self.p["bb2"][l], epi=nv.EPI_BIAS, block_n=pl.lin2_fwd)
+            self._k(nv.add_ln_fwd, tmp, sa, self.p["g2"][l], self.p["b2"][l], self.x[l + 1][:T], self.rstd2[l][:T],
+                    eps=d.ln_eps, p_drop=p_h, rng=rng, stream_id=_layer_stream(l, 1))
+        return self.x[d.n_layers][:T]
+
+    # ------------------------------------------------------------------------------------------------ backward
+    def _backward(self) -> None:
+        d, S, B, pl = self.dims, self.S, self.B, self.plan
+        H, D = d.n_heads, d.dim
+        MN = nv.MAJOR_MN
+        # gradient wrt the last hidden states: only the CLS rows are non-zero
+        self._k(nv.scatter_rows_bf16, self.dcls, self.g_a, B, D, S)
+        dy1, dy2 = self.g_a, None
+        for l in reversed(range(d.n_layers)):
+            x, qkv, ctx, sa, pre, hmid = self.x[l], self.qkv[l], self.ctx[l], self.sa[l], self.pre[l], self.hmid[l]
+            P = self.p
+            # output_layer_norm(dropout(ffn_out) + sa)
+            dz2 = self.g_c
+            da2 = self.g_d if d.dropout > 0 else dz2  # without dropout the two gradients coincide
+            self._k(nv.add_ln_bwd, dy1, dy2, self.x[l + 1], P["g2"][l], P["b2"][l], self.rstd2[l], dz2,
+                    da2 if d.dropout > 0 else None, P["d_g2"][l], P["d_b2"][l], P["d_bb2"][l], p_drop=d.dropout,
+                    rng=self.rng, stream_id=_layer_stream(l, 1))
+            # lin2: dW2 = da2^T hmid ; dpre = (da2 W2) * gelu'(pre)
+            self._gemm(da2, hmid, P["d_w2"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_lin2)
+            self._gemm(da2, P["w2"][l], self.g_wide, b_major=MN, aux=pre, epi=nv.EPI_DGELU, block_n=pl.lin2_dgrad)
+            # lin1: dW1 = dpre^T sa ; db1 = colsum(dpre) ; dsa = dpre W1
+            self._gemm(self.g_wide, sa, P["d_w1"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_wide)
+            self._k(nv.colsum_bf16, self.g_wide, P["d_bb1"][l])
+            dsa = self.g_b  # dy1/dy2 of this layer (g_a/g_b) are dead after the LN backward above
+            self._gemm(self.g_wide, P["w1"][l], dsa, b_major=MN, block_n=pl.lin1_dgrad)
+            # sa_layer_norm(attn_out + x): dz1 is the gradient wrt both attn_out and the residual x
+            dz1 = self.g_a
+            self._k(nv.add_ln_bwd, dsa, dz2, sa, P["g1"][l], P["b1"][l], self.rstd1[l], dz1, None, P["d_g1"][l],
+                    P["d_b1"][l], P["d_bo"][l])
+            # out_lin: dWo = dz1^T ctx ; dctx = dz1 Wo
+            self._gemm(dz1, ctx, P["d_wo"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_wide)
+            dctx = self.g_c
+            self._gemm(dz1, P["wo"][l], dctx, b_major=MN, block_n=pl.out_dgrad)
+            # attention
+            self._k(nv.attn_bwd, qkv, ctx, dctx, self.lse2[l], self.g_qkv, self.lens, B, S, H,
+                    p_drop=d.attention_dropout, rng=self.rng, stream_id=_layer_stream(l, 0))
+            # QKV: dWqkv = dqkv^T x ; dbqkv = colsum(dqkv) ; dx = dqkv Wqkv
+            self._gemm(self.g_qkv, x, P["d_wqkv"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_wide)
+            self._k(nv.colsum_bf16, self.g_qkv, P["d_bqkv"][l])
+            dxq = self.g_b
+            self._gemm(self.g_qkv, P["wqkv"][l], dxq, b_major=MN, block_n=pl.qkv_dgrad)
+            dy1, dy2 = dxq, dz1  # gradient wrt x_l = via QKV projection + via the residual
+        self._k(nv.embed_ln_bwd, dy1, dy2, self.ids, self.word, self.pos, self.eg, self.emb_mean, self.emb_rstd,
+                self.d_word, self.d_pos, self.d_eg, self.d_eb, S, p_drop=d.dropout, rng=self.rng,
+                stream_id=_STREAM_EMBED)
+
+    def _optimizer(self) -> None:
+        a = self.arena
+        lay = a.layout
+        self._k(nv.adam_step, a.flat, a.grad, a.exp_avg, a.exp_avg_sq, a.bf16, lay.total, 0, lay.gemm_end,
+                lay.gemm_end, lay.total, self.lr, self.betas[0], self.betas[1], self.eps, self.rng)
+        self._k(nv.step_advance, self.rng)
+
+    # ------------------------------------------------------------------------------------------------ public API
+    def _train_step_kernels(self) -> None:
+        self._n_launch = 0
+        h = self._forward(self.B, train=True)
+        self._k(nv.cls_head_train, h, self.S * self.dims.dim, self.cw, self.cb, self.labels, self.B, self.loss_accum,
+                self.logits, self.d_cw, self.d_cb, self.dcls, cols=self.dims.dim, p_drop=self.dims.head_dropout,
+                rng=self.rng, stream_id=_STREAM_HEAD)
+        self._backward()
+        self._optimizer()
+        self.launches_per_train_step = self._n_launch
+
+    def _unpack_inputs(self) -> None:
+        T, B = self.T, self.B
+        self.ids.copy_(self.d_in[:T])
+        self.lens.copy_(self.d_in[T: T + B])
+        self.labels.copy_(self.d_in[T + B:])
+
+    def set_batch(self, input_ids: torch.Tensor, lens: torch.Tensor, labels: torch.Tensor) -> None:
+        """Device-side batch set-up (inputs already on the GPU, e.g. from the device-resident dataset)."""
+        self.ids.copy_(input_ids.reshape(-1))
+        self.lens.copy_(lens)
+        self.labels.copy_(labels)
+
+    def capture(self) -> None:
+        """Warm up eagerly, then capture the training step (and its end-to-end variant) into CUDA graphs."""
+        s = torch.cuda.Stream(device=self.device)
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            saved = (self.arena.flat.clone(), self.rng.clone())
+            for _ in range(2):
+                self._train_step_kernels()
+            s.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=s):
+                self._train_step_kernels()
+            self._graph_train = g
+            g2 = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g2, stream=s):
+                self.d_in.copy_(self.h_in, non_blocking=True)
+                self._unpack_inputs()
+                self._train_step_kernels()
+                self.h_loss.copy_(self.loss_accum, non_blocking=True)
+            self._graph_train_e2e = g2
+            # undo the warm-up steps
+            self.arena.flat.copy_(saved[0])
+            self.rng.copy_(saved[1])
+            self.reset_optimizer()
+            self.refresh_bf16()
+            self.loss_accum.zero_()
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize(self.device)
+
+    def train_step(self) -> None:
+        """One optimisation step on the batch currently in the static input buffers (no host sync)."""
+        if self._graph_train is not None:
+            self._graph_train.replay()
+        else:
+            self._train_step_kernels()
+
+    def train_step_from_host(self, ids: torch.Tensor, lens: torch.Tensor, labels: torch.Tensor) -> float:
+        """End-to-end step as a user calls it: host tensors in, running mean loss out.  Copies the batch through
+        pinned memory (one H2D), runs the step, reads back the loss accumulators (one D2H, one sync)."""
+        T, B = self.T, self.B
+        self.h_in[:T].copy_(ids.reshape(-1))
+        self.h_in[T: T + B].copy_(lens)
+        self.h_in[T + B:].copy_(labels)
+        if self._graph_train_e2e is not None:
+            self._graph_train_e2e.replay()
+        else:
+            self.d_in.copy_(self.h_in, non_blocking=True)
+            self._unpack_inputs()
+            self._train_step_kernels()
+            self.h_loss.copy_(self.loss_accum, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(self.h_loss[0] / max(float(self.h_loss[1]), 1.0))
+
+    @property
+    def h2d_bytes_per_step(self) -> int:
+        return self.h_in.numel() * 4
+
+    @property
+    def d2h_bytes_per_step(self) -> int:
+        return self.h_loss.numel() * 4
+
+    def read_loss(self, reset: bool = True) -> Tuple[float, int]:
+        """(mean of batch-mean losses since the last reset, number of batches) — one D2H sync."""
+        v = self.loss_accum.tolist()
+        if reset:
+            self.loss_accum.zero_()
+        n = int(v[1])
+        return (v[0] / n if n else 0.0), n
+
+    # ---- evaluation ----
+    def eval_reset(self) -> None:
+        self.eval_loss_accum.zero_()
+        self.confusion.zero_()
+
+    def eval_batch(self, rows_b: Optional[int] = None, want_probs: bool = False) -> None:
+        """Forward (dropout off) + classifier metrics on the first ``rows_b`` samples of the static inputs."""
+        rows_b = self.B if rows_b is None else rows_b
+        h = self._forward(rows_b, train=False)
+        self._k(nv.cls_head_eval, h, self.S * self.dims.dim, self.cw, self.cb, self.labels, rows_b,
+                self.eval_loss_accum, self.confusion, self.probs if want_probs else None,
+                self.preds if want_probs else None, cols=self.dims.dim)
+
+    def eval_read(self) -> Tuple[float, int, torch.Tensor]:
+        """(sum of batch-mean losses, number of batches, 2x2 confusion matrix [true, pred]) — one sync."""
+        la = self.eval_loss_accum.tolist()
+        cm = self.confusion.cpu().view(2, 2).to(torch.int64)
+        return la[0], int(la[1]), cm
+
+    def logits_eval(self, rows_b: Optional[int] = None) -> torch.Tensor:
+        """Logits in eval mode for the current static batch (used by parity tests)."""
+        rows_b = self.B if rows_b is None else rows_b
+        h = self._forward(rows_b, train=False)
+        cls = h.view(rows_b, self.S, self.dims.dim)[:, 0, :].float()
+        return cls @ self.cw.t() + self.cb

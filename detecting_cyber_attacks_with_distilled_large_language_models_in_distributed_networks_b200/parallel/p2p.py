@@ -1,0 +1,157 @@
+"""Peer-memory runtime for the NVSwitch FedAvg path (one process per GPU, or one process driving several GPUs).
+
+The reference moves each client's 265 MB state_dict through pickle + gzip + TCP twice per round (client1.py:276-336,
+server.py:57-114; ≈31–43 s per round).  On an NVSwitch box every client's parameter arena instead lives
+in peer-mappable device memory, and aggregation is one kernel per GPU that loads the peers' arenas and stores the
+average (and the bf16 compute copy) into every client's buffers (``csrc/fedavg.cu``).  NCCL is not involved:
+``torch.distributed`` is used only to exchange the 64-byte CUDA IPC handles at set-up.
+
+``PeerGroup``       multi-process: cudaMalloc'd arena / bf16 mirror / signal pad per rank, IPC handles all-gathered.
+``LocalPeerGroup``  single process, N devices: direct peer access (used by tests and the single-process launcher).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import torch
+
+from ..ops import native as nv
+
+PAD_BYTES = 64 * 4
+TWO_SHOT, ONE_SHOT = 0, 1
+
+
+class PeerGroup:
+    def __init__(self, rank: int, world: int, arena_elems: int, mirror_elems: int, dist_group=None,
+                 with_out_buffer: bool = False, arena_dtype: torch.dtype = torch.float32):
+        import torch.distributed as dist
+
+        self.rank, self.world = rank, world
+        self.arena_elems, self.mirror_elems = arena_elems, mirror_elems
+        self.arena_dtype = arena_dtype
+        esz = 4 if arena_dtype == torch.float32 else 2
+        self.arena_buf = nv.RawDeviceBuffer(nv.p2p_alloc(arena_elems * esz), arena_elems * esz)
+        self.mirror_buf = nv.RawDeviceBuffer(nv.p2p_alloc(max(mirror_elems, 8) * 2), max(mirror_elems, 8) * 2)
+        self.pad_buf = nv.RawDeviceBuffer(nv.p2p_alloc(PAD_BYTES), PAD_BYTES)
+        self.out_buf = (nv.RawDeviceBuffer(nv.p2p_alloc(arena_elems * esz), arena_elems * esz)
+                        if with_out_buffer else None)
+        mine = {"arena": nv.p2p_ipc_get(self.arena_buf.ptr), "mirror": nv.p2p_ipc_get(self.mirror_buf.ptr),
+                "pad": nv.p2p_ipc_get(self.pad_buf.ptr),
+                "out": nv.p2p_ipc_get(self.out_buf.ptr) if self.out_buf else None}
+        gathered: List[Optional[dict]] = [None] * world
+        dist.all_gather_object(gathered, mine, group=dist_group)
+        self._opened: List[nv.RawDeviceBuffer] = []
+        self.arena_ptrs, self.mirror_ptrs, self.pad_ptrs, self.out_ptrs = [], [], [], []
+        for r, h in enumerate(gathered):
+            if r == rank:
+                self.arena_ptrs.append(self.arena_buf.ptr)
+                self.mirror_ptrs.append(self.mirror_buf.ptr)
+                self.pad_ptrs.append(self.pad_buf.ptr)
+                self.out_ptrs.append(self.out_buf.ptr if self.out_buf else 0)
+            else:
+                for name, lst in (("arena", self.arena_ptrs), ("mirror", self.mirror_ptrs), ("pad", self.pad_ptrs),
+                                  ("out", self.out_ptrs)):
+                    if h[name] is None:
+                        lst.append(0)
+                        continue
+                    p = nv.p2p_ipc_open(h[name])
+                    self._opened.append(nv.RawDeviceBuffer(p, 0, owner=False, ipc=True))
+                    lst.append(p)
+        self.epoch = 0
+        dist.barrier(group=dist_group)
+
+    # views for the engine
+    def arena_tensor(self) -> torch.Tensor:
+        return self.arena_buf.view(self.arena_dtype, numel=self.arena_elems)
+
+    def mirror_tensor(self) -> torch.Tensor:
+        return self.mirror_buf.view(torch.bfloat16, numel=self.mirror_elems)
+
+    def out_tensor(self) -> Optional[torch.Tensor]:
+        return self.out_buf.view(self.arena_dtype, numel=self.arena_elems) if self.out_buf else None
+
+    def pad_tensor(self) -> torch.Tensor:
+        return self.pad_buf.view(torch.int32, numel=64)
+
+    def fedavg(self, mode: int = TWO_SHOT, weights: Optional[Sequence[float]] = None,
+               participants: Optional[Sequence[int]] = None, with_mirror: bool = True, max_ctas: int = 0,
+               stream=None) -> None:
+        """Launch this rank's share of the aggregation (all participating ranks must call it).  In place for two-shot;
+        one-shot writes the ``out`` buffer.  ``participants`` restricts the average to a subset (quorum)."""
+        ranks = list(range(self.world)) if participants is None else list(participants)
+        if self.rank not in ranks:
+            return
+        self.epoch += 1
+        sel = lambda lst: [lst[r] for r in ranks]  # noqa: E731
+        nv.fedavg_p2p(sel(self.arena_ptrs), sel(self.pad_ptrs), ranks.index(self.rank), self.arena_elems, self.epoch,
+                      out_ptrs=sel(self.out_ptrs) if mode == ONE_SHOT else None,
+                      mirror_ptrs=sel(self.mirror_ptrs) if (with_mirror and self.mirror_elems) else None,
+                      weights=weights, in_bf16=self.arena_dtype == torch.bfloat16, mode=mode, bf16_begin=0,
+                      bf16_end=self.mirror_elems if with_mirror else 0, max_ctas=max_ctas, stream=stream)
+
+    def error_flag(self) -> int:
+        return int(self.pad_tensor()[33].item())
+
+    def close(self) -> None:
+        for b in self._opened:
+            b.free()
+        self._opened = []
+        for b in (self.arena_buf, self.mirror_buf, self.pad_buf, self.out_buf):
+            if b is not None:
+                b.free()
+
+
+class LocalPeerGroup:
+    """All ranks in one process (one CUDA device each) with direct peer access."""
+
+    def __init__(self, devices: Sequence[int], arena_elems: int, mirror_elems: int, with_out_buffer: bool = False,
+                 arena_dtype: torch.dtype = torch.float32):
+        self.devices = list(devices)
+        self.world = len(self.devices)
+        self.arena_elems, self.mirror_elems, self.arena_dtype = arena_elems, mirror_elems, arena_dtype
+        esz = 4 if arena_dtype == torch.float32 else 2
+        self.arena_bufs, self.mirror_bufs, self.pad_bufs, self.out_bufs = [], [], [], []
+        for d in self.devices:
+            with torch.cuda.device(d):
+                for peer in self.devices:
+                    if peer != d:
+                        if not nv.p2p_can_access(d, peer):
+                            raise nv.NativeError(f"device {d} cannot access peer {peer}")
+                        nv.p2p_enable_peer_access(peer)
+                self.arena_bufs.append(nv.RawDeviceBuffer(nv.p2p_alloc(arena_elems * esz), arena_elems * esz))
+                self.mirror_bufs.append(nv.RawDeviceBuffer(nv.p2p_alloc(max(mirror_elems, 8) * 2), max(mirror_elems, 8) * 2))
+                self.pad_bufs.append(nv.RawDeviceBuffer(nv.p2p_alloc(PAD_BYTES), PAD_BYTES))
+                if with_out_buffer:
+                    self.out_bufs.append(nv.RawDeviceBuffer(nv.p2p_alloc(arena_elems * esz), arena_elems * esz))
+        self.epoch = 0
+
+    def arena_tensor(self, r: int) -> torch.Tensor:
+        with torch.cuda.device(self.devices[r]):
+            return self.arena_bufs[r].view(self.arena_dtype, numel=self.arena_elems)
+
+    def mirror_tensor(self, r: int) -> torch.Tensor:
+        with torch.cuda.device(self.devices[r]):
+            return self.mirror_bufs[r].view(torch.bfloat16, numel=self.mirror_elems)
+
+    def out_tensor(self, r: int) -> torch.Tensor:
+        with torch.cuda.device(self.devices[r]):
+            return self.out_bufs[r].view(self.arena_dtype, numel=self.arena_elems)
+
+    def fedavg_all(self, mode: int = TWO_SHOT, weights: Optional[Sequence[float]] = None, with_mirror: bool = True,
+                   max_ctas: int = 0) -> None:
+        """Launch every rank's kernel (each on its own device's current stream); the kernels synchronise among
+        themselves through the signal pads."""
+        self.epoch += 1
+        for r, d in enumerate(self.devices):
+            with torch.cuda.device(d):
+                nv.fedavg_p2p([b.ptr for b in self.arena_bufs], [b.ptr for b in self.pad_bufs], r, self.arena_elems,
+                              self.epoch, out_ptrs=[b.ptr for b in self.out_bufs] if mode == ONE_SHOT else None,
+                              mirror_ptrs=[b.ptr for b in self.mirror_bufs] if (with_mirror and self.mirror_elems) else None,
+                              weights=weights, in_bf16=self.arena_dtype == torch.bfloat16, mode=mode, bf16_begin=0,
+                              bf16_end=self.mirror_elems if with_mirror else 0, max_ctas=max_ctas)
+
+    def close(self) -> None:
+        for lst in (self.arena_bufs, self.mirror_bufs, self.pad_bufs, self.out_bufs):
+            for r, b in enumerate(lst):
+                with torch.cuda.device(self.devices[r]):
+                    b.free()
