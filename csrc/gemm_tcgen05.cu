@@ -55,8 +55,24 @@ struct GemmCfg {
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024;
 };
 
+constexpr int GEMM_THREADS = 384;        // 12 warps: 0 = TMA, 1 = MMA, 2 = TMEM owner, 3 = idle, 4..11 = epilogue
+constexpr int EPI_THREADS = 256;
+
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+template <int N>
+struct TmemChunk;
+template <>
+struct TmemChunk<32> {
+    static __device__ __forceinline__ void ld(uint32_t taddr, uint32_t (&r)[32]) { tmem_ld_32x32b_x32(taddr, r); }
+};
+template <>
+struct TmemChunk<16> {
+    static __device__ __forceinline__ void ld(uint32_t taddr, uint32_t (&r)[16]) { tmem_ld_32x32b_x16(taddr, r); }
+};
+
 template <int BN, int A_MAJOR, int B_MAJOR>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const GemmParams p) {
     using Cfg = GemmCfg<BN>;
@@ -69,6 +85,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     __shared__ __align__(8) uint64_t empty_bar[STAGES];
     __shared__ __align__(8) uint64_t tmem_full_bar[2];
     __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+    __shared__ __align__(16) float s_bias[2][BN];
     __shared__ uint32_t tmem_base_smem;
 
     const uint32_t warp = threadIdx.x >> 5;
@@ -88,7 +105,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
             mbar_init(smem_u32(&tmem_full_bar[s]), 1);
-            mbar_init(smem_u32(&tmem_empty_bar[s]), 128);
+            mbar_init(smem_u32(&tmem_empty_bar[s]), EPI_THREADS);
         }
         fence_barrier_init();
     }
@@ -169,58 +186,87 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             }
             if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1u; }
         }
-    } else {
-        // ===================== epilogue (warps 2..5; TMEM lane quarter = warp % 4) =====================
+    } else if (warp >= 4) {
+        // ===================== epilogue: 8 warps.  TMEM lane quarter = warp % 4, column half = (warp - 4) / 4 =====
+        constexpr int HALF_N = BN / 2;
+        constexpr int CH = (HALF_N % 32 == 0) ? 32 : 16;
+        constexpr int NCH = HALF_N / CH;
         const uint32_t q = warp & 3u;
+        const int half = static_cast<int>(warp - 4) >> 2;
+        const int ep_tid = static_cast<int>(threadIdx.x) - 128;
+        const bool has_bias = (p.epi == DCAD_EPI_BIAS || p.epi == DCAD_EPI_BIAS_GELU);
         uint32_t acc_stage = 0, acc_phase = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
             const int m_blk = tile % p.num_m_blocks;
             const int n_blk = tile / p.num_m_blocks;
-            mbar_wait(smem_u32(&tmem_full_bar[acc_stage]), acc_phase);
-            tc_fence_after();
+            const int n_base = n_blk * BN;
             const int row = m_blk * BM + q * 32 + lane;
             const bool row_ok = row < p.M;
-            const uint32_t t_row = tmem_base + acc_stage * Cfg::ACC_STRIDE + ((q * 32u) << 16);
+            const int col_base = n_base + half * HALF_N;
+            // stage this tile's bias while the MMAs are still running
+            if (has_bias) {
+                if (ep_tid < BN) s_bias[acc_stage][ep_tid] = (n_base + ep_tid < p.N) ? __ldg(p.bias + n_base + ep_tid) : 0.f;
+                epi_bar_sync();
+            }
+            // prefetch the first aux chunk (dGELU pre-activations)
+            uint4 aux_cur[CH / 8];
+            const __nv_bfloat16* aux_row =
+                (p.epi == DCAD_EPI_DGELU && row_ok) ? p.aux + static_cast<size_t>(row) * p.ldaux + col_base : nullptr;
+            if (aux_row) {
+#pragma unroll
+                for (int j = 0; j < CH / 8; ++j)
+                    aux_cur[j] = (col_base + j * 8 < p.N) ? __ldg(reinterpret_cast<const uint4*>(aux_row) + j)
+                                                          : make_uint4(0, 0, 0, 0);
+            }
+            mbar_wait(smem_u32(&tmem_full_bar[acc_stage]), acc_phase);
+            tc_fence_after();
+            const uint32_t t_row = tmem_base + acc_stage * Cfg::ACC_STRIDE + ((q * 32u) << 16) + half * HALF_N;
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
-                uint32_t r[32];
-                tmem_ld_32x32b_x32(t_row + c * 32, r);
+            for (int c = 0; c < NCH; ++c) {
+                uint32_t r[CH];
+                TmemChunk<CH>::ld(t_row + c * CH, r);
+                // prefetch the next aux chunk while the TMEM load is in flight
+                uint4 aux_nxt[CH / 8];
+                if (aux_row && c + 1 < NCH) {
+#pragma unroll
+                    for (int j = 0; j < CH / 8; ++j)
+                        aux_nxt[j] = (col_base + (c + 1) * CH + j * 8 < p.N)
+                                         ? __ldg(reinterpret_cast<const uint4*>(aux_row + (c + 1) * CH) + j)
+                                         : make_uint4(0, 0, 0, 0);
+                }
                 tmem_ld_wait();
-                const int n0 = n_blk * BN + c * 32;
-                if (!row_ok || n0 >= p.N) continue;
-                float v[32];
+                const int n0 = col_base + c * CH;
+                if (row_ok && n0 < p.N) {
+                    float v[CH];
 #pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                if (p.epi == DCAD_EPI_BIAS || p.epi == DCAD_EPI_BIAS_GELU) {
+                    for (int j = 0; j < CH; ++j) v[j] = __uint_as_float(r[j]);
+                    if (has_bias) {
+                        const float4* bs = reinterpret_cast<const float4*>(&s_bias[acc_stage][half * HALF_N + c * CH]);
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4) {
-                        if (n0 + j < p.N) {
-                            const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + j));
+                        for (int j = 0; j < CH; j += 4) {
+                            const float4 b = bs[j >> 2];
                             v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
                         }
                     }
-                }
-                if (p.epi == DCAD_EPI_BIAS_GELU) {
-                    if (p.aux_out != nullptr) {
-                        __nv_bfloat16* ao = p.aux_out + static_cast<size_t>(row) * p.ldaux + n0;
+                    if (p.epi == DCAD_EPI_BIAS_GELU) {
+                        if (p.aux_out != nullptr) {
+                            __nv_bfloat16* ao = p.aux_out + static_cast<size_t>(row) * p.ldaux + n0;
 #pragma unroll
-                        for (int j = 0; j < 32; j += 8) {
-                            if (n0 + j < p.N) {
-                                uint4 o;
-                                o.x = pack_bf16x2(v[j], v[j + 1]); o.y = pack_bf16x2(v[j + 2], v[j + 3]);
-                                o.z = pack_bf16x2(v[j + 4], v[j + 5]); o.w = pack_bf16x2(v[j + 6], v[j + 7]);
-                                *reinterpret_cast<uint4*>(ao + j) = o;
+                            for (int j = 0; j < CH; j += 8) {
+                                if (n0 + j < p.N) {
+                                    uint4 o;
+                                    o.x = pack_bf16x2(v[j], v[j + 1]); o.y = pack_bf16x2(v[j + 2], v[j + 3]);
+                                    o.z = pack_bf16x2(v[j + 4], v[j + 5]); o.w = pack_bf16x2(v[j + 6], v[j + 7]);
+                                    *reinterpret_cast<uint4*>(ao + j) = o;
+                                }
                             }
                         }
-                    }
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
-                } else if (p.epi == DCAD_EPI_DGELU) {
-                    const __nv_bfloat16* ai = p.aux + static_cast<size_t>(row) * p.ldaux + n0;
+                        for (int j = 0; j < CH; ++j) v[j] = gelu_erf(v[j]);
+                    } else if (p.epi == DCAD_EPI_DGELU) {
 #pragma unroll
-                    for (int j = 0; j < 32; j += 8) {
-                        if (n0 + j < p.N) {
-                            const uint4 a = __ldg(reinterpret_cast<const uint4*>(ai + j));
+                        for (int j = 0; j < CH; j += 8) {
+                            const uint4 a = aux_cur[j >> 3];
                             const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y);
                             const float2 a2 = unpack_bf16x2(a.z), a3 = unpack_bf16x2(a.w);
                             v[j] *= dgelu_erf(a0.x); v[j + 1] *= dgelu_erf(a0.y);
@@ -229,31 +275,36 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                             v[j + 6] *= dgelu_erf(a3.x); v[j + 7] *= dgelu_erf(a3.y);
                         }
                     }
-                }
-                if (p.out_fp32) {
-                    float* d = reinterpret_cast<float*>(p.D) + static_cast<size_t>(row) * p.ldd + n0;
+                    if (p.out_fp32) {
+                        float* d = reinterpret_cast<float*>(p.D) + static_cast<size_t>(row) * p.ldd + n0;
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4) {
-                        if (n0 + j < p.N) {
-                            float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-                            if (p.accumulate) {
-                                const float4 old = *reinterpret_cast<const float4*>(d + j);
-                                o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+                        for (int j = 0; j < CH; j += 4) {
+                            if (n0 + j < p.N) {
+                                float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                                if (p.accumulate) {
+                                    const float4 old = *reinterpret_cast<const float4*>(d + j);
+                                    o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+                                }
+                                *reinterpret_cast<float4*>(d + j) = o;
                             }
-                            *reinterpret_cast<float4*>(d + j) = o;
                         }
-                    }
-                } else {
-                    __nv_bfloat16* d = reinterpret_cast<__nv_bfloat16*>(p.D) + static_cast<size_t>(row) * p.ldd + n0;
+                    } else {
+                        __nv_bfloat16* d =
+                            reinterpret_cast<__nv_bfloat16*>(p.D) + static_cast<size_t>(row) * p.ldd + n0;
 #pragma unroll
-                    for (int j = 0; j < 32; j += 8) {
-                        if (n0 + j < p.N) {
-                            uint4 o;
-                            o.x = pack_bf16x2(v[j], v[j + 1]); o.y = pack_bf16x2(v[j + 2], v[j + 3]);
-                            o.z = pack_bf16x2(v[j + 4], v[j + 5]); o.w = pack_bf16x2(v[j + 6], v[j + 7]);
-                            *reinterpret_cast<uint4*>(d + j) = o;
+                        for (int j = 0; j < CH; j += 8) {
+                            if (n0 + j < p.N) {
+                                uint4 o;
+                                o.x = pack_bf16x2(v[j], v[j + 1]); o.y = pack_bf16x2(v[j + 2], v[j + 3]);
+                                o.z = pack_bf16x2(v[j + 4], v[j + 5]); o.w = pack_bf16x2(v[j + 6], v[j + 7]);
+                                *reinterpret_cast<uint4*>(d + j) = o;
+                            }
                         }
                     }
+                }
+                if (aux_row) {
+#pragma unroll
+                    for (int j = 0; j < CH / 8; ++j) aux_cur[j] = aux_nxt[j];
                 }
             }
             tc_fence_before();
@@ -377,7 +428,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
     int grid = p.num_m_blocks * p.num_n_blocks;
     int cap = max_ctas > 0 ? max_ctas : num_sms();
     if (grid > cap) grid = cap;
-    kern<<<grid, 192, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, p);
+    kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, p);
     return (int)cudaGetLastError();
 }
 

@@ -13,7 +13,6 @@
 namespace dcad {
 
 constexpr int LN_WARPS = 8;
-constexpr int LN_ROWS_PER_CTA_BWD = 16;
 
 __device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&v)[8]) {
     const uint4 u = *reinterpret_cast<const uint4*>(p);
@@ -105,32 +104,26 @@ add_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy1, const __nv_bfloat16* __
                   float* __restrict__ dbias, int rows, uint32_t thresh, float keep_scale,
                   const uint64_t* __restrict__ rng, uint32_t stream_id) {
     constexpr int COLS = NV * 256;
-    __shared__ float s_acc[3 * COLS];
+    // one slot per warp: [warp][3][COLS] partial column sums (dgamma, dbeta, dbias); one row per warp
+    extern __shared__ float s_part[];
     const uint32_t warp = threadIdx.x >> 5, lane = lane_id();
     const uint64_t seed = rng_seed(rng);
-    float acc_g[NV][8], acc_b[NV][8], acc_bias[NV][8];
-#pragma unroll
-    for (int v = 0; v < NV; ++v)
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { acc_g[v][j] = 0.f; acc_b[v][j] = 0.f; acc_bias[v][j] = 0.f; }
-
-    const int row0 = blockIdx.x * LN_ROWS_PER_CTA_BWD;
-    for (int rr = warp; rr < LN_ROWS_PER_CTA_BWD; rr += LN_WARPS) {
-        const int row = row0 + rr;
-        if (row >= rows) break;
-        float g[NV][8], xh[NV][8];
+    const int row = blockIdx.x * LN_WARPS + warp;
+    float* slot = s_part + warp * 3 * COLS;
+    if (row < rows) {
+        float g[NV][8], xh[NV][8], d[NV][8];
         float c1 = 0.f, c2 = 0.f;
 #pragma unroll
         for (int v = 0; v < NV; ++v) {
             const int col = (v * 32 + lane) * 8;
             const size_t off = static_cast<size_t>(row) * COLS + col;
-            float d[8], yy[8], gm[8], bt[8];
-            load8(dy1 + off, d);
+            float yy[8], gm[8], bt[8];
+            load8(dy1 + off, d[v]);
             if (dy2) {
                 float d2[8];
                 load8(dy2 + off, d2);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) d[j] += d2[j];
+                for (int j = 0; j < 8; ++j) d[v][j] += d2[j];
             }
             load8(y + off, yy);
             load8f(gamma + col, gm);
@@ -138,11 +131,9 @@ add_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy1, const __nv_bfloat16* __
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 xh[v][j] = (yy[j] - bt[j]) / safe_gamma(gm[j]);
-                g[v][j] = d[j] * gm[j];
+                g[v][j] = d[v][j] * gm[j];
                 c1 += g[v][j];
                 c2 += g[v][j] * xh[v][j];
-                acc_g[v][j] += d[j] * xh[v][j];
-                acc_b[v][j] += d[j];
             }
         }
         c1 = warp_sum(c1) * (1.0f / COLS);
@@ -152,9 +143,9 @@ add_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy1, const __nv_bfloat16* __
         for (int v = 0; v < NV; ++v) {
             const int col = (v * 32 + lane) * 8;
             const size_t off = static_cast<size_t>(row) * COLS + col;
-            float o[8];
+            float o[8], pg[8];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) o[j] = rs * (g[v][j] - c1 - xh[v][j] * c2);
+            for (int j = 0; j < 8; ++j) { o[j] = rs * (g[v][j] - c1 - xh[v][j] * c2); pg[j] = d[v][j] * xh[v][j]; }
             store8(dz + off, o);
             if (da) {
 #pragma unroll
@@ -162,38 +153,23 @@ add_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy1, const __nv_bfloat16* __
                     o[j] = dropout_keep(seed, stream_id, row * COLS + col + j, thresh) ? o[j] * keep_scale : 0.f;
                 store8(da + off, o);
             }
-            if (dbias) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j) acc_bias[v][j] += o[j];
-            }
+            *reinterpret_cast<float4*>(slot + col) = make_float4(pg[0], pg[1], pg[2], pg[3]);
+            *reinterpret_cast<float4*>(slot + col + 4) = make_float4(pg[4], pg[5], pg[6], pg[7]);
+            *reinterpret_cast<float4*>(slot + COLS + col) = make_float4(d[v][0], d[v][1], d[v][2], d[v][3]);
+            *reinterpret_cast<float4*>(slot + COLS + col + 4) = make_float4(d[v][4], d[v][5], d[v][6], d[v][7]);
+            *reinterpret_cast<float4*>(slot + 2 * COLS + col) = make_float4(o[0], o[1], o[2], o[3]);
+            *reinterpret_cast<float4*>(slot + 2 * COLS + col + 4) = make_float4(o[4], o[5], o[6], o[7]);
         }
+    } else {
+        for (int c = lane; c < 3 * COLS; c += 32) slot[c] = 0.f;
     }
-    // cross-warp column reduction in shared memory, then one atomic per column per CTA
-    for (int w = 0; w < LN_WARPS; ++w) {
-        if (warp == w) {
+    __syncthreads();
+    for (int c = threadIdx.x; c < 3 * COLS; c += blockDim.x) {
+        float t = 0.f;
 #pragma unroll
-            for (int v = 0; v < NV; ++v) {
-                const int col = (v * 32 + lane) * 8;
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    if (w == 0) {
-                        s_acc[col + j] = acc_g[v][j];
-                        s_acc[COLS + col + j] = acc_b[v][j];
-                        s_acc[2 * COLS + col + j] = acc_bias[v][j];
-                    } else {
-                        s_acc[col + j] += acc_g[v][j];
-                        s_acc[COLS + col + j] += acc_b[v][j];
-                        s_acc[2 * COLS + col + j] += acc_bias[v][j];
-                    }
-                }
-            }
-        }
-        __syncthreads();
-    }
-    for (int c = threadIdx.x; c < COLS; c += blockDim.x) {
-        if (dgamma) atomicAdd(dgamma + c, s_acc[c]);
-        if (dbeta) atomicAdd(dbeta + c, s_acc[COLS + c]);
-        if (dbias) atomicAdd(dbias + c, s_acc[2 * COLS + c]);
+        for (int w = 0; w < LN_WARPS; ++w) t += s_part[w * 3 * COLS + c];
+        float* dst = c < COLS ? dgamma : (c < 2 * COLS ? dbeta : dbias);
+        if (dst) atomicAdd(dst + (c % COLS), t);
     }
 }
 
@@ -251,57 +227,55 @@ embed_ln_fwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ w
     }
 }
 
-// embeddings backward: recompute x from the tables, LN backward, scatter-add into word/pos gradients
+// embeddings backward: recompute x from the tables, LN backward, scatter-add into word/pos gradients.
+// Rows at or past the sample's valid length are padding: nothing downstream depends on them (keys are masked, only
+// the CLS row feeds the head), so their incoming gradient is exactly zero and they are skipped -- this also removes
+// the atomic pile-up on the [PAD] embedding row.
 template <int NV>
 __global__ void __launch_bounds__(LN_WARPS * 32)
 embed_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy1, const __nv_bfloat16* __restrict__ dy2,
                     const int32_t* __restrict__ ids, const float* __restrict__ word, const float* __restrict__ pos,
                     const float* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ rstd,
                     float* __restrict__ dword, float* __restrict__ dpos, float* __restrict__ dgamma,
-                    float* __restrict__ dbeta, int rows, int seq, uint32_t thresh, float keep_scale,
-                    const uint64_t* __restrict__ rng, uint32_t stream_id) {
+                    float* __restrict__ dbeta, const int32_t* __restrict__ lens, int rows, int seq, uint32_t thresh,
+                    float keep_scale, const uint64_t* __restrict__ rng, uint32_t stream_id) {
     constexpr int COLS = NV * 256;
-    __shared__ float s_acc[2 * COLS];
+    extern __shared__ float s_part[];  // [warp][2][COLS]
     const uint32_t warp = threadIdx.x >> 5, lane = lane_id();
     const uint64_t seed = rng_seed(rng);
-    float acc_g[NV][8], acc_b[NV][8];
-#pragma unroll
-    for (int v = 0; v < NV; ++v)
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { acc_g[v][j] = 0.f; acc_b[v][j] = 0.f; }
-    const int row0 = blockIdx.x * LN_ROWS_PER_CTA_BWD;
-    for (int rr = warp; rr < LN_ROWS_PER_CTA_BWD; rr += LN_WARPS) {
-        const int row = row0 + rr;
-        if (row >= rows) break;
+    const int row = blockIdx.x * LN_WARPS + warp;
+    float* slot = s_part + warp * 2 * COLS;
+    bool active = row < rows;
+    if (active && lens) active = (row % seq) < lens[row / seq];
+    if (active) {
         const int id = ids[row];
         const int ps = row % seq;
         const float mu = mean[row], rs = rstd[row];
-        float g[NV][8], xh[NV][8];
+        float g[NV][8], xh[NV][8], d[NV][8];
         float c1 = 0.f, c2 = 0.f;
 #pragma unroll
         for (int v = 0; v < NV; ++v) {
             const int col = (v * 32 + lane) * 8;
             const size_t off = static_cast<size_t>(row) * COLS + col;
-            float d[8], w[8], pp[8], gm[8];
-            load8(dy1 + off, d);
+            float w[8], pp[8], gm[8];
+            load8(dy1 + off, d[v]);
             if (dy2) {
                 float d2[8];
                 load8(dy2 + off, d2);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) d[j] += d2[j];
+                for (int j = 0; j < 8; ++j) d[v][j] += d2[j];
             }
             load8f(word + static_cast<size_t>(id) * COLS + col, w);
             load8f(pos + static_cast<size_t>(ps) * COLS + col, pp);
             load8f(gamma + col, gm);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-                if (thresh) d[j] = dropout_keep(seed, stream_id, row * COLS + col + j, thresh) ? d[j] * keep_scale : 0.f;
+                if (thresh)
+                    d[v][j] = dropout_keep(seed, stream_id, row * COLS + col + j, thresh) ? d[v][j] * keep_scale : 0.f;
                 xh[v][j] = (w[j] + pp[j] - mu) * rs;
-                g[v][j] = d[j] * gm[j];
+                g[v][j] = d[v][j] * gm[j];
                 c1 += g[v][j];
                 c2 += g[v][j] * xh[v][j];
-                acc_g[v][j] += d[j] * xh[v][j];
-                acc_b[v][j] += d[j];
             }
         }
         c1 = warp_sum(c1) * (1.0f / COLS);
@@ -309,31 +283,28 @@ embed_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy1, const __nv_bfloat16* 
 #pragma unroll
         for (int v = 0; v < NV; ++v) {
             const int col = (v * 32 + lane) * 8;
+            float pg[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 const float dx = rs * (g[v][j] - c1 - xh[v][j] * c2);
                 atomicAdd(dword + static_cast<size_t>(id) * COLS + col + j, dx);
                 atomicAdd(dpos + static_cast<size_t>(ps) * COLS + col + j, dx);
+                pg[j] = d[v][j] * xh[v][j];
             }
+            *reinterpret_cast<float4*>(slot + col) = make_float4(pg[0], pg[1], pg[2], pg[3]);
+            *reinterpret_cast<float4*>(slot + col + 4) = make_float4(pg[4], pg[5], pg[6], pg[7]);
+            *reinterpret_cast<float4*>(slot + COLS + col) = make_float4(d[v][0], d[v][1], d[v][2], d[v][3]);
+            *reinterpret_cast<float4*>(slot + COLS + col + 4) = make_float4(d[v][4], d[v][5], d[v][6], d[v][7]);
         }
+    } else {
+        for (int c = lane; c < 2 * COLS; c += 32) slot[c] = 0.f;
     }
-    for (int w = 0; w < LN_WARPS; ++w) {
-        if (warp == w) {
+    __syncthreads();
+    for (int c = threadIdx.x; c < 2 * COLS; c += blockDim.x) {
+        float t = 0.f;
 #pragma unroll
-            for (int v = 0; v < NV; ++v) {
-                const int col = (v * 32 + lane) * 8;
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    if (w == 0) { s_acc[col + j] = acc_g[v][j]; s_acc[COLS + col + j] = acc_b[v][j]; }
-                    else { s_acc[col + j] += acc_g[v][j]; s_acc[COLS + col + j] += acc_b[v][j]; }
-                }
-            }
-        }
-        __syncthreads();
-    }
-    for (int c = threadIdx.x; c < COLS; c += blockDim.x) {
-        atomicAdd(dgamma + c, s_acc[c]);
-        atomicAdd(dbeta + c, s_acc[COLS + c]);
+        for (int w = 0; w < LN_WARPS; ++w) t += s_part[w * 2 * COLS + c];
+        if (t != 0.f) atomicAdd((c < COLS ? dgamma : dbeta) + (c % COLS), t);
     }
 }
 
@@ -377,13 +348,13 @@ static inline uint32_t drop_thresh(float p) {
 
 using namespace dcad;
 
-#define DCAD_NV_DISPATCH(cols, CALL)      \
-    switch ((cols) / 256) {               \
-        case 1: { constexpr int NV = 1; CALL; } break; \
-        case 2: { constexpr int NV = 2; CALL; } break; \
-        case 3: { constexpr int NV = 3; CALL; } break; \
-        case 4: { constexpr int NV = 4; CALL; } break; \
-        default: return DCAD_ERR_BAD_SHAPE; \
+#define DCAD_NV_DISPATCH(cols, ...)                            \
+    switch ((cols) / 256) {                                    \
+        case 1: { constexpr int NV = 1; __VA_ARGS__; } break;  \
+        case 2: { constexpr int NV = 2; __VA_ARGS__; } break;  \
+        case 3: { constexpr int NV = 3; __VA_ARGS__; } break;  \
+        case 4: { constexpr int NV = 4; __VA_ARGS__; } break;  \
+        default: return DCAD_ERR_BAD_SHAPE;                    \
     }
 
 extern "C" int dcad_add_ln_fwd(const void* a, const void* res, const float* gamma, const float* beta, void* out,
@@ -412,12 +383,21 @@ extern "C" int dcad_add_ln_bwd(const void* dy1, const void* dy2, const void* y, 
     const uint32_t th = drop_thresh(p_drop);
     const float ks = p_drop > 0.f ? 1.0f / (1.0f - p_drop) : 1.0f;
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    const int grid = (rows + LN_ROWS_PER_CTA_BWD - 1) / LN_ROWS_PER_CTA_BWD;
-    DCAD_NV_DISPATCH(cols, (add_ln_bwd_kernel<NV><<<grid, LN_WARPS * 32, 0, s>>>(
-        reinterpret_cast<const __nv_bfloat16*>(dy1), reinterpret_cast<const __nv_bfloat16*>(dy2),
-        reinterpret_cast<const __nv_bfloat16*>(y), gamma, beta, rstd, reinterpret_cast<__nv_bfloat16*>(dz),
-        reinterpret_cast<__nv_bfloat16*>(p_drop > 0.f ? da : nullptr), dgamma, dbeta, dbias, rows, th, ks, rng,
-        stream_id)));
+    const int grid = (rows + LN_WARPS - 1) / LN_WARPS;
+    const int smem = LN_WARPS * 3 * cols * (int)sizeof(float);
+    DCAD_NV_DISPATCH(cols, {
+        static bool attr = false;
+        if (!attr) {
+            DCAD_CUDA_TRY(cudaFuncSetAttribute(add_ln_bwd_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               LN_WARPS * 3 * NV * 256 * (int)sizeof(float)));
+            attr = true;
+        }
+        add_ln_bwd_kernel<NV><<<grid, LN_WARPS * 32, smem, s>>>(
+            reinterpret_cast<const __nv_bfloat16*>(dy1), reinterpret_cast<const __nv_bfloat16*>(dy2),
+            reinterpret_cast<const __nv_bfloat16*>(y), gamma, beta, rstd, reinterpret_cast<__nv_bfloat16*>(dz),
+            reinterpret_cast<__nv_bfloat16*>(p_drop > 0.f ? da : nullptr), dgamma, dbeta, dbias, rows, th, ks, rng,
+            stream_id);
+    });
     return (int)cudaGetLastError();
 }
 
@@ -439,18 +419,28 @@ extern "C" int dcad_embed_ln_fwd(const int32_t* ids, const float* word, const fl
 
 extern "C" int dcad_embed_ln_bwd(const void* dy1, const void* dy2, const int32_t* ids, const float* word,
                                  const float* pos, const float* gamma, const float* mean, const float* rstd,
-                                 float* dword, float* dpos, float* dgamma, float* dbeta, int rows, int seq, int cols,
-                                 float p_drop, const uint64_t* rng, uint32_t stream_id, void* stream) {
+                                 float* dword, float* dpos, float* dgamma, float* dbeta, const int32_t* lens, int rows,
+                                 int seq, int cols, float p_drop, const uint64_t* rng, uint32_t stream_id,
+                                 void* stream) {
     if (rows <= 0) return 0;
     if (cols % 256 || cols > 1024 || seq <= 0) return DCAD_ERR_BAD_SHAPE;
     if (p_drop > 0.f && rng == nullptr) return DCAD_ERR_BAD_ARGUMENT;
     const uint32_t th = drop_thresh(p_drop);
     const float ks = p_drop > 0.f ? 1.0f / (1.0f - p_drop) : 1.0f;
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    const int grid = (rows + LN_ROWS_PER_CTA_BWD - 1) / LN_ROWS_PER_CTA_BWD;
-    DCAD_NV_DISPATCH(cols, (embed_ln_bwd_kernel<NV><<<grid, LN_WARPS * 32, 0, s>>>(
-        reinterpret_cast<const __nv_bfloat16*>(dy1), reinterpret_cast<const __nv_bfloat16*>(dy2), ids, word, pos,
-        gamma, mean, rstd, dword, dpos, dgamma, dbeta, rows, seq, th, ks, rng, stream_id)));
+    const int grid = (rows + LN_WARPS - 1) / LN_WARPS;
+    const int smem = LN_WARPS * 2 * cols * (int)sizeof(float);
+    DCAD_NV_DISPATCH(cols, {
+        static bool attr = false;
+        if (!attr) {
+            DCAD_CUDA_TRY(cudaFuncSetAttribute(embed_ln_bwd_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               LN_WARPS * 2 * NV * 256 * (int)sizeof(float)));
+            attr = true;
+        }
+        embed_ln_bwd_kernel<NV><<<grid, LN_WARPS * 32, smem, s>>>(
+            reinterpret_cast<const __nv_bfloat16*>(dy1), reinterpret_cast<const __nv_bfloat16*>(dy2), ids, word, pos,
+            gamma, mean, rstd, dword, dpos, dgamma, dbeta, lens, rows, seq, th, ks, rng, stream_id);
+    });
     return (int)cudaGetLastError();
 }
 

@@ -45,8 +45,9 @@ class GemmPlan:
     lin1_dgrad: int = 128   # -> [T, 768]
     out_dgrad: int = 128
     qkv_dgrad: int = 128
-    wgrad_wide: int = 128   # N = 768 outputs
-    wgrad_lin2: int = 256   # N = 3072 outputs
+    wgrad_wide: int = 128   # N = 768 outputs (lin1 / qkv wgrad)
+    wgrad_out: int = 64     # out_lin wgrad: 768x768 output, more (smaller) tiles fill more SMs
+    wgrad_lin2: int = 128   # N = 3072 outputs
 
 
 class B200Engine:
@@ -235,7 +236,7 @@ class B200Engine:
             self._k(nv.add_ln_bwd, dsa, dz2, sa, P["g1"][l], P["b1"][l], self.rstd1[l], dz1, None, P["d_g1"][l],
                     P["d_b1"][l], P["d_bo"][l])
             # out_lin: dWo = dz1^T ctx ; dctx = dz1 Wo
-            self._gemm(dz1, ctx, P["d_wo"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_wide)
+            self._gemm(dz1, ctx, P["d_wo"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_out)
             dctx = self.g_c
             self._gemm(dz1, P["wo"][l], dctx, b_major=MN, block_n=pl.out_dgrad)
             # attention
@@ -248,7 +249,7 @@ class B200Engine:
             self._gemm(self.g_qkv, P["wqkv"][l], dxq, b_major=MN, block_n=pl.qkv_dgrad)
             dy1, dy2 = dxq, dz1  # gradient wrt x_l = via QKV projection + via the residual
         self._k(nv.embed_ln_bwd, dy1, dy2, self.ids, self.word, self.pos, self.eg, self.emb_mean, self.emb_rstd,
-                self.d_word, self.d_pos, self.d_eg, self.d_eb, S, p_drop=d.dropout, rng=self.rng,
+                self.d_word, self.d_pos, self.d_eg, self.d_eb, S, lens=self.lens, p_drop=d.dropout, rng=self.rng,
                 stream_id=_STREAM_EMBED)
 
     def _optimizer(self) -> None:

@@ -83,7 +83,7 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("dcad_add_ln_fwd", [P, P, P, P, P, P, I, I, F, F, P, U32, P])
     sig("dcad_add_ln_bwd", [P, P, P, P, P, P, P, P, P, P, P, I, I, F, P, U32, P])
     sig("dcad_embed_ln_fwd", [P, P, P, P, P, P, P, P, I, I, I, F, F, P, U32, P])
-    sig("dcad_embed_ln_bwd", [P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, F, P, U32, P])
+    sig("dcad_embed_ln_bwd", [P, P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, F, P, U32, P])
     sig("dcad_colsum_bf16", [P, P, I, I, I, P])
     sig("dcad_cls_head_train", [P, I, P, P, P, I, F, P, U32, P, P, P, P, P, I, P])
     sig("dcad_cls_head_eval", [P, I, P, P, P, I, I, P, P, P, P, P])
@@ -177,12 +177,12 @@ def embed_ln_fwd(ids, word, pos, gamma, beta, out, mean, rstd, seq, *, eps=1e-12
     return out
 
 
-def embed_ln_bwd(dy1, dy2, ids, word, pos, gamma, mean, rstd, dword, dpos, dgamma, dbeta, seq, *, p_drop=0.0,
-                 rng=None, stream_id=0, stream=None):
+def embed_ln_bwd(dy1, dy2, ids, word, pos, gamma, mean, rstd, dword, dpos, dgamma, dbeta, seq, *, lens=None,
+                 p_drop=0.0, rng=None, stream_id=0, stream=None):
     rows, cols = dy1.shape
     check(lib().dcad_embed_ln_bwd(ptr(dy1), ptr(dy2), ptr(ids), ptr(word), ptr(pos), ptr(gamma), ptr(mean),
-                                  ptr(rstd), ptr(dword), ptr(dpos), ptr(dgamma), ptr(dbeta), rows, seq, cols, p_drop,
-                                  ptr(rng), stream_id, stream_ptr(stream)), "dcad_embed_ln_bwd")
+                                  ptr(rstd), ptr(dword), ptr(dpos), ptr(dgamma), ptr(dbeta), ptr(lens), rows, seq,
+                                  cols, p_drop, ptr(rng), stream_id, stream_ptr(stream)), "dcad_embed_ln_bwd")
 
 
 def colsum_bf16(x, out, stream=None):

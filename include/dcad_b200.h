@@ -68,11 +68,13 @@ int dcad_add_ln_bwd(const void* dy1, const void* dy2, const void* y, const float
 int dcad_embed_ln_fwd(const int32_t* ids, const float* word, const float* pos, const float* gamma, const float* beta,
                       void* out, float* mean, float* rstd, int rows, int seq, int cols, float eps, float p_drop,
                       const uint64_t* rng, uint32_t stream_id, void* stream);
-/* backward: scatter-adds into dword [vocab, cols] / dpos [max_pos, cols] and accumulates dgamma / dbeta. */
+/* backward: scatter-adds into dword [vocab, cols] / dpos [max_pos, cols] and accumulates dgamma / dbeta.
+ * lens [rows / seq] (may be NULL): rows at or past a sample's valid length are padding with an exactly-zero
+ * gradient and are skipped. */
 int dcad_embed_ln_bwd(const void* dy1, const void* dy2, const int32_t* ids, const float* word, const float* pos,
                       const float* gamma, const float* mean, const float* rstd, float* dword, float* dpos,
-                      float* dgamma, float* dbeta, int rows, int seq, int cols, float p_drop, const uint64_t* rng,
-                      uint32_t stream_id, void* stream);
+                      float* dgamma, float* dbeta, const int32_t* lens, int rows, int seq, int cols, float p_drop,
+                      const uint64_t* rng, uint32_t stream_id, void* stream);
 /* out[c] += sum_r x[r, c]  (bf16 in, fp32 accumulate): bias gradients (autograd of nn.Linear bias). */
 int dcad_colsum_bf16(const void* x, float* out, int rows, int cols, int ld, void* stream);
 

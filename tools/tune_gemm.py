@@ -1,0 +1,100 @@
+"""Times every GEMM of the DDoSClassifier training step (tokens = batch*seq) for each BLOCK_N, inside a CUDA graph
+(kernel time, not Python launch overhead), next to cuBLAS (torch.matmul) on the same math.  Prints a table and the
+best BLOCK_N per GEMM; writes gpurun_out/tune_gemm.json."""
+from __future__ import annotations
+
+import json
+import os
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+
+import torch  # noqa: E402
+
+from detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200.ops import native as nv  # noqa: E402
+
+T = int(os.environ.get("TOKENS", 2048))
+D, F = 768, 3072
+# name, M, N, K, a_major, b_major, epi
+GEMMS = [
+    ("qkv_fwd", T, 3 * D, D, 0, 0, 1), ("out_fwd", T, D, D, 0, 0, 1), ("lin1_fwd", T, F, D, 0, 0, 2),
+    ("lin2_fwd", T, D, F, 0, 0, 1),
+    ("lin2_dgrad", T, F, D, 0, 1, 3), ("lin1_dgrad", T, D, F, 0, 1, 0), ("out_dgrad", T, D, D, 0, 1, 0),
+    ("qkv_dgrad", T, D, 3 * D, 0, 1, 0),
+    ("lin2_wgrad", D, F, T, 1, 1, 0), ("lin1_wgrad", F, D, T, 1, 1, 0), ("out_wgrad", D, D, T, 1, 1, 0),
+    ("qkv_wgrad", 3 * D, D, T, 1, 1, 0),
+]
+
+
+def time_graph(fn, iters=20, reps=5):
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for _ in range(3):
+            fn()
+        s.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            for _ in range(iters):
+                fn()
+        best = 1e9
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(s)
+            g.replay()
+            e1.record(s)
+            s.synchronize()
+            best = min(best, e0.elapsed_time(e1) / iters)
+    torch.cuda.current_stream().wait_stream(s)
+    return best * 1e3  # us
+
+
+def main():
+    torch.manual_seed(0)
+    dev = "cuda"
+    res = []
+    for name, M, N, K, am, bm, epi in GEMMS:
+        a = torch.randn((M, K) if am == 0 else (K, M), device=dev).bfloat16()
+        b = (torch.randn((N, K) if bm == 0 else (K, N), device=dev) * 0.05).bfloat16()
+        wgrad = am == 1
+        out = torch.empty(M, N, device=dev, dtype=torch.float32 if wgrad else torch.bfloat16)
+        bias = torch.randn(N, device=dev) if epi in (1, 2) else None
+        aux = torch.randn(M, N, device=dev).bfloat16() if epi == 3 else None
+        aux_out = torch.empty(M, N, device=dev, dtype=torch.bfloat16) if epi == 2 else None
+        A = a if am == 0 else a.t()
+        B = b if bm == 0 else b.t()
+        cub = time_graph(lambda: torch.matmul(A, B.t()))
+        row = {"name": name, "M": M, "N": N, "K": K, "cublas_us": cub, "bn": {}}
+        for bn in (32, 64, 96, 128, 192, 256):
+            if N % bn and bn != 256:
+                continue
+            if bm == 1 and bn % 64:
+                continue
+            if bn == 32 and bm != 0:
+                continue
+            try:
+                us = time_graph(lambda: nv.gemm_bf16(a, b, out, a_major=am, b_major=bm, bias=bias, aux=aux,
+                                                     aux_out=aux_out, epi=epi, block_n=bn))
+                row["bn"][bn] = us
+            except Exception as e:  # noqa: BLE001
+                row["bn"][bn] = None
+                row.setdefault("errors", {})[bn] = repr(e)[:120]
+        ok = {k: v for k, v in row["bn"].items() if v}
+        row["best_bn"] = min(ok, key=ok.get) if ok else None
+        row["best_us"] = ok[row["best_bn"]] if ok else None
+        row["tflops_best"] = 2.0 * M * N * K / (row["best_us"] * 1e-6) / 1e12 if ok else None
+        res.append(row)
+        print(f"{name:11s} {M:5d}x{N:5d}x{K:5d} cublas {cub:7.1f}us | " +
+              " ".join(f"{bn}:{(v if v else -1):6.1f}" for bn, v in row["bn"].items()) +
+              f" | best {row['best_bn']} {row['best_us']:.1f}us {row['tflops_best']:.0f}TF", flush=True)
+    tot = sum(r["best_us"] for r in res) * 6
+    totc = sum(r["cublas_us"] for r in res) * 6
+    print(f"sum over 6 layers: ours(best) {tot:.0f} us, cuBLAS (no epilogues) {totc:.0f} us")
+    os.makedirs(ROOT / "gpurun_out", exist_ok=True)
+    (ROOT / "gpurun_out" / "tune_gemm.json").write_text(json.dumps(res, indent=1))
+
+
+if __name__ == "__main__":
+    main()
