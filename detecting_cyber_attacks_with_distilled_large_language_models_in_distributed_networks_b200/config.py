@@ -1,0 +1,87 @@
+"""One configuration object for every role (the reference hard-codes every knob as a literal — SURVEY.md §5.6).
+
+Defaults are the reference's literals: fraction 0.1 (client1.py:23), max_len 128 (:27), batch 16 (:370), lr 2e-5 and
+3 epochs (:380), ports 12345/12346 and 2 clients (server.py:11-13), 300 s socket timeout, 5 retries.
+"""
+from __future__ import annotations
+
+import argparse
+import dataclasses
+from dataclasses import dataclass, field
+from typing import Optional
+
+TRANSPORTS = ("nvswitch", "nvswitch-oneshot", "nccl", "socket", "none")
+
+
+@dataclass
+class FedConfig:
+    # topology
+    num_clients: int = 2
+    client_id: int = 1                 # 1-based, like the reference's "Client 1" / "Client 2"
+    rounds: int = 1
+    transport: str = "socket"          # nvswitch | nvswitch-oneshot | nccl (baseline) | socket | none
+    gpus_per_client: int = 1
+    # training (reference literals)
+    local_epochs: int = 3
+    batch_size: int = 16
+    max_len: int = 128
+    lr: float = 2e-5
+    backend: str = "auto"              # auto | b200 | torch
+    seed: Optional[int] = None         # default: 41 + client_id (reference: 42 / 43)
+    # data
+    data_path: str = "CICIDS2017.csv"
+    data_fraction: float = 0.1
+    synthetic_rows: int = 0            # >0: generate a synthetic CICIDS-shaped CSV when data_path is missing
+    disjoint_shards: bool = False      # extension: clients sample disjoint interleaved shards
+    model_dir: str = "./distilbert-base-uncased"   # vocab.txt (+ optional weights) if present; synthetic vocab otherwise
+    # model size overrides (tests / plumbing tier); None = DistilBERT-base
+    n_layers: Optional[int] = None
+    dim: Optional[int] = None
+    n_heads: Optional[int] = None
+    hidden_dim: Optional[int] = None
+    vocab_size: Optional[int] = None
+    # socket transport
+    host: str = "localhost"
+    port_recv: int = 12345
+    port_send: int = 12346
+    timeout: float = 300.0
+    accept_timeout: Optional[float] = None
+    max_retries: int = 5
+    gzip_level: int = 1
+    min_clients: Optional[int] = None  # quorum for the socket server (default: all)
+    # outputs
+    out_dir: str = "."
+    plots: bool = True
+    extra_curves: bool = False         # ROC / PR curves (dead code in the reference, optional here)
+    save_val_metrics: bool = False     # the reference computes validation metrics and drops them (Q9)
+    event_log: Optional[str] = None
+    quiet: bool = False
+
+    def resolved_seed(self) -> int:
+        return self.seed if self.seed is not None else 41 + self.client_id
+
+    def model_dims(self):
+        from .models.arena import ModelDims
+
+        over = {k: getattr(self, k) for k in ("n_layers", "dim", "n_heads", "hidden_dim", "vocab_size")
+                if getattr(self, k) is not None}
+        return dataclasses.replace(ModelDims(), **over)
+
+
+def add_arguments(ap: argparse.ArgumentParser) -> None:
+    for f in dataclasses.fields(FedConfig):
+        name = "--" + f.name.replace("_", "-")
+        if f.type in ("bool", bool):
+            ap.add_argument(name, action=argparse.BooleanOptionalAction, default=f.default)
+        else:
+            base = {"int": int, "float": float, "str": str, "Optional[int]": int, "Optional[float]": float,
+                    "Optional[str]": str}.get(str(f.type), str)
+            ap.add_argument(name, type=base, default=f.default)
+
+
+def from_args(ns: argparse.Namespace) -> FedConfig:
+    kw = {f.name: getattr(ns, f.name) for f in dataclasses.fields(FedConfig) if hasattr(ns, f.name)}
+    cfg = FedConfig(**kw)
+    if cfg.transport not in TRANSPORTS:
+        raise ValueError(f"transport must be one of {TRANSPORTS}")
+    return cfg

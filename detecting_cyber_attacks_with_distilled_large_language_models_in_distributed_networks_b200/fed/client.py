@@ -1,0 +1,107 @@
+"""A federated client, start to finish — the parametrised replacement for the copy-pasted ``client1.py`` /
+``client2.py`` (reference ``main`` client1.py:353-411; call stack in SURVEY.md §3.1).
+
+Per round: train locally -> evaluate (val, test) -> write ``clientN_local_metrics.csv`` -> save ``clientN_model.pth`` ->
+aggregate through the configured transport -> evaluate the aggregated model -> ``clientN_aggregated_metrics.csv`` ->
+plots -> save again.  File names, CSV schema, plot names and the resume-from-``clientN_model.pth`` behaviour match the
+reference; with ``rounds > 1`` later rounds add a ``_roundK`` suffix (the reference is single-round).  Degraded paths
+are kept: if aggregation fails the client still plots its local results (client1.py:405-410).
+"""
+from __future__ import annotations
+
+import os
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from ..config import FedConfig
+from ..data import cicids, synth
+from ..data.pack import PackedSplit, pack_texts
+from ..data.split import split_indices
+from ..data.tokenizer import WordPieceTokenizer
+from ..report.log import EventLog
+from ..report.metrics import EvalResult, save_metrics
+from ..report.plots import plot_evaluation
+from ..train.trainer import evaluate_model, make_backend, train_model
+from .transport import Transport
+
+
+def prepare_data(cfg: FedConfig, log: EventLog) -> Tuple[PackedSplit, PackedSplit, PackedSplit, WordPieceTokenizer]:
+    seed = cfg.resolved_seed()
+    path = cfg.data_path
+    if not os.path.exists(path):
+        if cfg.synthetic_rows <= 0:
+            raise FileNotFoundError(f"{path} does not exist (pass --synthetic-rows N to generate CICIDS-shaped data)")
+        os.makedirs(cfg.out_dir, exist_ok=True)
+        path = os.path.join(cfg.out_dir, "synthetic_CICIDS2017.csv")
+        if not os.path.exists(path):
+            synth.write_synthetic_csv(path, cfg.synthetic_rows, seed=0)
+    with log.phase("data preprocessing", path=path):
+        shard = (cfg.client_id - 1, cfg.num_clients) if cfg.disjoint_shards else None
+        texts, labels = cicids.preprocess_data(path, cfg.data_fraction, seed, shard=shard)
+    tok = WordPieceTokenizer.from_dir_or_synthetic(cfg.model_dir)
+    with log.phase("tokenisation", samples=len(texts)):
+        packed = pack_texts(tok, texts, labels, cfg.max_len)
+    tr, va, te = split_indices(len(texts), seed)
+    return packed.subset(tr), packed.subset(va), packed.subset(te), tok
+
+
+def run_client(cfg: FedConfig, transport: Optional[Transport] = None, backend=None,
+               backend_kwargs: Optional[dict] = None) -> Dict[str, EvalResult]:
+    cid = cfg.client_id
+    name = f"Client {cid}"
+    os.makedirs(cfg.out_dir, exist_ok=True)
+    log = EventLog(f"CLIENT {cid}", cfg.event_log, cfg.quiet)
+    log.say("Starting client")
+    out = lambda f: os.path.join(cfg.out_dir, f)  # noqa: E731
+    model_path = out(f"client{cid}_model.pth")
+
+    train, val, test, tok = prepare_data(cfg, log)
+    dims = cfg.model_dims()
+    if tok.vocab_size > dims.vocab_size:
+        raise ValueError(f"tokenizer vocabulary ({tok.vocab_size}) exceeds the model's ({dims.vocab_size})")
+    if backend is None:
+        kw = dict(dims=dims, batch=cfg.batch_size, seq=cfg.max_len, lr=cfg.lr, seed=cfg.resolved_seed())
+        kw.update(backend_kwargs or {})
+        backend = make_backend(cfg.backend, **kw)
+    if os.path.exists(model_path):  # reference client1.py:375-377: continue from the last (aggregated) weights
+        log.say(f"loading pre-trained model from {model_path}")
+        backend.load_state_dict(torch.load(model_path, map_location="cpu"))
+
+    results: Dict[str, EvalResult] = {}
+    for rnd in range(cfg.rounds):
+        sfx = "" if rnd == 0 else f"_round{rnd + 1}"
+        train_model(backend, train, cfg.local_epochs, seed=cfg.resolved_seed() + 1000 * rnd, log=log, name=name)
+        print(f"{name} evaluating local model on validation set...")
+        val_local = evaluate_model(backend, val, log, name, want_probs=False)
+        print(f"{name} evaluating local model on test set...")
+        local = evaluate_model(backend, test, log, name, want_probs=cfg.extra_curves)
+        save_metrics(local, out(f"client{cid}_local_metrics{sfx}.csv"))
+        if cfg.save_val_metrics:
+            save_metrics(val_local, out(f"client{cid}_local_val_metrics{sfx}.csv"))
+        torch.save(backend.state_dict(), model_path)
+        results[f"local{sfx}"] = local
+
+        aggregated: Optional[EvalResult] = None
+        ok = False
+        if transport is not None:
+            with log.phase("federated aggregation", transport=transport.name, round=rnd + 1):
+                ok = transport.aggregate(backend)
+        if ok:
+            log.say("updated with aggregated model")
+            print(f"{name} evaluating aggregated model on validation set...")
+            val_agg = evaluate_model(backend, val, log, name, want_probs=False)
+            print(f"{name} evaluating aggregated model on test set...")
+            aggregated = evaluate_model(backend, test, log, name, want_probs=cfg.extra_curves)
+            save_metrics(aggregated, out(f"client{cid}_aggregated_metrics{sfx}.csv"))
+            if cfg.save_val_metrics:
+                save_metrics(val_agg, out(f"client{cid}_aggregated_val_metrics{sfx}.csv"))
+            torch.save(backend.state_dict(), model_path)
+            results[f"aggregated{sfx}"] = aggregated
+        elif transport is not None:
+            log.say("skipping aggregated model evaluation due to aggregation failure")
+        if cfg.plots:
+            with log.phase("plot generation"):
+                plot_evaluation(local, aggregated, out(f"client{cid}_plots{sfx}"), cid, extra_curves=cfg.extra_curves)
+    log.say("Client shutdown")
+    return results

@@ -1,0 +1,101 @@
+"""L0 data layer parity with the reference (client1.py:68-93,365-366) and tokenizer parity with HF."""
+from __future__ import annotations
+
+import numpy as np
+import pandas as pd
+import pytest
+
+from detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200.data import (
+    cicids, pack, split, synth, tokenizer)
+
+
+@pytest.fixture(scope="module")
+def csv_path(tmp_path_factory):
+    p = tmp_path_factory.mktemp("data") / "CICIDS2017.csv"
+    synth.write_synthetic_csv(str(p), 800, seed=3)
+    return str(p)
+
+
+def test_synthetic_csv_has_reference_schema(csv_path):
+    header = open(csv_path).readline().rstrip("\n").split(",")
+    assert len(header) == 79 and header.count("Fwd Header Length") == 2 and header[-1] == "Label"
+    assert " Flow IAT Max" in header  # leading-blank headers preserved
+    raw = open(csv_path).read()
+    assert "Infinity" in raw
+    df = pd.read_csv(csv_path)
+    assert set(df["Label"].unique()) == {"BENIGN", "DDoS"}
+    assert np.isinf(df["Flow Bytes/s"]).sum() >= 1
+
+
+def test_features_to_text_matches_reference_bytes(csv_path, ref_client1):
+    df = pd.read_csv(csv_path)
+    df.replace([np.inf, -np.inf], np.nan, inplace=True)
+    df.fillna(df.mean(numeric_only=True), inplace=True)
+    expect = df.apply(ref_client1.features_to_text, axis=1).tolist()
+    assert cicids.frame_to_texts(df) == expect
+    assert cicids.features_to_text(df.iloc[0]) == expect[0]
+
+
+@pytest.mark.parametrize("client_id", [1, 2])
+def test_preprocess_data_matches_reference(csv_path, client_id, monkeypatch):
+    from conftest import load_reference_module
+
+    ref = load_reference_module(f"client{client_id}")
+    rt, rl = ref.preprocess_data(csv_path, 0.25)
+    texts, labels = cicids.preprocess_data(csv_path, 0.25, cicids.client_seed(client_id))
+    assert texts == rt and labels == rl
+    assert cicids.client_seed(1) == 42 and cicids.client_seed(2) == 43
+
+
+def test_split_is_the_reference_60_20_20():
+    from sklearn.model_selection import train_test_split
+
+    texts = [f"t{i}" for i in range(503)]
+    labels = list(range(503))
+    xtr, xtmp, ytr, ytmp = train_test_split(texts, labels, test_size=0.4, random_state=42)
+    xva, xte, yva, yte = train_test_split(xtmp, ytmp, test_size=0.5, random_state=42)
+    got = split.split_lists(texts, labels, 42)
+    assert got == (xtr, xva, xte, ytr, yva, yte)
+    tr, va, te = split.split_indices(503, 42)
+    assert len(tr) == 301 and len(va) == 101 and len(te) == 101
+
+
+def test_disjoint_shards_do_not_overlap(csv_path):
+    a, _ = cicids.preprocess_data(csv_path, 1.0, 42, shard=(0, 2))
+    b, _ = cicids.preprocess_data(csv_path, 1.0, 43, shard=(1, 2))
+    assert len(a) + len(b) == 800
+
+
+def test_wordpiece_matches_hf_tokenizer(tmp_path):
+    transformers = pytest.importorskip("transformers")
+    vocab = tokenizer.synthetic_vocab()
+    assert len(vocab) == 30522 and vocab[0] == "[PAD]" and vocab[100] == "[UNK]" and vocab[101] == "[CLS]"
+    assert vocab[102] == "[SEP]" and vocab[103] == "[MASK]" and len(set(vocab)) == 30522
+    d = tmp_path / "distilbert-base-uncased"
+    tokenizer.write_vocab(str(d / "vocab.txt"), vocab)
+    hf = transformers.DistilBertTokenizer.from_pretrained(str(d))
+    ours = tokenizer.WordPieceTokenizer.from_dir_or_synthetic(str(d))
+    texts = cicids.frame_to_texts(cicids.clean_frame(synth.synth_flows(40, seed=5)))
+    texts += ["Héllo, wörld!  unknownwordzzz 12345678901234567890 a/b", ""]
+    for t in texts:
+        enc = hf(t, add_special_tokens=True, max_length=128, padding="max_length", truncation=True)
+        ids, n = ours.encode(t, 128)
+        assert ids == enc["input_ids"], t
+        assert n == sum(enc["attention_mask"])
+
+
+def test_pack_and_iterate():
+    tok = tokenizer.WordPieceTokenizer(tokenizer.synthetic_vocab())
+    texts = cicids.frame_to_texts(cicids.clean_frame(synth.synth_flows(50, seed=1)))
+    ps = pack.pack_texts(tok, texts, [i % 2 for i in range(50)])
+    assert ps.input_ids.shape == (50, 128) and int(ps.lens.max()) <= 128
+    assert (ps.attention_mask().sum(1) == ps.lens).all()
+    assert ps.num_batches(16) == 4
+    sizes = [b[0].shape[0] for b in pack.iterate_batches(ps, 16)]
+    assert sizes == [16, 16, 16, 2]
+    import torch
+    g1 = torch.Generator().manual_seed(7)
+    g2 = torch.Generator().manual_seed(7)
+    a = [b[2].tolist() for b in pack.iterate_batches(ps, 16, shuffle=True, generator=g1)]
+    b = [b[2].tolist() for b in pack.iterate_batches(ps, 16, shuffle=True, generator=g2)]
+    assert a == b  # seeded shuffling is reproducible (the reference's is not: SURVEY Q12)

@@ -1,0 +1,34 @@
+"""Multi-process launcher on CPU: 2 ranks over gloo (127.0.0.1), tiny model, one FedAvg round."""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+
+import pandas as pd
+import torch
+
+from detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200.data import synth
+
+PKG = "detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200"
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_two_rank_gloo_launch(tmp_path):
+    tmp = str(tmp_path)
+    synth.write_synthetic_csv(os.path.join(tmp, "CICIDS2017.csv"), 200, seed=21)
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""), CUDA_VISIBLE_DEVICES="")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", str(29700 + os.getpid() % 200), "-m", f"{PKG}.cli", "launch",
+           "--num-clients", "2", "--backend", "torch", "--local-epochs", "1", "--data-path",
+           os.path.join(tmp, "CICIDS2017.csv"), "--data-fraction", "0.5", "--out-dir", tmp, "--n-layers", "1", "--dim",
+           "64", "--n-heads", "4", "--hidden-dim", "128", "--max-len", "64", "--no-plots", "--quiet"]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-3000:]
+    a = torch.load(os.path.join(tmp, "client1_model.pth"))
+    b = torch.load(os.path.join(tmp, "client2_model.pth"))
+    assert all(torch.equal(a[k], b[k]) for k in a)
+    assert os.path.exists(os.path.join(tmp, "ddos_distilbert_model.pth"))
+    for cid in (1, 2):
+        for kind in ("local", "aggregated"):
+            assert len(pd.read_csv(os.path.join(tmp, f"client{cid}_{kind}_metrics.csv"))) == 1
