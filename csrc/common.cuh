@@ -52,12 +52,32 @@ __device__ __forceinline__ float2 unpack_bf16x2(uint32_t u) {
     return __bfloat1622float2(v);
 }
 
-// exact (erf) GELU, the activation HF DistilBERT uses, and its derivative
-__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+// erf-based GELU (the activation HF DistilBERT uses) and its derivative.  erf is evaluated with the
+// Abramowitz-Stegun 7.1.26 rational approximation (|error| <= 1.5e-7, far below bf16 resolution): one MUFU.EX2,
+// one MUFU.RCP and 6 FMAs instead of libdevice erff's ~40 instructions -- the GELU epilogue is ALU-bound otherwise.
+// Both functions share the single exponential exp(-x^2/2).
+__device__ __forceinline__ void gelu_parts(float x, float& cdf, float& pdf) {
+    const float z = fabsf(x) * 0.70710678118654752f;           // |x| / sqrt(2)
+    const float e = __expf(-z * z);                            // exp(-x^2 / 2)
+    float t;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
+    float poly = fmaf(1.061405429f, t, -1.453152027f);
+    poly = fmaf(poly, t, 1.421413741f);
+    poly = fmaf(poly, t, -0.284496736f);
+    poly = fmaf(poly, t, 0.254829592f);
+    const float erf_abs = 1.0f - poly * t * e;                 // erf(|x| / sqrt(2))
+    cdf = 0.5f * (1.0f + copysignf(erf_abs, x));
+    pdf = 0.39894228040143268f * e;
+}
+__device__ __forceinline__ float gelu_erf(float x) {
+    float cdf, pdf;
+    gelu_parts(x, cdf, pdf);
+    return x * cdf;
+}
 __device__ __forceinline__ float dgelu_erf(float x) {
-    const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
-    const float pdf = 0.39894228040143268f * __expf(-0.5f * x * x);
-    return cdf + x * pdf;
+    float cdf, pdf;
+    gelu_parts(x, cdf, pdf);
+    return fmaf(x, pdf, cdf);
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -142,6 +162,26 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst_smem, const CUtensorMap
         : "memory");
 }
 
+// TMA stores (shared -> global), bulk-group completion
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src_smem, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(map), "r"(src_smem), "r"(c0), "r"(c1) : "memory");
+}
+// global[tile] += shared[tile] (fp32 add performed by the TMA unit at L2)
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, uint32_t src_smem, int c0, int c1) {
+    asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(map), "r"(src_smem), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_group_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait_group() {
+    asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+
 // ----------------------------------------------------------------------------------------------
 // tcgen05 / TMEM
 // ----------------------------------------------------------------------------------------------
@@ -204,6 +244,13 @@ __device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&r)
         "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
         : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
           "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x32b_x8(uint32_t taddr, uint32_t (&r)[8]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
         : "r"(taddr)
         : "memory");
 }

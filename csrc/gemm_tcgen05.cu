@@ -1,5 +1,6 @@
 // Persistent, warp-specialised bf16 GEMM for sm_100a: TMA -> 128B-swizzled smem ring -> tcgen05.mma with fp32
-// accumulators in TMEM (double-buffered) -> tcgen05.ld epilogue (bias / GELU / dGELU / fp32 store).
+// accumulators in TMEM (double-buffered) -> tcgen05.ld epilogue (bias / GELU / dGELU) -> swizzled smem staging ->
+// TMA store (or TMA reduce-add for split-K weight gradients).
 //
 // Replaces the cuBLAS GEMMs that the reference reaches through HF DistilBERT's nn.Linear layers
 // (reference client1.py:61 -> transformers modeling_distilbert.py:187-189,205,224-226) and their autograd
@@ -7,10 +8,15 @@
 // materialising a transposed tensor:
 //     forward  Y[T,N]  = X[T,K]  W[N,K]^T        A K-major , B K-major
 //     dgrad    dX[T,K] = dY[T,N] W[N,K]          A K-major , B MN-major
-//     wgrad    dW[N,K] = dY[T,N]^T X[T,K]        A MN-major, B MN-major
+//     wgrad    dW[N,K] = dY[T,N]^T X[T,K]        A MN-major, B MN-major   (fp32 out, optional split-K)
 //
-// Roles (192 threads): warp 0 = TMA producer, warp 1 = single-thread MMA issuer, warps 2..5 = epilogue
-// (warp 2 also owns the TMEM allocation).  Three mbarrier pipelines: smem full/empty, TMEM full/empty.
+// Roles (640 threads): warp 0 = TMA producer, warp 1 = single-thread MMA issuer, warp 2 = TMEM owner,
+// warps 4..19 = epilogue (TMEM lane quarter = warp % 4; the four warps of a quarter split each staging slab).
+// Three mbarrier pipelines: smem full/empty, TMEM full/empty, plus bulk-group tracking of the TMA stores.
+//
+// Measured on B200 (tools/microbench_mma.py): a tcgen05.mma of N <= 128 costs ~80-110 cycles to issue regardless of
+// N, only N = 256 runs at the tensor-pipe rate (128 cycles) -- hence wide tiles, and split-K (not narrower tiles)
+// when a problem has too few tiles for 148 SMs.
 #include <mutex>
 #include <unordered_map>
 
@@ -22,19 +28,21 @@ namespace dcad {
 constexpr int BM = 128;  // UMMA M (cta_group::1, full-rate shape)
 constexpr int BK = 64;   // one 128-byte swizzle atom of bf16 along the reduction dim per stage
 constexpr int UMMA_K = 16;
-constexpr int SLAB_BYTES = BK * 128;  // one [BK][64] MN-major slab
+constexpr int SLAB_BYTES = BK * 128;       // one [BK][64] MN-major operand slab
+constexpr int STAGING_BYTES = BM * 128;    // one [128 rows][128 B] output slab (64 bf16 or 32 fp32 columns)
+constexpr int NUM_STAGING = 4;             // D ping-pong + aux_out ping-pong
 
 struct GemmParams {
     int M, N, K;
-    int ldd, ldaux;
+    int ldaux;
     const float* bias;
     const __nv_bfloat16* aux;  // EPI_DGELU: pre-activation (same shape as D)
-    __nv_bfloat16* aux_out;    // EPI_BIAS_GELU: where to keep the pre-activation for backward (may be null)
-    void* D;
+    int has_aux_out;           // EPI_BIAS_GELU: also store the pre-activation through tmAux
     int epi;
     int out_fp32;
-    int accumulate;  // fp32 output only: D += acc
-    int num_m_blocks, num_n_blocks, num_k_blocks;
+    int split_k;               // > 1: fp32 output accumulated with TMA reduce-add (output must be zero-initialised)
+    int num_m_blocks, num_n_blocks, num_k_blocks, kb_per_split;
+    unsigned long long* timing;  // optional: per-role globaltimer stamps of CTA 0 (profiling aid), else null
 };
 
 __host__ __device__ constexpr int pow2_ceil(int v) {
@@ -48,37 +56,38 @@ struct GemmCfg {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES_RAW = (200 * 1024) / STAGE_BYTES;
+    static constexpr int STAGES_RAW = (160 * 1024) / STAGE_BYTES;
     static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
     static constexpr int ACC_STRIDE = pow2_ceil(BN);  // TMEM columns per accumulator stage
     static constexpr int TMEM_COLS = 2 * ACC_STRIDE;  // two accumulator stages
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + NUM_STAGING * STAGING_BYTES + 1024;
 };
 
-constexpr int GEMM_THREADS = 384;        // 12 warps: 0 = TMA, 1 = MMA, 2 = TMEM owner, 3 = idle, 4..11 = epilogue
-constexpr int EPI_THREADS = 256;
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+#define DCAD_STAMP(i) do { if (p.timing && blockIdx.x == 0 && lane == 0) p.timing[i] = gtimer(); } while (0)
 
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+constexpr int GEMM_THREADS = 640;  // 4 control warps + 16 epilogue warps
+constexpr int EPI_THREADS = 512;
 
-template <int N>
-struct TmemChunk;
-template <>
-struct TmemChunk<32> {
-    static __device__ __forceinline__ void ld(uint32_t taddr, uint32_t (&r)[32]) { tmem_ld_32x32b_x32(taddr, r); }
-};
-template <>
-struct TmemChunk<16> {
-    static __device__ __forceinline__ void ld(uint32_t taddr, uint32_t (&r)[16]) { tmem_ld_32x32b_x16(taddr, r); }
-};
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 512;" ::: "memory"); }
+
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
 
 template <int BN, int A_MAJOR, int B_MAJOR>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                         const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmAux,
                          const GemmParams p) {
     using Cfg = GemmCfg<BN>;
     constexpr int STAGES = Cfg::STAGES;
-    static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "BLOCK_N must be a multiple of 32 in [32,256]");
-    static_assert(B_MAJOR == kMajorK || BN % 64 == 0, "MN-major B needs 64-column slabs");
+    static_assert(BN % 64 == 0 && BN >= 64 && BN <= 256, "BLOCK_N must be a multiple of 64 in [64,256]");
+    static_assert(STAGES >= 2, "need at least a double-buffered operand ring");
 
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[STAGES];
@@ -91,10 +100,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t lane = lane_id();
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024-B alignment
+    const uint32_t staging_base = smem_base + STAGES * Cfg::STAGE_BYTES;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
+        tma_prefetch_desc(&tmD);
+        if (p.has_aux_out) tma_prefetch_desc(&tmAux);
     }
     if (warp == 1 && lane == 0) {
 #pragma unroll
@@ -118,15 +130,20 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_smem;
 
-    const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+    // work unit = (output tile, k-split); units are strided over the persistent CTAs
+    const int num_units = p.num_m_blocks * p.num_n_blocks * p.split_k;
+    if (warp == 0) DCAD_STAMP(0);
 
     if (warp == 0) {
         // ===================== TMA producer =====================
         uint32_t stage = 0, phase = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+            const int tile = unit / p.split_k, split = unit % p.split_k;
             const int m_blk = tile % p.num_m_blocks;
             const int n_blk = tile / p.num_m_blocks;
-            for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+            const int kb0 = split * p.kb_per_split;
+            const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
+            for (int kb = kb0; kb < kb1; ++kb) {
                 mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
                 if (lane == 0) {
                     const uint32_t bar = smem_u32(&full_bar[stage]);
@@ -152,169 +169,186 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                 if (++stage == STAGES) { stage = 0; phase ^= 1u; }
             }
         }
+        DCAD_STAMP(1);
     } else if (warp == 1) {
         // ===================== MMA issuer (one thread) =====================
+        // Descriptors are built once; per MMA only the 14-bit start-address field (16-byte units) advances.
         constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MAJOR, B_MAJOR);
+        constexpr uint32_t A_KSTEP = (A_MAJOR == kMajorK ? UMMA_K * 2 : UMMA_K * 128) >> 4;
+        constexpr uint32_t B_KSTEP = (B_MAJOR == kMajorK ? UMMA_K * 2 : UMMA_K * 128) >> 4;
+        const uint64_t a_desc0 = (A_MAJOR == kMajorK) ? make_smem_desc_sw128(smem_base, 16, 1024)
+                                                      : make_smem_desc_sw128(smem_base, SLAB_BYTES, 1024);
+        const uint64_t b_desc0 = (B_MAJOR == kMajorK) ? make_smem_desc_sw128(smem_base + Cfg::A_BYTES, 16, 1024)
+                                                      : make_smem_desc_sw128(smem_base + Cfg::A_BYTES, SLAB_BYTES, 1024);
+        const uint32_t a_hi = static_cast<uint32_t>(a_desc0 >> 32), b_hi = static_cast<uint32_t>(b_desc0 >> 32);
+        const uint32_t a_lo0 = static_cast<uint32_t>(a_desc0), b_lo0 = static_cast<uint32_t>(b_desc0);
         uint32_t stage = 0, phase = 0, acc_stage = 0, acc_phase = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        bool first = true;
+        for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+            const int split = unit % p.split_k;
+            const int kb0 = split * p.kb_per_split;
+            const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
             mbar_wait(smem_u32(&tmem_empty_bar[acc_stage]), acc_phase ^ 1u);
             tc_fence_after();
             const uint32_t tmem_d = tmem_base + acc_stage * Cfg::ACC_STRIDE;
-            for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+            for (int kb = kb0; kb < kb1; ++kb) {
                 mbar_wait(smem_u32(&full_bar[stage]), phase);
                 tc_fence_after();
+                if (first) { DCAD_STAMP(2); first = false; }
                 if (lane == 0) {
-                    const uint32_t sA = smem_base + stage * Cfg::STAGE_BYTES;
-                    const uint32_t sB = sA + Cfg::A_BYTES;
+                    const uint32_t a_lo = a_lo0 + stage * (Cfg::STAGE_BYTES >> 4);
+                    const uint32_t b_lo = b_lo0 + stage * (Cfg::STAGE_BYTES >> 4);
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k) {
-                        const uint64_t adesc =
-                            (A_MAJOR == kMajorK)
-                                ? make_smem_desc_sw128(sA + k * (UMMA_K * 2), 16, 1024)
-                                : make_smem_desc_sw128(sA + k * (UMMA_K * 128), SLAB_BYTES, 1024);
-                        const uint64_t bdesc =
-                            (B_MAJOR == kMajorK)
-                                ? make_smem_desc_sw128(sB + k * (UMMA_K * 2), 16, 1024)
-                                : make_smem_desc_sw128(sB + k * (UMMA_K * 128), SLAB_BYTES, 1024);
-                        umma_bf16_ss(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                        const uint64_t adesc = (static_cast<uint64_t>(a_hi) << 32) | (a_lo + k * A_KSTEP);
+                        const uint64_t bdesc = (static_cast<uint64_t>(b_hi) << 32) | (b_lo + k * B_KSTEP);
+                        umma_bf16_ss(tmem_d, adesc, bdesc, idesc, (kb != kb0 || k != 0) ? 1u : 0u);
                     }
                     umma_commit(smem_u32(&empty_bar[stage]));  // frees the smem slot when the MMAs retire
-                    if (kb == p.num_k_blocks - 1) umma_commit(smem_u32(&tmem_full_bar[acc_stage]));
+                    if (kb == kb1 - 1) umma_commit(smem_u32(&tmem_full_bar[acc_stage]));
                 }
                 __syncwarp();
                 if (++stage == STAGES) { stage = 0; phase ^= 1u; }
             }
             if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1u; }
         }
+        DCAD_STAMP(3);
     } else if (warp >= 4) {
-        // ===================== epilogue: 8 warps.  TMEM lane quarter = warp % 4, column half = (warp - 4) / 4 =====
-        constexpr int HALF_N = BN / 2;
-        constexpr int CH = (HALF_N % 32 == 0) ? 32 : 16;
-        constexpr int NCH = HALF_N / CH;
+        // ===================== epilogue (16 warps) =====================
+        // Output leaves through [128 rows][128 B] slabs staged in 128B-swizzled smem and written by TMA: 64 bf16 or
+        // 32 fp32 columns per slab.  Warp (q, part) owns rows 32q..32q+31 and quarter `part` of every slab, so a
+        // thread converts 16 bf16 (or moves 8 fp32) columns per slab: the GELU / dGELU epilogues are ALU-bound and
+        // need all the lanes they can get.
         const uint32_t q = warp & 3u;
-        const int half = static_cast<int>(warp - 4) >> 2;
+        const int part = static_cast<int>(warp - 4) >> 2;  // 0..3
         const int ep_tid = static_cast<int>(threadIdx.x) - 128;
         const bool has_bias = (p.epi == DCAD_EPI_BIAS || p.epi == DCAD_EPI_BIAS_GELU);
-        uint32_t acc_stage = 0, acc_phase = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int r_in_tile = q * 32 + lane;
+        uint32_t acc_stage = 0, acc_phase = 0, slab_ctr = 0;
+        for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+            const int tile = unit / p.split_k;
             const int m_blk = tile % p.num_m_blocks;
             const int n_blk = tile / p.num_m_blocks;
             const int n_base = n_blk * BN;
-            const int row = m_blk * BM + q * 32 + lane;
+            const int row = m_blk * BM + r_in_tile;
             const bool row_ok = row < p.M;
-            const int col_base = n_base + half * HALF_N;
-            // stage this tile's bias while the MMAs are still running
-            if (has_bias) {
-                if (ep_tid < BN) s_bias[acc_stage][ep_tid] = (n_base + ep_tid < p.N) ? __ldg(p.bias + n_base + ep_tid) : 0.f;
-                epi_bar_sync();
+            if (has_bias) {  // stage this tile's bias while the MMAs are still running
+                if (ep_tid < BN)
+                    s_bias[acc_stage][ep_tid] = (n_base + ep_tid < p.N) ? __ldg(p.bias + n_base + ep_tid) : 0.f;
             }
-            // prefetch the first aux chunk (dGELU pre-activations)
-            uint4 aux_cur[CH / 8];
             const __nv_bfloat16* aux_row =
-                (p.epi == DCAD_EPI_DGELU && row_ok) ? p.aux + static_cast<size_t>(row) * p.ldaux + col_base : nullptr;
-            if (aux_row) {
-#pragma unroll
-                for (int j = 0; j < CH / 8; ++j)
-                    aux_cur[j] = (col_base + j * 8 < p.N) ? __ldg(reinterpret_cast<const uint4*>(aux_row) + j)
-                                                          : make_uint4(0, 0, 0, 0);
-            }
+                (p.epi == DCAD_EPI_DGELU && row_ok) ? p.aux + static_cast<size_t>(row) * p.ldaux + n_base : nullptr;
             mbar_wait(smem_u32(&tmem_full_bar[acc_stage]), acc_phase);
             tc_fence_after();
-            const uint32_t t_row = tmem_base + acc_stage * Cfg::ACC_STRIDE + ((q * 32u) << 16) + half * HALF_N;
+            if (warp == 4) DCAD_STAMP(4);
+            const uint32_t t_row = tmem_base + acc_stage * Cfg::ACC_STRIDE + ((q * 32u) << 16);
+
+            if (!p.out_fp32) {
+                // ---- bf16 output: 64-column slabs, this thread converts 16 columns per slab ----
 #pragma unroll 1
-            for (int c = 0; c < NCH; ++c) {
-                uint32_t r[CH];
-                TmemChunk<CH>::ld(t_row + c * CH, r);
-                // prefetch the next aux chunk while the TMEM load is in flight
-                uint4 aux_nxt[CH / 8];
-                if (aux_row && c + 1 < NCH) {
+                for (int s = 0; s < BN / 64; ++s) {
+                    const uint32_t buf = slab_ctr & 1u;
+                    const int c0 = s * 64 + part * 16;  // first accumulator column handled by this thread
+                    uint32_t r[16];
+                    tmem_ld_32x32b_x16(t_row + c0, r);
+                    uint4 av[2];
 #pragma unroll
-                    for (int j = 0; j < CH / 8; ++j)
-                        aux_nxt[j] = (col_base + (c + 1) * CH + j * 8 < p.N)
-                                         ? __ldg(reinterpret_cast<const uint4*>(aux_row + (c + 1) * CH) + j)
-                                         : make_uint4(0, 0, 0, 0);
-                }
-                tmem_ld_wait();
-                const int n0 = col_base + c * CH;
-                if (row_ok && n0 < p.N) {
-                    float v[CH];
+                    for (int j = 0; j < 2; ++j)
+                        av[j] = (aux_row && n_base + c0 + j * 8 < p.N)
+                                    ? __ldg(reinterpret_cast<const uint4*>(aux_row + c0) + j) : make_uint4(0, 0, 0, 0);
+                    if (ep_tid == 0) bulk_wait_group_read<1>();  // the store that last read staging[buf] is done
+                    epi_bar_sync();                               // (also publishes s_bias on the first slab)
+                    tmem_ld_wait();
+                    float v[16];
 #pragma unroll
-                    for (int j = 0; j < CH; ++j) v[j] = __uint_as_float(r[j]);
+                    for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
                     if (has_bias) {
-                        const float4* bs = reinterpret_cast<const float4*>(&s_bias[acc_stage][half * HALF_N + c * CH]);
+                        const float4* bs = reinterpret_cast<const float4*>(&s_bias[acc_stage][c0]);
 #pragma unroll
-                        for (int j = 0; j < CH; j += 4) {
+                        for (int j = 0; j < 16; j += 4) {
                             const float4 b = bs[j >> 2];
                             v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
                         }
                     }
+                    const uint32_t sD = staging_base + buf * STAGING_BYTES;
                     if (p.epi == DCAD_EPI_BIAS_GELU) {
-                        if (p.aux_out != nullptr) {
-                            __nv_bfloat16* ao = p.aux_out + static_cast<size_t>(row) * p.ldaux + n0;
+                        if (p.has_aux_out) {
+                            const uint32_t sX = staging_base + (2 + buf) * STAGING_BYTES;
 #pragma unroll
-                            for (int j = 0; j < CH; j += 8) {
-                                if (n0 + j < p.N) {
-                                    uint4 o;
-                                    o.x = pack_bf16x2(v[j], v[j + 1]); o.y = pack_bf16x2(v[j + 2], v[j + 3]);
-                                    o.z = pack_bf16x2(v[j + 4], v[j + 5]); o.w = pack_bf16x2(v[j + 6], v[j + 7]);
-                                    *reinterpret_cast<uint4*>(ao + j) = o;
-                                }
-                            }
+                            for (int j = 0; j < 2; ++j)
+                                st_shared_v4(sX + sw128_offset(r_in_tile, part * 2 + j),
+                                             pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                                             pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
                         }
 #pragma unroll
-                        for (int j = 0; j < CH; ++j) v[j] = gelu_erf(v[j]);
+                        for (int j = 0; j < 16; ++j) v[j] = gelu_erf(v[j]);
                     } else if (p.epi == DCAD_EPI_DGELU) {
 #pragma unroll
-                        for (int j = 0; j < CH; j += 8) {
-                            const uint4 a = aux_cur[j >> 3];
-                            const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y);
-                            const float2 a2 = unpack_bf16x2(a.z), a3 = unpack_bf16x2(a.w);
-                            v[j] *= dgelu_erf(a0.x); v[j + 1] *= dgelu_erf(a0.y);
-                            v[j + 2] *= dgelu_erf(a1.x); v[j + 3] *= dgelu_erf(a1.y);
-                            v[j + 4] *= dgelu_erf(a2.x); v[j + 5] *= dgelu_erf(a2.y);
-                            v[j + 6] *= dgelu_erf(a3.x); v[j + 7] *= dgelu_erf(a3.y);
+                        for (int j = 0; j < 2; ++j) {
+                            const float2 a0 = unpack_bf16x2(av[j].x), a1 = unpack_bf16x2(av[j].y);
+                            const float2 a2 = unpack_bf16x2(av[j].z), a3 = unpack_bf16x2(av[j].w);
+                            v[8 * j] *= dgelu_erf(a0.x); v[8 * j + 1] *= dgelu_erf(a0.y);
+                            v[8 * j + 2] *= dgelu_erf(a1.x); v[8 * j + 3] *= dgelu_erf(a1.y);
+                            v[8 * j + 4] *= dgelu_erf(a2.x); v[8 * j + 5] *= dgelu_erf(a2.y);
+                            v[8 * j + 6] *= dgelu_erf(a3.x); v[8 * j + 7] *= dgelu_erf(a3.y);
                         }
                     }
-                    if (p.out_fp32) {
-                        float* d = reinterpret_cast<float*>(p.D) + static_cast<size_t>(row) * p.ldd + n0;
 #pragma unroll
-                        for (int j = 0; j < CH; j += 4) {
-                            if (n0 + j < p.N) {
-                                float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-                                if (p.accumulate) {
-                                    const float4 old = *reinterpret_cast<const float4*>(d + j);
-                                    o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
-                                }
-                                *reinterpret_cast<float4*>(d + j) = o;
-                            }
+                    for (int j = 0; j < 2; ++j)
+                        st_shared_v4(sD + sw128_offset(r_in_tile, part * 2 + j),
+                                     pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                                     pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+                    fence_proxy_async_smem();
+                    epi_bar_sync();
+                    if (ep_tid == 0) {
+                        if (n_base + s * 64 < p.N) {
+                            tma_store_2d(&tmD, sD, n_base + s * 64, m_blk * BM);
+                            if (p.epi == DCAD_EPI_BIAS_GELU && p.has_aux_out)
+                                tma_store_2d(&tmAux, staging_base + (2 + buf) * STAGING_BYTES, n_base + s * 64, m_blk * BM);
                         }
-                    } else {
-                        __nv_bfloat16* d =
-                            reinterpret_cast<__nv_bfloat16*>(p.D) + static_cast<size_t>(row) * p.ldd + n0;
-#pragma unroll
-                        for (int j = 0; j < CH; j += 8) {
-                            if (n0 + j < p.N) {
-                                uint4 o;
-                                o.x = pack_bf16x2(v[j], v[j + 1]); o.y = pack_bf16x2(v[j + 2], v[j + 3]);
-                                o.z = pack_bf16x2(v[j + 4], v[j + 5]); o.w = pack_bf16x2(v[j + 6], v[j + 7]);
-                                *reinterpret_cast<uint4*>(d + j) = o;
-                            }
-                        }
+                        bulk_commit_group();
                     }
+                    ++slab_ctr;
                 }
-                if (aux_row) {
+            } else {
+                // ---- fp32 output (weight gradients): 32-column slabs, this thread moves 8 columns per slab ----
+#pragma unroll 1
+                for (int s = 0; s < BN / 32; ++s) {
+                    const uint32_t buf = slab_ctr & 1u;
+                    const int c0 = s * 32 + part * 8;
+                    uint32_t r[8];
+                    tmem_ld_32x32b_x8(t_row + c0, r);
+                    if (ep_tid == 0) bulk_wait_group_read<1>();
+                    epi_bar_sync();
+                    tmem_ld_wait();
+                    const uint32_t sD = staging_base + buf * STAGING_BYTES;
 #pragma unroll
-                    for (int j = 0; j < CH / 8; ++j) aux_cur[j] = aux_nxt[j];
+                    for (int j = 0; j < 2; ++j)
+                        st_shared_v4(sD + sw128_offset(r_in_tile, part * 2 + j), r[4 * j], r[4 * j + 1], r[4 * j + 2],
+                                     r[4 * j + 3]);
+                    fence_proxy_async_smem();
+                    epi_bar_sync();
+                    if (ep_tid == 0) {
+                        if (n_base + s * 32 < p.N) {
+                            if (p.split_k > 1) tma_reduce_add_2d(&tmD, sD, n_base + s * 32, m_blk * BM);
+                            else tma_store_2d(&tmD, sD, n_base + s * 32, m_blk * BM);
+                        }
+                        bulk_commit_group();
+                    }
+                    ++slab_ctr;
                 }
             }
             tc_fence_before();
             mbar_arrive(smem_u32(&tmem_empty_bar[acc_stage]));
+            if (warp == 4) DCAD_STAMP(5);
             if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1u; }
         }
+        if (ep_tid == 0) bulk_wait_group<0>();  // all output writes have landed before the CTA retires
     }
 
     tc_fence_before();
     __syncthreads();
+    if (warp == 0) DCAD_STAMP(6);
     if (warp == 2) {
         tc_fence_after();
         tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
@@ -344,27 +378,28 @@ static EncodeTiledFn get_encode_fn() {
 struct MapKey {
     const void* ptr;
     uint64_t rows, cols, ld;
-    uint32_t box_rows, box_cols;
+    uint32_t box_rows, box_cols, esize;
     bool operator==(const MapKey& o) const {
         return ptr == o.ptr && rows == o.rows && cols == o.cols && ld == o.ld && box_rows == o.box_rows &&
-               box_cols == o.box_cols;
+               box_cols == o.box_cols && esize == o.esize;
     }
 };
 struct MapKeyHash {
     size_t operator()(const MapKey& k) const {
         size_t h = reinterpret_cast<size_t>(k.ptr);
         h = h * 1000003u ^ k.rows; h = h * 1000003u ^ k.cols; h = h * 1000003u ^ k.ld;
-        h = h * 1000003u ^ k.box_rows; h = h * 1000003u ^ k.box_cols;
+        h = h * 1000003u ^ k.box_rows; h = h * 1000003u ^ k.box_cols; h = h * 1000003u ^ k.esize;
         return h;
     }
 };
 
-// 2D bf16 row-major [rows][ld] tensor, box = box_rows x box_cols (box_cols == 64 => 128-byte swizzle span)
-int make_tensor_map_bf16_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld,
-                            uint32_t box_rows, uint32_t box_cols) {
+// 2D row-major [rows][ld] tensor of bf16 (esize 2) or fp32 (esize 4); box = box_rows x box_cols elements with
+// box_cols * esize == 128 bytes (the 128-byte swizzle span)
+int make_tensor_map_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+                       uint32_t box_cols, uint32_t esize) {
     static std::mutex mu;
     static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
-    MapKey key{ptr, rows, cols, ld, box_rows, box_cols};
+    MapKey key{ptr, rows, cols, ld, box_rows, box_cols, esize};
     {
         std::lock_guard<std::mutex> g(mu);
         auto it = cache.find(key);
@@ -372,19 +407,24 @@ int make_tensor_map_bf16_2d(CUtensorMap* out, const void* ptr, uint64_t rows, ui
     }
     EncodeTiledFn enc = get_encode_fn();
     if (!enc) return DCAD_ERR_NO_DRIVER_ENTRY;
-    if ((reinterpret_cast<uintptr_t>(ptr) & 15u) || (ld * 2) % 16 != 0) return DCAD_ERR_BAD_ALIGNMENT;
+    if ((reinterpret_cast<uintptr_t>(ptr) & 15u) || (ld * esize) % 16 != 0) return DCAD_ERR_BAD_ALIGNMENT;
     cuuint64_t gdim[2] = {cols, rows};
-    cuuint64_t gstride[1] = {ld * 2};
+    cuuint64_t gstride[1] = {ld * esize};
     cuuint32_t box[2] = {box_cols, box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CUresult r = enc(out, esize == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                     const_cast<void*>(ptr), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return DCAD_ERR_TENSOR_MAP;
     std::lock_guard<std::mutex> g(mu);
     if (cache.size() > 4096) cache.clear();
     cache.emplace(key, *out);
     return 0;
+}
+
+int make_tensor_map_bf16_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld,
+                            uint32_t box_rows, uint32_t box_cols) {
+    return make_tensor_map_2d(out, ptr, rows, cols, ld, box_rows, box_cols, 2);
 }
 
 // 3D bf16 tensor [d2][d1][d0] (d0 contiguous), box = 1 x b1 x b0; used by the attention kernels so that rows past the
@@ -416,8 +456,8 @@ static int num_sms() {
 }
 
 template <int BN, int A_MAJOR, int B_MAJOR>
-static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int max_ctas,
-                       cudaStream_t stream) {
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmD,
+                       const CUtensorMap& tmAux, const GemmParams& p, int max_ctas, cudaStream_t stream) {
     using Cfg = GemmCfg<BN>;
     auto kern = gemm_bf16_tcgen05_kernel<BN, A_MAJOR, B_MAJOR>;
     static bool attr_set = false;
@@ -425,10 +465,10 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
         DCAD_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
         attr_set = true;
     }
-    int grid = p.num_m_blocks * p.num_n_blocks;
+    int grid = p.num_m_blocks * p.num_n_blocks * p.split_k;
     int cap = max_ctas > 0 ? max_ctas : num_sms();
     if (grid > cap) grid = cap;
-    kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, p);
+    kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, tmD, tmAux, p);
     return (int)cudaGetLastError();
 }
 
@@ -436,43 +476,60 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
 
 using namespace dcad;
 
+static unsigned long long* g_gemm_timing = nullptr;
+// profiling aid: when set, CTA 0 of every following GEMM writes 7 globaltimer stamps (ns) to this device buffer
+extern "C" void dcad_gemm_set_timing_buffer(void* dev_ptr) { g_gemm_timing = reinterpret_cast<unsigned long long*>(dev_ptr); }
+
 extern "C" int dcad_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major,
                               int lda, int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux,
-                              int epi, int out_fp32, int accumulate, int block_n, int max_ctas, void* stream) {
+                              int epi, int out_fp32, int split_k, int block_n, int max_ctas, void* stream) {
     if (M <= 0 || N <= 0 || K <= 0) return DCAD_ERR_BAD_SHAPE;
     if ((N % 8) || (ldd % 8) || (lda % 8) || (ldb % 8)) return DCAD_ERR_BAD_ALIGNMENT;
     if ((epi == DCAD_EPI_BIAS || epi == DCAD_EPI_BIAS_GELU) && bias == nullptr) return DCAD_ERR_BAD_ARGUMENT;
     if (epi == DCAD_EPI_DGELU && aux == nullptr) return DCAD_ERR_BAD_ARGUMENT;
-    if (accumulate && !out_fp32) return DCAD_ERR_BAD_ARGUMENT;
+    if (split_k < 1) split_k = 1;
+    if (split_k > 1 && (!out_fp32 || epi != DCAD_EPI_NONE)) return DCAD_ERR_BAD_ARGUMENT;
+    if (out_fp32 && epi != DCAD_EPI_NONE) return DCAD_ERR_BAD_ARGUMENT;
 
     int bn = block_n;
-    if (bn <= 0) bn = (N % 128 == 0) ? 128 : 64;
+    if (bn <= 0) bn = (N >= 256) ? 256 : (N > 128 ? 192 : (N > 64 ? 128 : 64));
 
     GemmParams p;
-    p.M = M; p.N = N; p.K = K; p.ldd = ldd; p.ldaux = ldaux > 0 ? ldaux : ldd;
+    p.M = M; p.N = N; p.K = K; p.ldaux = ldaux > 0 ? ldaux : ldd;
     p.bias = bias;
     p.aux = reinterpret_cast<const __nv_bfloat16*>(aux);
-    p.aux_out = reinterpret_cast<__nv_bfloat16*>(aux_out);
-    p.D = D; p.epi = epi; p.out_fp32 = out_fp32; p.accumulate = accumulate;
+    p.has_aux_out = (epi == DCAD_EPI_BIAS_GELU && aux_out != nullptr) ? 1 : 0;
+    p.epi = epi; p.out_fp32 = out_fp32;
     p.num_m_blocks = (M + BM - 1) / BM;
     p.num_n_blocks = (N + bn - 1) / bn;
     p.num_k_blocks = (K + BK - 1) / BK;
+    if (split_k > p.num_k_blocks) split_k = p.num_k_blocks;
+    p.kb_per_split = (p.num_k_blocks + split_k - 1) / split_k;
+    split_k = (p.num_k_blocks + p.kb_per_split - 1) / p.kb_per_split;  // no empty splits
+    p.split_k = split_k;
+    p.timing = g_gemm_timing;
 
-    CUtensorMap tmA, tmB;
+    CUtensorMap tmA, tmB, tmD, tmAux;
     int rc;
-    if (a_major == kMajorK) rc = make_tensor_map_bf16_2d(&tmA, A, M, K, lda, BM, BK);   // A stored [M][lda]
-    else                    rc = make_tensor_map_bf16_2d(&tmA, A, K, M, lda, BK, 64);   // A stored [K][lda]
+    if (a_major == kMajorK) rc = make_tensor_map_2d(&tmA, A, M, K, lda, BM, BK, 2);   // A stored [M][lda]
+    else                    rc = make_tensor_map_2d(&tmA, A, K, M, lda, BK, 64, 2);   // A stored [K][lda]
     if (rc) return rc;
-    if (b_major == kMajorK) rc = make_tensor_map_bf16_2d(&tmB, B, N, K, ldb, bn, BK);   // B stored [N][ldb]
-    else                    rc = make_tensor_map_bf16_2d(&tmB, B, K, N, ldb, BK, 64);   // B stored [K][ldb]
+    if (b_major == kMajorK) rc = make_tensor_map_2d(&tmB, B, N, K, ldb, bn, BK, 2);   // B stored [N][ldb]
+    else                    rc = make_tensor_map_2d(&tmB, B, K, N, ldb, BK, 64, 2);   // B stored [K][ldb]
     if (rc) return rc;
+    rc = out_fp32 ? make_tensor_map_2d(&tmD, D, M, N, ldd, BM, 32, 4) : make_tensor_map_2d(&tmD, D, M, N, ldd, BM, 64, 2);
+    if (rc) return rc;
+    if (p.has_aux_out) {
+        rc = make_tensor_map_2d(&tmAux, aux_out, M, N, p.ldaux, BM, 64, 2);
+        if (rc) return rc;
+    } else {
+        tmAux = tmD;
+    }
 
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
 #define DCAD_GEMM_CASE(BN_, AM_, BM_) \
-    if (bn == BN_ && a_major == AM_ && b_major == BM_) return launch_gemm<BN_, AM_, BM_>(tmA, tmB, p, max_ctas, s);
-    DCAD_GEMM_CASE(32, 0, 0)
+    if (bn == BN_ && a_major == AM_ && b_major == BM_) return launch_gemm<BN_, AM_, BM_>(tmA, tmB, tmD, tmAux, p, max_ctas, s);
     DCAD_GEMM_CASE(64, 0, 0)
-    DCAD_GEMM_CASE(96, 0, 0)
     DCAD_GEMM_CASE(128, 0, 0)
     DCAD_GEMM_CASE(192, 0, 0)
     DCAD_GEMM_CASE(256, 0, 0)

@@ -36,18 +36,21 @@ def _layer_stream(layer: int, site: int) -> int:
 
 @dataclass
 class GemmPlan:
-    """BLOCK_N per GEMM of the step (M = tokens).  Values measured on B200 with tools/tune_gemm.py."""
+    """(BLOCK_N, split_k) per GEMM of the step (M = tokens).  A tcgen05.mma of N <= 128 costs as much issue time as
+    one of N = 256 (tools/microbench_mma.py), so tiles are as wide as the problem allows and weight-gradient GEMMs,
+    whose output has few tiles, split the token (reduction) dimension instead.  Measured with tools/tune_gemm.py."""
     qkv_fwd: int = 256
-    out_fwd: int = 96
+    out_fwd: int = 128
     lin1_fwd: int = 192
-    lin2_fwd: int = 96
+    lin2_fwd: int = 256
     lin2_dgrad: int = 192   # -> [T, 3072]
-    lin1_dgrad: int = 128   # -> [T, 768]
+    lin1_dgrad: int = 256   # -> [T, 768]
     out_dgrad: int = 128
-    qkv_dgrad: int = 128
-    wgrad_wide: int = 128   # N = 768 outputs (lin1 / qkv wgrad)
-    wgrad_out: int = 64     # out_lin wgrad: 768x768 output, more (smaller) tiles fill more SMs
-    wgrad_lin2: int = 128   # N = 3072 outputs
+    qkv_dgrad: int = 256
+    wgrad_lin1: tuple = (256, 2)   # [3072, 768] <- reduce over T
+    wgrad_lin2: tuple = (256, 2)   # [768, 3072]
+    wgrad_qkv: tuple = (256, 2)    # [2304, 768]
+    wgrad_out: tuple = (128, 4)    # [768, 768]
 
 
 class B200Engine:
@@ -224,10 +227,12 @@ class B200Engine:
                     da2 if d.dropout > 0 else None, P["d_g2"][l], P["d_b2"][l], P["d_bb2"][l], p_drop=d.dropout,
                     rng=self.rng, stream_id=_layer_stream(l, 1))
             # lin2: dW2 = da2^T hmid ; dpre = (da2 W2) * gelu'(pre)
-            self._gemm(da2, hmid, P["d_w2"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_lin2)
+            self._gemm(da2, hmid, P["d_w2"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_lin2[0],
+                       split_k=pl.wgrad_lin2[1])
             self._gemm(da2, P["w2"][l], self.g_wide, b_major=MN, aux=pre, epi=nv.EPI_DGELU, block_n=pl.lin2_dgrad)
             # lin1: dW1 = dpre^T sa ; db1 = colsum(dpre) ; dsa = dpre W1
-            self._gemm(self.g_wide, sa, P["d_w1"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_wide)
+            self._gemm(self.g_wide, sa, P["d_w1"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_lin1[0],
+                       split_k=pl.wgrad_lin1[1])
             self._k(nv.colsum_bf16, self.g_wide, P["d_bb1"][l])
             dsa = self.g_b  # dy1/dy2 of this layer (g_a/g_b) are dead after the LN backward above
             self._gemm(self.g_wide, P["w1"][l], dsa, b_major=MN, block_n=pl.lin1_dgrad)
@@ -236,14 +241,16 @@ class B200Engine:
             self._k(nv.add_ln_bwd, dsa, dz2, sa, P["g1"][l], P["b1"][l], self.rstd1[l], dz1, None, P["d_g1"][l],
                     P["d_b1"][l], P["d_bo"][l])
             # out_lin: dWo = dz1^T ctx ; dctx = dz1 Wo
-            self._gemm(dz1, ctx, P["d_wo"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_out)
+            self._gemm(dz1, ctx, P["d_wo"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_out[0],
+                       split_k=pl.wgrad_out[1])
             dctx = self.g_c
             self._gemm(dz1, P["wo"][l], dctx, b_major=MN, block_n=pl.out_dgrad)
             # attention
             self._k(nv.attn_bwd, qkv, ctx, dctx, self.lse2[l], self.g_qkv, self.lens, B, S, H,
                     p_drop=d.attention_dropout, rng=self.rng, stream_id=_layer_stream(l, 0))
             # QKV: dWqkv = dqkv^T x ; dbqkv = colsum(dqkv) ; dx = dqkv Wqkv
-            self._gemm(self.g_qkv, x, P["d_wqkv"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_wide)
+            self._gemm(self.g_qkv, x, P["d_wqkv"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_qkv[0],
+                       split_k=pl.wgrad_qkv[1])
             self._k(nv.colsum_bf16, self.g_qkv, P["d_bqkv"][l])
             dxq = self.g_b
             self._gemm(self.g_qkv, P["wqkv"][l], dxq, b_major=MN, block_n=pl.qkv_dgrad)
@@ -256,7 +263,7 @@ class B200Engine:
         a = self.arena
         lay = a.layout
         self._k(nv.adam_step, a.flat, a.grad, a.exp_avg, a.exp_avg_sq, a.bf16, lay.total, 0, lay.gemm_end,
-                lay.gemm_end, lay.total, self.lr, self.betas[0], self.betas[1], self.eps, self.rng)
+                0, lay.total, self.lr, self.betas[0], self.betas[1], self.eps, self.rng)
         self._k(nv.step_advance, self.rng)
 
     # ------------------------------------------------------------------------------------------------ public API

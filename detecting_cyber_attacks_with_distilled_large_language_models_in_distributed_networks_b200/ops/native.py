@@ -110,11 +110,13 @@ def _declare(L: ctypes.CDLL) -> None:
 # --------------------------------------------------------------------------------------------------------------
 def gemm_bf16(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_major: int = MAJOR_K, b_major: int = MAJOR_K,
               bias: Optional[torch.Tensor] = None, aux: Optional[torch.Tensor] = None,
-              aux_out: Optional[torch.Tensor] = None, epi: int = EPI_NONE, accumulate: bool = False,
+              aux_out: Optional[torch.Tensor] = None, epi: int = EPI_NONE, split_k: int = 1,
               block_n: int = 0, max_ctas: int = 0, stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
     """``out[M,N] = epilogue(A·Bᵀ)`` on the tcgen05 kernel.  ``a``/``b`` are 2-D bf16 with unit inner stride.
 
     ``a`` is ``[M,K]`` (MAJOR_K) or ``[K,M]`` (MAJOR_MN); ``b`` is ``[N,K]`` (MAJOR_K) or ``[K,N]`` (MAJOR_MN).
+    ``split_k > 1`` (fp32 ``out`` only, no epilogue) splits the reduction over several CTAs that accumulate into
+    ``out`` with TMA reduce-add: ``out`` must be zero beforehand.
     """
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
     assert a.dim() == 2 and b.dim() == 2 and out.dim() == 2
@@ -144,7 +146,7 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_major: i
         assert bias.dtype == torch.float32 and bias.numel() == N
     rc = lib().dcad_gemm_bf16(a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K, a_major, b_major, a.stride(0),
                               b.stride(0), out.stride(0), ptr(bias), ptr(aux), ptr(aux_out), ldaux, epi, out_fp32,
-                              1 if accumulate else 0, block_n, max_ctas, stream_ptr(stream))
+                              split_k, block_n, max_ctas, stream_ptr(stream))
     check(rc, "dcad_gemm_bf16")
     return out
 

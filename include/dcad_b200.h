@@ -38,16 +38,20 @@ extern "C" {
 
 int dcad_version(void);
 
-/* bf16 x bf16 -> fp32-accumulated GEMM on tcgen05 tensor cores (TMA-fed, TMEM accumulators, persistent).
+/* bf16 x bf16 -> fp32-accumulated GEMM on tcgen05 tensor cores (TMA-fed, TMEM accumulators, persistent, TMA-store
+ * epilogue).
  *   D[M,N] = epilogue( sum_k A(m,k) * B(n,k) )
  * A is [M][lda] when a_major == DCAD_MAJOR_K, [K][lda] when DCAD_MAJOR_MN; likewise B with N.
- * D is bf16 (out_fp32 == 0) or fp32 (out_fp32 == 1; accumulate != 0 adds into D).
- * block_n: 0 = auto, else one of 32/64/96/128/192/256 (MN-major B: 64/128/192/256).  max_ctas: 0 = #SMs.
+ * D is bf16 (out_fp32 == 0) or fp32 (out_fp32 == 1, epilogue must be DCAD_EPI_NONE).
+ * split_k > 1 (fp32 D only): the reduction is split over several CTAs that accumulate into D with TMA reduce-add;
+ * D must be zero on entry.  block_n: 0 = auto, else 64/128/192/256.  max_ctas: 0 = #SMs.
  * Replaces the cuBLAS calls behind nn.Linear forward/backward in the reference (client1.py:61,109).
  */
 int dcad_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major, int lda,
                    int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
-                   int out_fp32, int accumulate, int block_n, int max_ctas, void* stream);
+                   int out_fp32, int split_k, int block_n, int max_ctas, void* stream);
+/* profiling aid: CTA 0 of every following GEMM writes 7 globaltimer stamps (ns) into this device buffer (NULL = off) */
+void dcad_gemm_set_timing_buffer(void* dev_ptr);
 
 /* ---- LayerNorm family (warp per row; cols must be 256/512/768/1024) ----
  * rng points at two uint64 in device memory: {seed, step}; dropout masks are a pure function of

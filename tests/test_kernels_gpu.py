@@ -30,7 +30,7 @@ def _rel(a, b):
 
 
 # ---------------------------------------------------------------- GEMM
-@pytest.mark.parametrize("a_major,b_major,bn", [(0, 0, 96), (0, 0, 256), (0, 1, 128), (1, 1, 128), (1, 1, 64)])
+@pytest.mark.parametrize("a_major,b_major,bn", [(0, 0, 64), (0, 0, 256), (0, 1, 128), (0, 1, 192), (1, 1, 128), (1, 1, 64)])
 def test_gemm_matches_matmul(nv, a_major, b_major, bn):
     torch.manual_seed(0)
     M, N, K = 384, 768, 320
@@ -42,6 +42,33 @@ def test_gemm_matches_matmul(nv, a_major, b_major, bn):
     B = b.float() if b_major == 0 else b.float().t()
     ref = A @ B.t()
     assert _rel(out, ref) < 1e-3
+
+
+def test_gemm_split_k_reduce_add(nv):
+    torch.manual_seed(11)
+    T, Nw, Kw = 2048, 768, 512      # dW[Nw, Kw] = dY[T, Nw]^T X[T, Kw]
+    dy = torch.randn(T, Nw, device="cuda").bfloat16()
+    x = torch.randn(T, Kw, device="cuda").bfloat16()
+    ref = dy.float().t() @ x.float()
+    for split in (1, 2, 5, 8):
+        out = torch.zeros(Nw, Kw, device="cuda")
+        nv.gemm_bf16(dy, x, out, a_major=nv.MAJOR_MN, b_major=nv.MAJOR_MN, block_n=256, split_k=split)
+        assert _rel(out, ref) < 1e-3, split
+
+
+def test_gemm_ragged_shapes_bf16_and_fp32(nv):
+    torch.manual_seed(12)
+    M, N, K = 200, 776, 72
+    a = torch.randn(M, K, device="cuda").bfloat16()
+    b = torch.randn(N, K, device="cuda").bfloat16()
+    for dt in (torch.bfloat16, torch.float32):
+        out = torch.full((M, N), float("nan"), device="cuda", dtype=dt)
+        nv.gemm_bf16(a, b, out, block_n=128)
+        assert _rel(out, a.float() @ b.float().t()) < (1e-2 if dt == torch.bfloat16 else 1e-3)
+    # strided output view (leading dimension larger than N)
+    big = torch.zeros(M, 1024, device="cuda", dtype=torch.bfloat16)
+    nv.gemm_bf16(a, b, big[:, 8:8 + N], block_n=256)
+    assert _rel(big[:, 8:8 + N], a.float() @ b.float().t()) < 1e-2 and torch.all(big[:, :8] == 0)
 
 
 def test_gemm_epilogues(nv):

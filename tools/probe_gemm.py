@@ -72,11 +72,11 @@ def run_group(group: str) -> dict:
         print(json.dumps(rec), flush=True)
 
     if group == "kk":
-        for bn in (32, 64, 96, 128, 192, 256):
+        for bn in (64, 128, 192, 256):
             case(256, 768, 128, 0, 0, bn, tag="small")
         case(2048, 768, 768, 0, 0, 128, tag="out_lin")
         case(2048, 2304, 768, 0, 0, 256, tag="qkv")
-        case(2048, 768, 3072, 0, 0, 96, tag="lin2")
+        case(2048, 768, 3072, 0, 0, 128, tag="lin2")
         case(200, 776, 72, 0, 0, 64, tag="ragged")
         case(16, 768, 768, 0, 0, 64, tag="tiny_m")
     elif group == "kmn":
@@ -102,7 +102,7 @@ def run_group(group: str) -> dict:
                   (768, 768, 2048, 1, 1), (3072, 768, 2048, 1, 1), (768, 3072, 2048, 1, 1), (2304, 768, 2048, 1, 1),
                   (8192, 8192, 8192, 0, 0)]
         for (M, N, K, am, bm) in shapes:
-            bns = [b for b in (64, 96, 128, 192, 256) if N % b == 0 and (bm == 0 or b % 64 == 0)]
+            bns = [b for b in (64, 128, 192, 256) if N % b == 0]
             for bn in bns:
                 a = torch.randn((M, K) if am == 0 else (K, M), device=dev).bfloat16()
                 b = torch.randn((N, K) if bm == 0 else (K, N), device=dev).bfloat16()

@@ -67,20 +67,19 @@ def main():
         B = b if bm == 0 else b.t()
         cub = time_graph(lambda: torch.matmul(A, B.t()))
         row = {"name": name, "M": M, "N": N, "K": K, "cublas_us": cub, "bn": {}}
-        for bn in (32, 64, 96, 128, 192, 256):
-            if N % bn and bn != 256:
-                continue
-            if bm == 1 and bn % 64:
-                continue
-            if bn == 32 and bm != 0:
-                continue
+        cands = [(bn, 1) for bn in (64, 128, 192, 256) if N % bn == 0]
+        if wgrad:
+            cands = [(bn, sk) for bn in (128, 256) for sk in (1, 2, 3, 4, 8)]
+        for bn, sk in cands:
             try:
+                if wgrad:
+                    out.zero_()
                 us = time_graph(lambda: nv.gemm_bf16(a, b, out, a_major=am, b_major=bm, bias=bias, aux=aux,
-                                                     aux_out=aux_out, epi=epi, block_n=bn))
-                row["bn"][bn] = us
+                                                     aux_out=aux_out, epi=epi, block_n=bn, split_k=sk))
+                row["bn"][f"{bn}/{sk}" if wgrad else bn] = us
             except Exception as e:  # noqa: BLE001
-                row["bn"][bn] = None
-                row.setdefault("errors", {})[bn] = repr(e)[:120]
+                row["bn"][f"{bn}/{sk}"] = None
+                row.setdefault("errors", {})[f"{bn}/{sk}"] = repr(e)[:120]
         ok = {k: v for k, v in row["bn"].items() if v}
         row["best_bn"] = min(ok, key=ok.get) if ok else None
         row["best_us"] = ok[row["best_bn"]] if ok else None
