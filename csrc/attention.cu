@@ -40,21 +40,27 @@ __device__ __forceinline__ void st_tile8(uint8_t* tile, int row, int j0, const f
 }
 
 // ------------------------------------------------------------------------------------------------
-// forward
+// forward.  256 threads: thread (row = tid & 127, hsel = tid >> 7) owns query `row` and keys [64*hsel, 64*hsel+64).
+// Two threads per row double the warps per scheduler: the softmax phase is a long dependent ALU chain per thread and
+// was latency-bound with one warp per scheduler.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128, 2)
+constexpr int AT_THREADS = 256;
+
+__global__ void __launch_bounds__(AT_THREADS, 2)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __restrict__ ctx,
                 float* __restrict__ lse2_out, const int32_t* __restrict__ lens, int S, int H, float scale,
                 uint32_t thresh, float keep_scale, const uint64_t* __restrict__ rng, uint32_t stream_id) {
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bar_load, bar_mma1, bar_mma2;
     __shared__ uint32_t tmem_base_smem;
+    __shared__ float s_max[2][AT_S], s_sum[2][AT_S];
 
     const int bh = blockIdx.x, b = bh / H, h = bh % H;
     const int tid = threadIdx.x, warp = tid >> 5;
+    const int row = tid & (AT_S - 1), hsel = tid >> 7;
     uint8_t* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw));
     uint8_t* sQ = smem; uint8_t* sK = smem + TILE_BYTES; uint8_t* sV = smem + 2 * TILE_BYTES;
-    uint8_t* sP = smem + 3 * TILE_BYTES;  // 2 slabs
+    uint8_t* sP = smem + 3 * TILE_BYTES;  // 2 slabs: keys 0..63 | 64..127
     const int HD = H * AT_D;
 
     if (tid == 0) {
@@ -94,40 +100,40 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
     mbar_wait(smem_u32(&bar_mma1), 0);
     tc_fence_after();
 
-    const int row = tid;
-    const uint32_t t_lane = (static_cast<uint32_t>(warp) * 32u) << 16;
-    // pass 1: row max over valid keys
+    const uint32_t t_lane = (static_cast<uint32_t>(warp & 3) * 32u) << 16;
+    const int key0 = hsel * 64;
+    // the two 32-key chunks of this thread's half stay in registers for both passes
+    uint32_t r0[32], r1[32];
+    tmem_ld_32x32b_x32(tS + t_lane + key0, r0);
+    tmem_ld_32x32b_x32(tS + t_lane + key0 + 32, r1);
+    tmem_ld_wait();
     float mx = -INFINITY;
-#pragma unroll 1
-    for (int c = 0; c < 4; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(tS + t_lane + c * 32, r);
-        tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-            if (c * 32 + j < len) mx = fmaxf(mx, __uint_as_float(r[j]));
+    for (int j = 0; j < 32; ++j) {
+        if (key0 + j < len) mx = fmaxf(mx, __uint_as_float(r0[j]));
+        if (key0 + 32 + j < len) mx = fmaxf(mx, __uint_as_float(r1[j]));
     }
-    const float m2 = mx * sc2;
-    // pass 2: p = exp2(s*sc2 - m2), row sum, dropout, write bf16 P (unnormalised) to smem
+    s_max[hsel][row] = mx;
+    __syncthreads();
+    const float m2 = fmaxf(s_max[0][row], s_max[1][row]) * sc2;  // key 0 is always valid -> finite
     float sum = 0.f;
     const uint32_t drop_base = (static_cast<uint32_t>(bh) * AT_S + row) * AT_S;
-#pragma unroll 1
-    for (int c = 0; c < 4; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(tS + t_lane + c * 32, r);
-        tmem_ld_wait();
-        float p[32];
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+        float pv[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-            const int key = c * 32 + j;
-            float e = key < len ? exp2f(__uint_as_float(r[j]) * sc2 - m2) : 0.f;
+            const int key = key0 + c * 32 + j;
+            const float sv = __uint_as_float(c == 0 ? r0[j] : r1[j]);
+            float e = key < len ? exp2f(sv * sc2 - m2) : 0.f;
             sum += e;
             if (thresh) e = dropout_keep(seed, stream_id, drop_base + key, thresh) ? e * keep_scale : 0.f;
-            p[j] = e;
+            pv[j] = e;
         }
 #pragma unroll
-        for (int j = 0; j < 32; j += 8) st_tile8(sP, row, c * 32 + j, p + j);
+        for (int j = 0; j < 32; j += 8) st_tile8(sP, row, key0 + c * 32 + j, pv + j);
     }
+    s_sum[hsel][row] = sum;
     fence_proxy_async_smem();
     tc_fence_before();
     __syncthreads();
@@ -140,17 +146,17 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
                          make_smem_desc_sw128(smem_u32(sV) + k * 2048, TILE_BYTES, 1024), idesc, k != 0);
         umma_commit(smem_u32(&bar_mma2));
     }
-    if (lse2_out && row < S) lse2_out[static_cast<size_t>(bh) * AT_S + row] = m2 + log2f(sum);
-    const float inv = 1.0f / sum;
+    const float total = s_sum[0][row] + s_sum[1][row];
+    if (hsel == 0 && lse2_out && row < S) lse2_out[static_cast<size_t>(bh) * AT_S + row] = m2 + log2f(total);
+    const float inv = 1.0f / total;
     mbar_wait(smem_u32(&bar_mma2), 0);
     tc_fence_after();
-#pragma unroll 1
-    for (int c = 0; c < 2; ++c) {
+    {
         uint32_t r[32];
-        tmem_ld_32x32b_x32(tO + t_lane + c * 32, r);
+        tmem_ld_32x32b_x32(tO + t_lane + hsel * 32, r);  // this thread stores 32 of the 64 head-dim columns
         tmem_ld_wait();
         if (row < S) {
-            __nv_bfloat16* dst = ctx + (static_cast<size_t>(b) * S + row) * HD + h * AT_D + c * 32;
+            __nv_bfloat16* dst = ctx + (static_cast<size_t>(b) * S + row) * HD + h * AT_D + hsel * 32;
 #pragma unroll
             for (int j = 0; j < 32; j += 8) {
                 uint4 o;
@@ -168,9 +174,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
 }
 
 // ------------------------------------------------------------------------------------------------
-// backward
+// backward (same thread mapping as forward)
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128, 1)
+__global__ void __launch_bounds__(AT_THREADS, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_dctx,
                 const __nv_bfloat16* __restrict__ ctx, const __nv_bfloat16* __restrict__ dctx,
                 const float* __restrict__ lse2, __nv_bfloat16* __restrict__ dqkv, const int32_t* __restrict__ lens,
@@ -182,6 +188,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
 
     const int bh = blockIdx.x, b = bh / H, h = bh % H;
     const int tid = threadIdx.x, warp = tid >> 5;
+    const int row = tid & (AT_S - 1), hsel = tid >> 7;
     uint8_t* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw));
     uint8_t* sQ = smem; uint8_t* sK = smem + TILE_BYTES; uint8_t* sV = smem + 2 * TILE_BYTES;
     uint8_t* sdO = smem + 3 * TILE_BYTES;
@@ -212,8 +219,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         tma_load_3d(smem_u32(sV), &tm_qkv, bar, 2 * HD + h * AT_D, 0, b);
         tma_load_3d(smem_u32(sdO), &tm_dctx, bar, h * AT_D, 0, b);
     }
-    const int row = tid;
-    // delta = rowsum(dO * O), from global while the TMA loads fly
+    // delta = rowsum(dO * O), from global while the TMA loads fly (both threads of a row compute it)
     float delta = 0.f;
     if (row < S) {
         const uint4* po = reinterpret_cast<const uint4*>(ctx + (static_cast<size_t>(b) * S + row) * HD + h * AT_D);
@@ -245,36 +251,37 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     const uint64_t seed = attn_seed(rng);
     const float sc2 = scale * LOG2E;
     const float l2 = (row < S) ? lse2[static_cast<size_t>(bh) * AT_S + row] : 0.f;
-    const uint32_t t_lane = (static_cast<uint32_t>(warp) * 32u) << 16;
+    const uint32_t t_lane = (static_cast<uint32_t>(warp & 3) * 32u) << 16;
     const uint32_t drop_base = (static_cast<uint32_t>(bh) * AT_S + row) * AT_S;
+    const int key0 = hsel * 64;
     mbar_wait(smem_u32(&bar_mma1), 0);
     tc_fence_after();
 #pragma unroll 1
-    for (int c = 0; c < 4; ++c) {
+    for (int c = 0; c < 2; ++c) {
         uint32_t rs[32], rp[32];
-        tmem_ld_32x32b_x32(tS + t_lane + c * 32, rs);
-        tmem_ld_32x32b_x32(tdP + t_lane + c * 32, rp);
+        tmem_ld_32x32b_x32(tS + t_lane + key0 + c * 32, rs);
+        tmem_ld_32x32b_x32(tdP + t_lane + key0 + c * 32, rp);
         tmem_ld_wait();
         float pd[32], ds[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-            const int key = c * 32 + j;
+            const int key = key0 + c * 32 + j;
             const bool valid = key < len && row < S;
-            const float p = valid ? exp2f(__uint_as_float(rs[j]) * sc2 - l2) : 0.f;
+            const float pr = valid ? exp2f(__uint_as_float(rs[j]) * sc2 - l2) : 0.f;
             float dp = __uint_as_float(rp[j]);
-            float pk = p;
+            float pk = pr;
             if (thresh) {
                 const bool keep = dropout_keep(seed, stream_id, drop_base + key, thresh);
-                pk = keep ? p * keep_scale : 0.f;
+                pk = keep ? pr * keep_scale : 0.f;
                 dp = keep ? dp * keep_scale : 0.f;
             }
             pd[j] = pk;
-            ds[j] = valid ? p * (dp - delta) * scale : 0.f;
+            ds[j] = valid ? pr * (dp - delta) * scale : 0.f;
         }
 #pragma unroll
         for (int j = 0; j < 32; j += 8) {
-            st_tile8(sP, row, c * 32 + j, pd + j);
-            st_tile8(sdS, row, c * 32 + j, ds + j);
+            st_tile8(sP, row, key0 + c * 32 + j, pd + j);
+            st_tile8(sdS, row, key0 + c * 32 + j, ds + j);
         }
     }
     fence_proxy_async_smem();
@@ -300,27 +307,24 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     }
     mbar_wait(smem_u32(&bar_mma2), 0);
     tc_fence_after();
-    // rows of dQ are queries, rows of dK/dV are keys: thread `row` writes token `row` of all three
+    // rows of dQ are queries, rows of dK/dV are keys: thread (row, hsel) writes 32 head-dim columns of token `row`
 #pragma unroll 1
     for (int which = 0; which < 3; ++which) {
         const uint32_t tsrc = which == 0 ? tdQ : (which == 1 ? tdK : tdV);
-#pragma unroll 1
-        for (int c = 0; c < 2; ++c) {
-            uint32_t r[32];
-            tmem_ld_32x32b_x32(tsrc + t_lane + c * 32, r);
-            tmem_ld_wait();
-            if (row < S) {
-                __nv_bfloat16* dst =
-                    dqkv + (static_cast<size_t>(b) * S + row) * (3 * HD) + which * HD + h * AT_D + c * 32;
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tsrc + t_lane + hsel * 32, r);
+        tmem_ld_wait();
+        if (row < S) {
+            __nv_bfloat16* dst =
+                dqkv + (static_cast<size_t>(b) * S + row) * (3 * HD) + which * HD + h * AT_D + hsel * 32;
 #pragma unroll
-                for (int j = 0; j < 32; j += 8) {
-                    uint4 o;
-                    o.x = pack_bf16x2(__uint_as_float(r[j]), __uint_as_float(r[j + 1]));
-                    o.y = pack_bf16x2(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
-                    o.z = pack_bf16x2(__uint_as_float(r[j + 4]), __uint_as_float(r[j + 5]));
-                    o.w = pack_bf16x2(__uint_as_float(r[j + 6]), __uint_as_float(r[j + 7]));
-                    *reinterpret_cast<uint4*>(dst + j) = o;
-                }
+            for (int j = 0; j < 32; j += 8) {
+                uint4 o;
+                o.x = pack_bf16x2(__uint_as_float(r[j]), __uint_as_float(r[j + 1]));
+                o.y = pack_bf16x2(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+                o.z = pack_bf16x2(__uint_as_float(r[j + 4]), __uint_as_float(r[j + 5]));
+                o.w = pack_bf16x2(__uint_as_float(r[j + 6]), __uint_as_float(r[j + 7]));
+                *reinterpret_cast<uint4*>(dst + j) = o;
             }
         }
     }
@@ -357,7 +361,7 @@ extern "C" int dcad_attn_fwd(const void* qkv, void* ctx, float* lse2, const int3
         attr = true;
     }
     const float ks = p_drop > 0.f ? 1.0f / (1.0f - p_drop) : 1.0f;
-    attn_fwd_kernel<<<B * H, 128, SMEM, reinterpret_cast<cudaStream_t>(stream)>>>(
+    attn_fwd_kernel<<<B * H, AT_THREADS, SMEM, reinterpret_cast<cudaStream_t>(stream)>>>(
         tm, reinterpret_cast<__nv_bfloat16*>(ctx), lse2, lens, S, H, 0.125f, drop_thresh_attn(p_drop), ks, rng,
         stream_id);
     return (int)cudaGetLastError();
@@ -383,7 +387,7 @@ extern "C" int dcad_attn_bwd(const void* qkv, const void* ctx, const void* dctx,
         attr = true;
     }
     const float ks = p_drop > 0.f ? 1.0f / (1.0f - p_drop) : 1.0f;
-    attn_bwd_kernel<<<B * H, 128, SMEM, reinterpret_cast<cudaStream_t>(stream)>>>(
+    attn_bwd_kernel<<<B * H, AT_THREADS, SMEM, reinterpret_cast<cudaStream_t>(stream)>>>(
         tq, td, reinterpret_cast<const __nv_bfloat16*>(ctx), reinterpret_cast<const __nv_bfloat16*>(dctx), lse2,
         reinterpret_cast<__nv_bfloat16*>(dqkv), lens, S, H, 0.125f, drop_thresh_attn(p_drop), ks, rng, stream_id);
     return (int)cudaGetLastError();
