@@ -82,28 +82,41 @@ struct VecIO<true> {  // bf16 arena, 8 elements per 16-byte access
     }
 };
 
-// average one 16-byte vector position across n clients, in client order.  Loads are issued in batches of 8
-// clients before any arithmetic so that up to 8 peer reads per thread are in flight (NVLink latency ~2 us).
-template <bool IN_BF16>
-__device__ __forceinline__ void reduce_vec(const FedArgs& a, int n, int64_t vec, float (&acc)[VecIO<IN_BF16>::ELEMS]) {
+// Average U vector positions (16 bytes each) across n clients, in client order.  All U*n loads are issued before
+// any arithmetic so that many peer reads per thread are in flight: NVLink round trips are ~2-3 us, and
+// 770 GB/s x 3 us = 2.3 MB must be outstanding per GPU to keep the links busy.
+template <bool IN_BF16, int U>
+__device__ __forceinline__ void reduce_vecs(const FedArgs& a, int n, const int64_t (&vec)[U], const bool (&ok)[U],
+                                            float (&acc)[U][VecIO<IN_BF16>::ELEMS]) {
     constexpr int E = VecIO<IN_BF16>::ELEMS;
+    constexpr int KB = (IN_BF16 ? 8 : 16) / U;  // clients per batch: at most 64 staged floats per thread
 #pragma unroll
-    for (int j = 0; j < E; ++j) acc[j] = 0.f;
-    for (int k0 = 0; k0 < n; k0 += 8) {
-        float t[8][E];
+    for (int u = 0; u < U; ++u)
 #pragma unroll
-        for (int u = 0; u < 8; ++u)
-            if (k0 + u < n) VecIO<IN_BF16>::load(a.arena[k0 + u], vec, t[u]);
+        for (int j = 0; j < E; ++j) acc[u][j] = 0.f;
+    for (int k0 = 0; k0 < n; k0 += KB) {
+        float t[U][KB][E];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            if (k0 + u < n) {
-                if (a.use_weights) {
-                    const float w = a.weight[k0 + u];
+        for (int kk = 0; kk < KB; ++kk)
 #pragma unroll
-                    for (int j = 0; j < E; ++j) acc[j] = (k0 + u == 0) ? w * t[u][j] : fmaf(w, t[u][j], acc[j]);
-                } else {
+            for (int u = 0; u < U; ++u)
+                if (k0 + kk < n && ok[u]) VecIO<IN_BF16>::load(a.arena[k0 + kk], vec[u], t[u][kk]);
 #pragma unroll
-                    for (int j = 0; j < E; ++j) acc[j] = (k0 + u == 0) ? t[u][j] : acc[j] + t[u][j];
+        for (int kk = 0; kk < KB; ++kk) {
+            if (k0 + kk < n) {
+                const float w = a.use_weights ? a.weight[k0 + kk] : 1.0f;
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    if (!ok[u]) continue;
+                    if (a.use_weights) {
+#pragma unroll
+                        for (int j = 0; j < E; ++j)
+                            acc[u][j] = (k0 + kk == 0) ? w * t[u][kk][j] : fmaf(w, t[u][kk][j], acc[u][j]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < E; ++j)
+                            acc[u][j] = (k0 + kk == 0) ? t[u][kk][j] : acc[u][j] + t[u][kk][j];
+                    }
                 }
             }
         }
@@ -111,7 +124,9 @@ __device__ __forceinline__ void reduce_vec(const FedArgs& a, int n, int64_t vec,
     if (!a.use_weights) {
         const float nf = static_cast<float>(n);
 #pragma unroll
-        for (int j = 0; j < E; ++j) acc[j] = __fdiv_rn(acc[j], nf);  // reference: base[key] /= len(models)
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+            for (int j = 0; j < E; ++j) acc[u][j] = __fdiv_rn(acc[u][j], nf);  // reference: base[key] /= len(models)
     }
 }
 
@@ -128,17 +143,27 @@ __device__ __forceinline__ void store_mirror(void* mirror, int64_t elem0, int64_
     }
 }
 
+constexpr int FED_U = 4;  // vector positions per thread per iteration
+
 // ---- local: sources readable from this GPU, single destination ----
 template <bool IN_BF16>
 __global__ void __launch_bounds__(512)
 fedavg_local_kernel(const FedArgs a, int n, int64_t num_vecs, int64_t bf16_begin, int64_t bf16_end) {
     constexpr int E = VecIO<IN_BF16>::ELEMS;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
-    for (int64_t vec = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; vec < num_vecs; vec += stride) {
-        float acc[E];
-        reduce_vec<IN_BF16>(a, n, vec, acc);
-        VecIO<IN_BF16>::store(a.out[0], vec, acc);
-        store_mirror<IN_BF16>(a.mirror[0], vec * E, bf16_begin, bf16_end, acc);
+    for (int64_t v0 = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; v0 < num_vecs; v0 += stride * FED_U) {
+        int64_t vec[FED_U];
+        bool ok[FED_U];
+#pragma unroll
+        for (int u = 0; u < FED_U; ++u) { vec[u] = v0 + u * stride; ok[u] = vec[u] < num_vecs; }
+        float acc[FED_U][E];
+        reduce_vecs<IN_BF16, FED_U>(a, n, vec, ok, acc);
+#pragma unroll
+        for (int u = 0; u < FED_U; ++u) {
+            if (!ok[u]) continue;
+            VecIO<IN_BF16>::store(a.out[0], vec[u], acc[u]);
+            store_mirror<IN_BF16>(a.mirror[0], vec[u] * E, bf16_begin, bf16_end, acc[u]);
+        }
     }
 }
 
@@ -162,17 +187,25 @@ fedavg_p2p_kernel(const FedArgs a, int rank, int n, int64_t num_vecs, int mode, 
         hi = num_vecs * (rank + 1) / n;
     }
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
-    for (int64_t vec = lo + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; vec < hi; vec += stride) {
-        float acc[E];
-        reduce_vec<IN_BF16>(a, n, vec, acc);
-        if (mode == DCAD_FED_TWO_SHOT) {
-            for (int k = 0; k < n; ++k) {
-                VecIO<IN_BF16>::store(a.arena[k], vec, acc);
-                store_mirror<IN_BF16>(a.mirror[k], vec * E, bf16_begin, bf16_end, acc);
+    for (int64_t v0 = lo + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; v0 < hi; v0 += stride * FED_U) {
+        int64_t vec[FED_U];
+        bool ok[FED_U];
+#pragma unroll
+        for (int u = 0; u < FED_U; ++u) { vec[u] = v0 + u * stride; ok[u] = vec[u] < hi; }
+        float acc[FED_U][E];
+        reduce_vecs<IN_BF16, FED_U>(a, n, vec, ok, acc);
+#pragma unroll
+        for (int u = 0; u < FED_U; ++u) {
+            if (!ok[u]) continue;
+            if (mode == DCAD_FED_TWO_SHOT) {
+                for (int k = 0; k < n; ++k) {
+                    VecIO<IN_BF16>::store(a.arena[k], vec[u], acc[u]);
+                    store_mirror<IN_BF16>(a.mirror[k], vec[u] * E, bf16_begin, bf16_end, acc[u]);
+                }
+            } else {
+                VecIO<IN_BF16>::store(a.out[rank], vec[u], acc[u]);
+                store_mirror<IN_BF16>(a.mirror[rank], vec[u] * E, bf16_begin, bf16_end, acc[u]);
             }
-        } else {
-            VecIO<IN_BF16>::store(a.out[rank], vec, acc);
-            store_mirror<IN_BF16>(a.mirror[rank], vec * E, bf16_begin, bf16_end, acc);
         }
     }
     // end barrier: the last block of this rank tells every peer its pushes are visible, then waits for theirs

@@ -1,0 +1,78 @@
+"""Multi-GPU tests of the peer-memory FedAvg kernels (need >= 2 visible B200s: `gpurun --gpus 2 -- pytest -m gpu`).
+Skipped on a single-GPU box."""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+PKG = "detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200"
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _need(n):
+    if not torch.cuda.is_available() or torch.cuda.device_count() < n:
+        pytest.skip(f"needs {n} GPUs")
+
+
+def _reference_mean(arenas):
+    base = arenas[0].cpu().clone()
+    for a in arenas[1:]:
+        base += a.cpu()
+    base /= len(arenas)
+    return base
+
+
+@pytest.mark.parametrize("mode", ["two_shot", "one_shot"])
+def test_local_peer_group_fedavg_matches_reference(mode):
+    _need(2)
+    from importlib import import_module
+
+    p2p = import_module(f"{PKG}.parallel.p2p")
+    n = torch.cuda.device_count() if torch.cuda.device_count() in (2, 4, 8) else 2
+    elems, mirror = 1 << 22, 1 << 21
+    grp = p2p.LocalPeerGroup(list(range(n)), elems, mirror, with_out_buffer=(mode == "one_shot"))
+    try:
+        srcs = []
+        for r in range(n):
+            with torch.cuda.device(r):
+                t = grp.arena_tensor(r)
+                t.copy_(torch.randn(elems, device=f"cuda:{r}", generator=torch.Generator(f"cuda:{r}").manual_seed(r)))
+                srcs.append(t.clone())
+        for r in range(n):
+            torch.cuda.synchronize(r)
+        expect = _reference_mean(srcs)
+        for rep in range(2):  # epochs must be reusable
+            if rep == 1:
+                for r in range(n):
+                    with torch.cuda.device(r):
+                        grp.arena_tensor(r).copy_(srcs[r])
+                        torch.cuda.synchronize(r)
+            grp.fedavg_all(p2p.TWO_SHOT if mode == "two_shot" else p2p.ONE_SHOT)
+            for r in range(n):
+                torch.cuda.synchronize(r)
+            for r in range(n):
+                with torch.cuda.device(r):
+                    got = grp.arena_tensor(r) if mode == "two_shot" else grp.out_tensor(r)
+                    assert torch.equal(got.cpu(), expect), (mode, r, rep)   # bit parity with server.py:72-76
+                    assert torch.equal(grp.mirror_tensor(r).cpu(), expect[:mirror].bfloat16())
+                    pad = grp.pad_bufs[r].view(torch.int32, numel=64)
+                    assert int(pad[33].item()) == 0  # no handshake timeout
+    finally:
+        grp.close()
+
+
+def test_multiprocess_ipc_fedavg_and_bench():
+    """One process per GPU (torchrun), arenas exchanged as CUDA IPC handles, FedAvg through bench.py's code path."""
+    _need(2)
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", str(29800 + os.getpid() % 100), os.path.join(ROOT, "tools", "mp_fedavg_check.py")]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-3000:])
+    assert "FEDAVG_IPC_OK" in r.stdout
