@@ -19,6 +19,9 @@ import os
 import sys
 import time
 
+# keep stdout clean for the ONE JSON line: NCCL's banner / debug output goes to stderr
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
