@@ -41,6 +41,7 @@ struct GemmParams {
     int epi;
     int out_fp32;
     int split_k;               // > 1: fp32 output accumulated with TMA reduce-add (output must be zero-initialised)
+    int ws_row_stride;         // > 0: workspace mode, split s stores its fp32 partial tile at row s*ws_row_stride + m
     int num_m_blocks, num_n_blocks, num_k_blocks, kb_per_split;
     unsigned long long* timing;  // optional: per-role globaltimer stamps of CTA 0 (profiling aid), else null
 };
@@ -230,6 +231,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             const int m_blk = tile % p.num_m_blocks;
             const int n_blk = tile / p.num_m_blocks;
             const int n_base = n_blk * BN;
+            const int out_row0 = (unit % p.split_k) * p.ws_row_stride + m_blk * BM;  // ws_row_stride == 0 unless workspace mode
             const int row = m_blk * BM + r_in_tile;
             const bool row_ok = row < p.M;
             if (has_bias) {  // stage this tile's bias while the MMAs are still running
@@ -330,8 +332,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                     epi_bar_sync();
                     if (ep_tid == 0) {
                         if (n_base + s * 32 < p.N) {
-                            if (p.split_k > 1) tma_reduce_add_2d(&tmD, sD, n_base + s * 32, m_blk * BM);
-                            else tma_store_2d(&tmD, sD, n_base + s * 32, m_blk * BM);
+                            if (p.split_k > 1 && p.ws_row_stride == 0) tma_reduce_add_2d(&tmD, sD, n_base + s * 32, out_row0);
+                            else tma_store_2d(&tmD, sD, n_base + s * 32, out_row0);
                         }
                         bulk_commit_group();
                     }
@@ -480,9 +482,11 @@ static unsigned long long* g_gemm_timing = nullptr;
 // profiling aid: when set, CTA 0 of every following GEMM writes 7 globaltimer stamps (ns) to this device buffer
 extern "C" void dcad_gemm_set_timing_buffer(void* dev_ptr) { g_gemm_timing = reinterpret_cast<unsigned long long*>(dev_ptr); }
 
-extern "C" int dcad_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major,
-                              int lda, int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux,
-                              int epi, int out_fp32, int split_k, int block_n, int max_ctas, void* stream) {
+// ws_row_stride > 0: D is an fp32 workspace of split_k row-slices of ws_row_stride rows each (plain stores);
+// ws_row_stride == 0 with split_k > 1: D is the fp32 result, accumulated with TMA reduce-add.
+static int gemm_dispatch(const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major, int lda,
+                         int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
+                         int out_fp32, int split_k, int ws_row_stride, int block_n, int max_ctas, cudaStream_t s) {
     if (M <= 0 || N <= 0 || K <= 0) return DCAD_ERR_BAD_SHAPE;
     if ((N % 8) || (ldd % 8) || (lda % 8) || (ldb % 8)) return DCAD_ERR_BAD_ALIGNMENT;
     if ((epi == DCAD_EPI_BIAS || epi == DCAD_EPI_BIAS_GELU) && bias == nullptr) return DCAD_ERR_BAD_ARGUMENT;
@@ -507,6 +511,7 @@ extern "C" int dcad_gemm_bf16(const void* A, const void* B, void* D, int M, int 
     p.kb_per_split = (p.num_k_blocks + split_k - 1) / split_k;
     split_k = (p.num_k_blocks + p.kb_per_split - 1) / p.kb_per_split;  // no empty splits
     p.split_k = split_k;
+    p.ws_row_stride = ws_row_stride;
     p.timing = g_gemm_timing;
 
     CUtensorMap tmA, tmB, tmD, tmAux;
@@ -517,7 +522,8 @@ extern "C" int dcad_gemm_bf16(const void* A, const void* B, void* D, int M, int 
     if (b_major == kMajorK) rc = make_tensor_map_2d(&tmB, B, N, K, ldb, bn, BK, 2);   // B stored [N][ldb]
     else                    rc = make_tensor_map_2d(&tmB, B, K, N, ldb, BK, 64, 2);   // B stored [K][ldb]
     if (rc) return rc;
-    rc = out_fp32 ? make_tensor_map_2d(&tmD, D, M, N, ldd, BM, 32, 4) : make_tensor_map_2d(&tmD, D, M, N, ldd, BM, 64, 2);
+    const uint64_t d_rows = ws_row_stride > 0 ? static_cast<uint64_t>(ws_row_stride) * split_k : static_cast<uint64_t>(M);
+    rc = out_fp32 ? make_tensor_map_2d(&tmD, D, d_rows, N, ldd, BM, 32, 4) : make_tensor_map_2d(&tmD, D, d_rows, N, ldd, BM, 64, 2);
     if (rc) return rc;
     if (p.has_aux_out) {
         rc = make_tensor_map_2d(&tmAux, aux_out, M, N, p.ldaux, BM, 64, 2);
@@ -526,7 +532,6 @@ extern "C" int dcad_gemm_bf16(const void* A, const void* B, void* D, int M, int 
         tmAux = tmD;
     }
 
-    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
 #define DCAD_GEMM_CASE(BN_, AM_, BM_) \
     if (bn == BN_ && a_major == AM_ && b_major == BM_) return launch_gemm<BN_, AM_, BM_>(tmA, tmB, tmD, tmAux, p, max_ctas, s);
     DCAD_GEMM_CASE(64, 0, 0)
@@ -543,4 +548,111 @@ extern "C" int dcad_gemm_bf16(const void* A, const void* B, void* D, int M, int 
     DCAD_GEMM_CASE(256, 1, 1)
 #undef DCAD_GEMM_CASE
     return DCAD_ERR_UNSUPPORTED_TILE;
+}
+
+extern "C" int dcad_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major,
+                              int lda, int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux,
+                              int epi, int out_fp32, int split_k, int block_n, int max_ctas, void* stream) {
+    return gemm_dispatch(A, B, D, M, N, K, a_major, b_major, lda, ldb, ldd, bias, aux, aux_out, ldaux, epi, out_fp32,
+                         split_k, 0, block_n, max_ctas, reinterpret_cast<cudaStream_t>(stream));
+}
+
+// ------------------------------------------------------------------------------------------------
+// Split-K with an fp32 workspace, for bf16-output GEMMs whose output has too few tiles for 148 SMs but whose
+// reduction is long (FFN lin2 forward and lin1 dgrad: 2048 x 768 output, K = 3072).  Pass 1: the tcgen05 GEMM with
+// the reduction cut into split_k slices, each slice storing its fp32 partial tile into its own row-slice of the
+// workspace (no atomics, no ordering between slices).  Pass 2: one elementwise kernel sums the slices in slice order
+// (deterministic), applies the epilogue and writes bf16.
+// ------------------------------------------------------------------------------------------------
+namespace dcad {
+
+__global__ void __launch_bounds__(256)
+splitk_reduce_kernel(const float* __restrict__ ws, int splits, int64_t slice_elems, int M, int N,
+                     const float* __restrict__ bias, const __nv_bfloat16* __restrict__ aux, int ldaux,
+                     __nv_bfloat16* __restrict__ aux_out, __nv_bfloat16* __restrict__ D, int ldd, int epi) {
+    const int vec_per_row = N >> 3;
+    const int64_t total = static_cast<int64_t>(M) * vec_per_row;
+    for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int row = static_cast<int>(i / vec_per_row);
+        const int col = static_cast<int>(i % vec_per_row) << 3;
+        const float* src = ws + static_cast<int64_t>(row) * N + col;
+        float v[8];
+        {
+            const float4 a = *reinterpret_cast<const float4*>(src);
+            const float4 b = *reinterpret_cast<const float4*>(src + 4);
+            v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+        }
+        for (int s = 1; s < splits; ++s) {
+            const float4 a = *reinterpret_cast<const float4*>(src + s * slice_elems);
+            const float4 b = *reinterpret_cast<const float4*>(src + s * slice_elems + 4);
+            v[0] += a.x; v[1] += a.y; v[2] += a.z; v[3] += a.w; v[4] += b.x; v[5] += b.y; v[6] += b.z; v[7] += b.w;
+        }
+        if (epi == DCAD_EPI_BIAS || epi == DCAD_EPI_BIAS_GELU) {
+            const float4 a = __ldg(reinterpret_cast<const float4*>(bias + col));
+            const float4 b = __ldg(reinterpret_cast<const float4*>(bias + col + 4));
+            v[0] += a.x; v[1] += a.y; v[2] += a.z; v[3] += a.w; v[4] += b.x; v[5] += b.y; v[6] += b.z; v[7] += b.w;
+        }
+        if (epi == DCAD_EPI_BIAS_GELU) {
+            if (aux_out) {
+                uint4 o;
+                o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
+                o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+                *reinterpret_cast<uint4*>(aux_out + static_cast<int64_t>(row) * ldaux + col) = o;
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = gelu_erf(v[j]);
+        } else if (epi == DCAD_EPI_DGELU) {
+            const uint4 a = __ldg(reinterpret_cast<const uint4*>(aux + static_cast<int64_t>(row) * ldaux + col));
+            const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), a2 = unpack_bf16x2(a.z), a3 = unpack_bf16x2(a.w);
+            v[0] *= dgelu_erf(a0.x); v[1] *= dgelu_erf(a0.y); v[2] *= dgelu_erf(a1.x); v[3] *= dgelu_erf(a1.y);
+            v[4] *= dgelu_erf(a2.x); v[5] *= dgelu_erf(a2.y); v[6] *= dgelu_erf(a3.x); v[7] *= dgelu_erf(a3.y);
+        }
+        uint4 o;
+        o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
+        o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+        *reinterpret_cast<uint4*>(D + static_cast<int64_t>(row) * ldd + col) = o;
+    }
+}
+
+// shared by the workspace entry points: pass 1 + pass 2 on `ws` (device memory, >= dcad_gemm_splitk_workspace_bytes)
+static int gemm_splitk_run(const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major,
+                           int lda, int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux,
+                           int epi, int split_k, int block_n, int max_ctas, float* ws, cudaStream_t s) {
+    const int m_pad = (M + BM - 1) / BM * BM;
+    int rc = gemm_dispatch(A, B, ws, M, N, K, a_major, b_major, lda, ldb, N, nullptr, nullptr, nullptr, 0, DCAD_EPI_NONE, 1,
+                           split_k, m_pad, block_n, max_ctas, s);
+    if (rc) return rc;
+    int kb = (K + BK - 1) / BK;
+    int sk = split_k > kb ? kb : split_k;
+    const int per = (kb + sk - 1) / sk;
+    sk = (kb + per - 1) / per;  // the split count the GEMM actually used
+    const int64_t total = static_cast<int64_t>(M) * (N >> 3);
+    int blocks = static_cast<int>((total + 255) / 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    splitk_reduce_kernel<<<blocks, 256, 0, s>>>(ws, sk, static_cast<int64_t>(m_pad) * N, M, N, bias,
+                                                reinterpret_cast<const __nv_bfloat16*>(aux), ldaux > 0 ? ldaux : ldd,
+                                                reinterpret_cast<__nv_bfloat16*>(aux_out),
+                                                reinterpret_cast<__nv_bfloat16*>(D), ldd, epi);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace dcad
+
+extern "C" size_t dcad_gemm_splitk_workspace_bytes(int M, int N, int split_k) {
+    const size_t m_pad = static_cast<size_t>((M + BM - 1) / BM * BM);
+    return m_pad * static_cast<size_t>(N) * static_cast<size_t>(split_k < 1 ? 1 : split_k) * sizeof(float);
+}
+
+extern "C" int dcad_gemm_bf16_splitk(const void* A, const void* B, void* D, int M, int N, int K, int a_major,
+                                     int b_major, int lda, int ldb, int ldd, const float* bias, const void* aux,
+                                     void* aux_out, int ldaux, int epi, int split_k, int block_n, int max_ctas,
+                                     void* workspace, size_t workspace_bytes, void* stream) {
+    if (split_k < 2) return DCAD_ERR_BAD_ARGUMENT;
+    if (workspace == nullptr || (reinterpret_cast<uintptr_t>(workspace) & 255u)) return DCAD_ERR_BAD_ALIGNMENT;
+    if ((epi == DCAD_EPI_BIAS || epi == DCAD_EPI_BIAS_GELU) && bias == nullptr) return DCAD_ERR_BAD_ARGUMENT;
+    if (epi == DCAD_EPI_DGELU && aux == nullptr) return DCAD_ERR_BAD_ARGUMENT;
+    if (workspace_bytes < dcad_gemm_splitk_workspace_bytes(M, N, split_k)) return DCAD_ERR_TOO_LARGE;
+    return gemm_splitk_run(A, B, D, M, N, K, a_major, b_major, lda, ldb, ldd, bias, aux, aux_out, ldaux, epi, split_k,
+                           block_n, max_ctas, reinterpret_cast<float*>(workspace), reinterpret_cast<cudaStream_t>(stream));
 }

@@ -42,9 +42,9 @@ class GemmPlan:
     qkv_fwd: int = 256
     out_fwd: int = 128
     lin1_fwd: int = 192
-    lin2_fwd: int = 256
+    lin2_fwd: tuple = (256, 3)     # (BLOCK_N, split_k): K = 3072, only 48 output tiles -> workspace split-K
     lin2_dgrad: int = 192   # -> [T, 3072]
-    lin1_dgrad: int = 256   # -> [T, 768]
+    lin1_dgrad: tuple = (256, 3)   # -> [T, 768], K = 3072
     out_dgrad: int = 128
     qkv_dgrad: int = 256
     wgrad_lin1: tuple = (256, 2)   # [3072, 768] <- reduce over T
@@ -112,6 +112,9 @@ class B200Engine:
         self.g_qkv = torch.empty(T, 3 * D, **bf)
         self.dcls = torch.empty(batch, D, **bf)
         self.logits = torch.empty(batch, dims.n_classes, **f32)
+        # scratch for the split-K GEMMs (fp32 partial tiles), sized for the larger of the two users
+        sk = max(self.plan.lin2_fwd[1], self.plan.lin1_dgrad[1], 2)
+        self.splitk_ws = torch.empty(nv.gemm_splitk_workspace_bytes(T, D, sk) // 4, **f32)
         # device-side accumulators
         self.loss_accum = torch.zeros(2, **f32)                       # {sum of batch-mean losses, #batches}
         self.eval_loss_accum = torch.zeros(2, **f32)
@@ -177,6 +180,14 @@ class B200Engine:
         self._n_launch += 1
         return nv.gemm_bf16(*args, **kw)
 
+    def _gemm_splitk(self, a, b, out, cfg, **kw):
+        """(BLOCK_N, split_k) GEMM: plain persistent GEMM when split_k == 1, else two launches through the workspace."""
+        bn, sk = cfg
+        if sk <= 1:
+            return self._gemm(a, b, out, block_n=bn, **kw)
+        self._n_launch += 2
+        return nv.gemm_bf16_splitk(a, b, out, self.splitk_ws, split_k=sk, block_n=bn, **kw)
+
     def _k(self, fn, *args, **kw):
         self._n_launch += 1
         return fn(*args, **kw)
@@ -204,7 +215,7 @@ class B200Engine:
             self._k(nv.add_ln_fwd, tmp, x, self.p["g1"][l], self.p["b1"][l], sa, self.rstd1[l][:T], eps=d.ln_eps)
             self._gemm(sa, self.p["w1"][l], hmid, bias=self.p["bb1"][l], aux_out=pre if train else None,
                        epi=nv.EPI_BIAS_GELU, block_n=pl.lin1_fwd)
-            self._gemm(hmid, self.p["w2"][l], tmp, bias=self.p["bb2"][l], epi=nv.EPI_BIAS, block_n=pl.lin2_fwd)
+            self._gemm_splitk(hmid, self.p["w2"][l], tmp, pl.lin2_fwd, bias=self.p["bb2"][l], epi=nv.EPI_BIAS)
             self._k(nv.add_ln_fwd, tmp, sa, self.p["g2"][l], self.p["b2"][l], self.x[l + 1][:T], self.rstd2[l][:T],
                     eps=d.ln_eps, p_drop=p_h, rng=rng, stream_id=_layer_stream(l, 1))
         return self.x[d.n_layers][:T]
@@ -235,7 +246,7 @@ class B200Engine:
                        split_k=pl.wgrad_lin1[1])
             self._k(nv.colsum_bf16, self.g_wide, P["d_bb1"][l])
             dsa = self.g_b  # dy1/dy2 of this layer (g_a/g_b) are dead after the LN backward above
-            self._gemm(self.g_wide, P["w1"][l], dsa, b_major=MN, block_n=pl.lin1_dgrad)
+            self._gemm_splitk(self.g_wide, P["w1"][l], dsa, pl.lin1_dgrad, b_major=MN)
             # sa_layer_norm(attn_out + x): dz1 is the gradient wrt both attn_out and the residual x
             dz1 = self.g_a
             self._k(nv.add_ln_bwd, dsa, dz2, sa, P["g1"][l], P["b1"][l], self.rstd1[l], dz1, None, P["d_g1"][l],

@@ -80,6 +80,8 @@ def _declare(L: ctypes.CDLL) -> None:
     P, I, F, L64, U32 = c_void_p, c_int, c_float, c_int64, c_uint32
     sig("dcad_version", [])
     sig("dcad_gemm_bf16", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, I, I, P])
+    sig("dcad_gemm_splitk_workspace_bytes", [I, I, I], ctypes.c_size_t)
+    sig("dcad_gemm_bf16_splitk", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, I, P, ctypes.c_size_t, P])
     sig("dcad_add_ln_fwd", [P, P, P, P, P, P, I, I, F, F, P, U32, P])
     sig("dcad_add_ln_bwd", [P, P, P, P, P, P, P, P, P, P, P, I, I, F, P, U32, P])
     sig("dcad_embed_ln_fwd", [P, P, P, P, P, P, P, P, I, I, I, F, F, P, U32, P])
@@ -148,6 +150,33 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_major: i
                               b.stride(0), out.stride(0), ptr(bias), ptr(aux), ptr(aux_out), ldaux, epi, out_fp32,
                               split_k, block_n, max_ctas, stream_ptr(stream))
     check(rc, "dcad_gemm_bf16")
+    return out
+
+
+def gemm_splitk_workspace_bytes(M: int, N: int, split_k: int) -> int:
+    return int(lib().dcad_gemm_splitk_workspace_bytes(M, N, split_k))
+
+
+def gemm_bf16_splitk(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, workspace: torch.Tensor, *, split_k: int,
+                     a_major: int = MAJOR_K, b_major: int = MAJOR_K, bias: Optional[torch.Tensor] = None,
+                     aux: Optional[torch.Tensor] = None, aux_out: Optional[torch.Tensor] = None, epi: int = EPI_NONE,
+                     block_n: int = 0, max_ctas: int = 0, stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
+    """bf16-output GEMM with the reduction split over ``split_k`` CTAs per tile; ``workspace`` is caller-owned scratch
+    (any dtype, >= ``gemm_splitk_workspace_bytes(M, N, split_k)`` bytes, 256-byte aligned)."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and out.dtype == torch.bfloat16
+    assert a.stride(1) == 1 and b.stride(1) == 1 and out.stride(1) == 1
+    M, N = out.shape
+    K = a.shape[1] if a_major == MAJOR_K else a.shape[0]
+    ldaux = 0
+    if aux is not None:
+        ldaux = aux.stride(0)
+    if aux_out is not None:
+        ldaux = aux_out.stride(0)
+    rc = lib().dcad_gemm_bf16_splitk(a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K, a_major, b_major, a.stride(0),
+                                     b.stride(0), out.stride(0), ptr(bias), ptr(aux), ptr(aux_out), ldaux, epi, split_k,
+                                     block_n, max_ctas, workspace.data_ptr(), workspace.numel() * workspace.element_size(),
+                                     stream_ptr(stream))
+    check(rc, "dcad_gemm_bf16_splitk")
     return out
 
 

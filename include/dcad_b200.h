@@ -50,6 +50,16 @@ int dcad_version(void);
 int dcad_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major, int lda,
                    int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
                    int out_fp32, int split_k, int block_n, int max_ctas, void* stream);
+/* Split-K for bf16-output GEMMs with a long reduction and few output tiles (FFN lin2 forward / lin1 dgrad).  The
+ * reduction is cut into split_k slices; every slice writes its fp32 partial tile to `workspace` (scratch, contents
+ * undefined on return), then a second kernel sums the slices in order, applies the epilogue and writes bf16 D.
+ * workspace: device memory, 256-byte aligned, at least dcad_gemm_splitk_workspace_bytes(M, N, split_k) bytes
+ * (ceil(M/128)*128 * N * split_k * 4); too small -> DCAD_ERR_TOO_LARGE.  split_k >= 2. */
+size_t dcad_gemm_splitk_workspace_bytes(int M, int N, int split_k);
+int dcad_gemm_bf16_splitk(const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major, int lda,
+                          int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
+                          int split_k, int block_n, int max_ctas, void* workspace, size_t workspace_bytes,
+                          void* stream);
 /* profiling aid: CTA 0 of every following GEMM writes 7 globaltimer stamps (ns) into this device buffer (NULL = off) */
 void dcad_gemm_set_timing_buffer(void* dev_ptr);
 

@@ -56,6 +56,45 @@ def test_gemm_split_k_reduce_add(nv):
         assert _rel(out, ref) < 1e-3, split
 
 
+@pytest.mark.parametrize("epi", ["bias", "gelu", "dgelu", "none"])
+def test_gemm_splitk_workspace(nv, epi):
+    """Two-pass split-K (fp32 partial tiles in a scratch workspace, then an ordered reduce + epilogue)."""
+    torch.manual_seed(13)
+    M, N, K = 520, 768, 1536      # M not a multiple of the 128-row tile
+    a = torch.randn(M, K, device="cuda").bfloat16()
+    w = (torch.randn(N, K, device="cuda") * 0.05).bfloat16()
+    bias = torch.randn(N, device="cuda")
+    aux = torch.randn(M, N, device="cuda").bfloat16()
+    ref = a.float() @ w.float().t()
+    kw = {}
+    if epi in ("bias", "gelu"):
+        ref = ref + bias
+        kw["bias"] = bias
+    pre = ref
+    if epi == "gelu":
+        ref = F.gelu(pre)
+        kw["aux_out"] = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    if epi == "dgelu":
+        x = aux.float().requires_grad_(True)
+        F.gelu(x).backward(torch.ones_like(x))
+        ref = ref * x.grad
+        kw["aux"] = aux
+    code = {"none": nv.EPI_NONE, "bias": nv.EPI_BIAS, "gelu": nv.EPI_BIAS_GELU, "dgelu": nv.EPI_DGELU}[epi]
+    for split in (2, 3, 4):
+        ws = torch.empty(nv.gemm_splitk_workspace_bytes(M, N, split) // 4, device="cuda")
+        out = torch.full((M, N), float("nan"), device="cuda", dtype=torch.bfloat16)
+        nv.gemm_bf16_splitk(a, w, out, ws, split_k=split, epi=code, block_n=256, **kw)
+        assert _rel(out, ref) < 1e-2, (epi, split)
+        if epi == "gelu":
+            assert _rel(kw["aux_out"], pre) < 1e-2
+    # same result as the single-pass kernel up to bf16 rounding, and a too-small workspace is refused
+    one = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    nv.gemm_bf16(a, w, one, block_n=256, epi=code, **{k: v for k, v in kw.items()})
+    assert _rel(out, one) < 1e-2
+    with pytest.raises(nv.NativeError):
+        nv.gemm_bf16_splitk(a, w, out, torch.empty(1024, device="cuda"), split_k=2, epi=code, **kw)
+
+
 def test_gemm_ragged_shapes_bf16_and_fp32(nv):
     torch.manual_seed(12)
     M, N, K = 200, 776, 72

@@ -80,6 +80,15 @@ def main():
             except Exception as e:  # noqa: BLE001
                 row["bn"][f"{bn}/{sk}"] = None
                 row.setdefault("errors", {})[f"{bn}/{sk}"] = repr(e)[:120]
+        if name in ("lin2_fwd", "lin1_dgrad", "out_fwd", "out_dgrad"):
+            for bn, sk in ((256, 2), (256, 3), (256, 4), (128, 2), (128, 3)):
+                ws = torch.empty(nv.gemm_splitk_workspace_bytes(M, N, sk) // 4, device=dev)
+                try:
+                    us = time_graph(lambda: nv.gemm_bf16_splitk(a, b, out, ws, split_k=sk, a_major=am, b_major=bm,
+                                                                bias=bias, aux=aux, aux_out=aux_out, epi=epi, block_n=bn))
+                    row["bn"][f"ws{bn}/{sk}"] = us
+                except Exception as e:  # noqa: BLE001
+                    row["bn"][f"ws{bn}/{sk}"] = None
         ok = {k: v for k, v in row["bn"].items() if v}
         row["best_bn"] = min(ok, key=ok.get) if ok else None
         row["best_us"] = ok[row["best_bn"]] if ok else None
