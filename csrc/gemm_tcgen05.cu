@@ -397,12 +397,15 @@ struct MapKeyHash {
 
 // 2D row-major [rows][ld] tensor of bf16 (esize 2) or fp32 (esize 4); box = box_rows x box_cols elements with
 // box_cols * esize == 128 bytes (the 128-byte swizzle span)
+static thread_local bool t_tensor_map_cache_enabled = true;  // off => maps are encoded on the stack, no host heap use
+
 int make_tensor_map_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
                        uint32_t box_cols, uint32_t esize) {
     static std::mutex mu;
     static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
     MapKey key{ptr, rows, cols, ld, box_rows, box_cols, esize};
-    {
+    const bool use_cache = t_tensor_map_cache_enabled;
+    if (use_cache) {
         std::lock_guard<std::mutex> g(mu);
         auto it = cache.find(key);
         if (it != cache.end()) { *out = it->second; return 0; }
@@ -418,6 +421,7 @@ int make_tensor_map_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_
                      const_cast<void*>(ptr), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return DCAD_ERR_TENSOR_MAP;
+    if (!use_cache) return 0;
     std::lock_guard<std::mutex> g(mu);
     if (cache.size() > 4096) cache.clear();
     cache.emplace(key, *out);
@@ -655,4 +659,64 @@ extern "C" int dcad_gemm_bf16_splitk(const void* A, const void* B, void* D, int 
     if (workspace_bytes < dcad_gemm_splitk_workspace_bytes(M, N, split_k)) return DCAD_ERR_TOO_LARGE;
     return gemm_splitk_run(A, B, D, M, N, K, a_major, b_major, lda, ldb, ldd, bias, aux, aux_out, ldaux, epi, split_k,
                            block_n, max_ctas, reinterpret_cast<float*>(workspace), reinterpret_cast<cudaStream_t>(stream));
+}
+
+// ------------------------------------------------------------------------------------------------
+// Split-K GEMM for hosts that cannot hand over a workspace.
+//
+// dcad_gemm_bf16_splitk needs fp32 scratch that somebody must have allocated.  Not every host can: a runtime that
+// issues this GEMM while its stream is being captured into a CUDA graph, an inference server whose device memory pool
+// is carved up once at start-up and then frozen, a plug-in running inside an application that forbids cudaMalloc
+// after initialisation because an allocation stalls every stream on the device.  For them the scratch is part of the
+// library image: one fixed region per GPU that has loaded the library, kept until the process exits.  The call below
+// allocates and frees nothing on the device or the host (tensor maps are encoded on the stack, the map cache is
+// bypassed) and calls no allocating library routine.
+//
+// g_splitk_static_ws is a DEVICE object.  Host code may not pass its name to a kernel: the usable address is
+// obtained with cudaGetSymbolAddress, once per GPU, while that GPU is current, and cached.
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_splitk_static_ws[DCAD_SPLITK_STATIC_BYTES];
+
+namespace {
+constexpr int kMaxDevicesForStaticWs = 64;
+float* g_static_ws_ptr[kMaxDevicesForStaticWs] = {};
+
+// device address of the CURRENT GPU's built-in workspace; the first call on a GPU resolves and caches it
+int static_workspace(float** out) {
+    int dev = -1;
+    DCAD_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevicesForStaticWs) return DCAD_ERR_BAD_ARGUMENT;
+    if (g_static_ws_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        DCAD_CUDA_TRY(cudaGetSymbolAddress(&p, g_splitk_static_ws));
+        g_static_ws_ptr[dev] = reinterpret_cast<float*>(p);
+    }
+    *out = g_static_ws_ptr[dev];
+    return 0;
+}
+}  // namespace
+
+extern "C" size_t dcad_gemm_splitk_static_capacity(void) { return DCAD_SPLITK_STATIC_BYTES; }
+
+extern "C" int dcad_gemm_bf16_splitk_static(const void* A, const void* B, void* D, int M, int N, int K, int a_major,
+                                            int b_major, int lda, int ldb, int ldd, const float* bias,
+                                            const void* aux, void* aux_out, int ldaux, int epi, int split_k,
+                                            int block_n, int max_ctas, void* stream) {
+    if (split_k < 2) return DCAD_ERR_BAD_ARGUMENT;
+    if ((epi == DCAD_EPI_BIAS || epi == DCAD_EPI_BIAS_GELU) && bias == nullptr) return DCAD_ERR_BAD_ARGUMENT;
+    if (epi == DCAD_EPI_DGELU && aux == nullptr) return DCAD_ERR_BAD_ARGUMENT;
+    if (M <= 0 || N <= 0 || K <= 0) return DCAD_ERR_BAD_SHAPE;
+    // the built-in scratch has a fixed size: refuse anything that does not fit rather than spill past it
+    if (dcad_gemm_splitk_workspace_bytes(M, N, split_k) > static_cast<size_t>(DCAD_SPLITK_STATIC_BYTES))
+        return DCAD_ERR_TOO_LARGE;
+    float* ws = nullptr;
+    int rc = static_workspace(&ws);
+    if (rc) return rc;
+    // Nothing in the scratch has to be cleared: pass 1 stores every partial element that pass 2 reads, so whatever
+    // an earlier call left behind is overwritten or never looked at.
+    t_tensor_map_cache_enabled = false;
+    rc = gemm_splitk_run(A, B, D, M, N, K, a_major, b_major, lda, ldb, ldd, bias, aux, aux_out, ldaux, epi, split_k,
+                         block_n, max_ctas, ws, reinterpret_cast<cudaStream_t>(stream));
+    t_tensor_map_cache_enabled = true;
+    return rc;
 }

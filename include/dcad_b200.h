@@ -60,6 +60,26 @@ int dcad_gemm_bf16_splitk(const void* A, const void* B, void* D, int M, int N, i
                           int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
                           int split_k, int block_n, int max_ctas, void* workspace, size_t workspace_bytes,
                           void* stream);
+/* Split-K GEMM without a caller-supplied workspace (no counterpart in the reference, which never touches device
+ * memory itself).  Same arguments, kernels and results as dcad_gemm_bf16_splitk, except that the fp32 scratch is a
+ * fixed DCAD_SPLITK_STATIC_BYTES (24 MiB) region built into the library, one per GPU that has loaded it, held until
+ * the process exits.  It exists for hosts that are not allowed to allocate once they are running: code issuing this
+ * GEMM during stream capture, servers with a device pool frozen at start-up, plug-ins in applications that ban
+ * run-time cudaMalloc because it synchronises the device.  The call performs no cudaMalloc / cudaFree, no host heap
+ * allocation and no allocating library call; A, B, bias, aux (inputs) and D, aux_out (outputs) remain the caller's.
+ *   limit       ceil(M/128)*128 * N * split_k * 4 bytes must fit in dcad_gemm_splitk_static_capacity(); a larger
+ *               problem is refused with DCAD_ERR_TOO_LARGE (2048 x 768 with split_k = 3 needs 18.9 MB).
+ *   first call  the first call made on a GPU looks up that GPU's scratch address (cudaGetSymbolAddress on the current
+ *               device).  Make that first call outside of, and before, any stream capture.
+ *   sharing     every call on a GPU uses the same region and finds the previous call's partial sums in it; none of it
+ *               needs clearing because the first pass rewrites everything the second pass reads.  Calls whose
+ *               execution overlaps on one GPU (different streams or threads) overwrite each other's partials: run
+ *               them one after another. */
+#define DCAD_SPLITK_STATIC_BYTES (24u << 20)
+size_t dcad_gemm_splitk_static_capacity(void);
+int dcad_gemm_bf16_splitk_static(const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major,
+                                 int lda, int ldb, int ldd, const float* bias, const void* aux, void* aux_out,
+                                 int ldaux, int epi, int split_k, int block_n, int max_ctas, void* stream);
 /* profiling aid: CTA 0 of every following GEMM writes 7 globaltimer stamps (ns) into this device buffer (NULL = off) */
 void dcad_gemm_set_timing_buffer(void* dev_ptr);
 
