@@ -35,7 +35,11 @@ def prepare_data(cfg: FedConfig, log: EventLog) -> Tuple[PackedSplit, PackedSpli
         os.makedirs(cfg.out_dir, exist_ok=True)
         path = os.path.join(cfg.out_dir, "synthetic_CICIDS2017.csv")
         if not os.path.exists(path):
-            synth.write_synthetic_csv(path, cfg.synthetic_rows, seed=0)
+            # several clients of one launch may get here together: each writes its own temporary file (the content is
+            # deterministic) and publishes it with an atomic rename, so nobody ever reads a half-written CSV
+            tmp = f"{path}.{os.getpid()}.tmp"
+            synth.write_synthetic_csv(tmp, cfg.synthetic_rows, seed=0)
+            os.replace(tmp, path)
     with log.phase("data preprocessing", path=path):
         shard = (cfg.client_id - 1, cfg.num_clients) if cfg.disjoint_shards else None
         texts, labels = cicids.preprocess_data(path, cfg.data_fraction, seed, shard=shard)
