@@ -86,7 +86,10 @@ def run_ours(args, rank: int, world: int, local_rank: int) -> dict:
     flat = bf16 = None
     if world > 1 and not args.no_fedavg:
         p2p = importlib.import_module(f"{PKG}.parallel.p2p")
-        group = p2p.PeerGroup(rank, world, layout.total, layout.gemm_end)
+        try:  # symmetric-memory allocation also carries an NVLink multicast mapping (NVLS) when the host exposes it
+            group = p2p.SymmPeerGroup(rank, world, layout.total, layout.gemm_end)
+        except Exception:  # noqa: BLE001
+            group = p2p.PeerGroup(rank, world, layout.total, layout.gemm_end)
         flat, bf16 = group.arena_tensor(), group.mirror_tensor()
     eng = eng_mod.B200Engine(dims, batch=B, seq=S, device=local_rank, init_seed=rank, seed=1234 + rank,
                              flat_params=flat, bf16_params=bf16)
@@ -175,15 +178,21 @@ def run_ours(args, rank: int, world: int, local_rank: int) -> dict:
         p2p = importlib.import_module(f"{PKG}.parallel.p2p")
         nccl_base = importlib.import_module(f"{PKG}.parallel.nccl_baseline")
         iters = 10
-        for _ in range(3):
-            group.fedavg(p2p.TWO_SHOT)
-        barrier()
-        e0.record()
-        for _ in range(iters):
-            group.fedavg(p2p.TWO_SHOT)
-        e1.record()
-        torch.cuda.synchronize(dev)
-        fed_ms = max_over_ranks(e0.elapsed_time(e1) / iters)
+
+        def time_round(mode):
+            for _ in range(3):
+                group.fedavg(mode)
+            barrier()
+            e0.record()
+            for _ in range(iters):
+                group.fedavg(mode)
+            e1.record()
+            torch.cuda.synchronize(dev)
+            return max_over_ranks(e0.elapsed_time(e1) / iters)
+
+        two_shot_ms = time_round(p2p.TWO_SHOT)
+        nvls_ms = time_round(p2p.NVLS) if getattr(group, "has_nvls", False) else None
+        fed_ms = min(two_shot_ms, nvls_ms) if nvls_ms is not None else two_shot_ms
         err = group.error_flag()
         # NCCL all-reduce baseline on a scratch copy of the arena (same bytes), incl. the scale and the bf16 cast
         scratch = eng.arena.flat.clone()
@@ -199,11 +208,17 @@ def run_ours(args, rank: int, world: int, local_rank: int) -> dict:
         nccl_ms = max_over_ranks(e0.elapsed_time(e1) / iters)
         bytes_arena = layout.total * 4
         bytes_mirror = layout.gemm_end * 2
-        # two-shot traffic INTO each GPU over NVLink: (N-1)/N of the arena pulled from peers (reduce-scatter by
-        # reads) + the (N-1) peers each pushing their averaged shard and its bf16 mirror (all-gather by writes)
-        ingress = (world - 1) / world * (2 * bytes_arena + bytes_mirror)
+        use_nvls = nvls_ms is not None and nvls_ms <= two_shot_ms
+        # bytes arriving at each GPU over NVLink.  two-shot: (N-1)/N of the arena pulled from peers + the peers' pushed
+        # shards with their bf16 copies.  NVLS: the switch-reduced own shard + the other ranks' multicast stores.
+        ingress_two_shot = (world - 1) / world * (2 * bytes_arena + bytes_mirror)
+        ingress_nvls = bytes_arena / world + (world - 1) / world * (bytes_arena + bytes_mirror)
+        ingress = ingress_nvls if use_nvls else ingress_two_shot
         out["fedavg"] = {
-            "round_latency_ms": fed_ms, "kernel": "fedavg_p2p two-shot, in place, fp32 arena 265.5 MB + fused bf16 mirror 85 MB",
+            "round_latency_ms": fed_ms,
+            "kernel": ("fedavg_nvls (multimem.ld_reduce + multimem.st)" if use_nvls else "fedavg_p2p two-shot")
+                      + ", in place, fp32 arena 265.5 MB + fused bf16 mirror 85 MB",
+            "two_shot_ms": two_shot_ms, "nvls_ms": nvls_ms,
             "nccl_allreduce_baseline_ms": nccl_ms, "handshake_error_flag": err,
             "nvlink_ingress_bytes_per_gpu": ingress,
             "achieved_ingress_GBps": ingress / (fed_ms * 1e-3) / 1e9,

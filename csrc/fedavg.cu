@@ -223,6 +223,71 @@ fedavg_p2p_kernel(const FedArgs a, int rank, int n, int64_t num_vecs, int mode, 
     }
 }
 
+// ---- NVLS: in-switch reduction over a multicast mapping of all clients' arenas ----
+// multimem.ld_reduce pulls element i already summed over all N GPUs by the NVSwitch (ingress S/N per GPU instead of
+// (N-1)/N*S), multimem.st writes the averaged value (and its bf16 copy) into all N arenas with one store.  The
+// summation order inside the switch is unspecified, so this path is fp32-tolerance, not bit, equal to the reference
+// loop; it cannot apply per-client weights.
+__device__ __forceinline__ float4 multimem_ld_reduce_add_f32x4(const void* mc_ptr) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc_ptr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void multimem_st_f32x4(void* mc_ptr, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                 ::"l"(mc_ptr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void multimem_st_b32x2(void* mc_ptr, uint32_t a, uint32_t b) {
+    asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};"
+                 ::"l"(mc_ptr), "f"(__uint_as_float(a)), "f"(__uint_as_float(b)) : "memory");
+}
+
+__global__ void __launch_bounds__(512)
+fedavg_nvls_kernel(const FedArgs a, float* mc_arena, __nv_bfloat16* mc_mirror, int rank, int n, int64_t num_vecs,
+                   int64_t bf16_begin, int64_t bf16_end, uint32_t epoch) {
+    uint32_t* my_pad = a.pad[rank];
+    if (blockIdx.x == 0 && threadIdx.x < n) st_release_sys(a.pad[threadIdx.x] + PAD_READY + rank, epoch);
+    if (threadIdx.x < n) {
+        if (!spin_until_ge(my_pad + PAD_READY + threadIdx.x, epoch)) my_pad[PAD_ERROR] = 1;
+    }
+    __syncthreads();
+    const int64_t lo = num_vecs * rank / n, hi = num_vecs * (rank + 1) / n;
+    const float inv_n = 1.0f / static_cast<float>(n);
+    const float nf = static_cast<float>(n);
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    for (int64_t v0 = lo + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; v0 < hi; v0 += stride * 4) {
+        float4 acc[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (v0 + u * stride < hi) acc[u] = multimem_ld_reduce_add_f32x4(mc_arena + (v0 + u * stride) * 4);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t vec = v0 + u * stride;
+            if (vec >= hi) continue;
+            float4 r = acc[u];
+            r.x = __fdiv_rn(r.x, nf); r.y = __fdiv_rn(r.y, nf); r.z = __fdiv_rn(r.z, nf); r.w = __fdiv_rn(r.w, nf);
+            multimem_st_f32x4(mc_arena + vec * 4, r);
+            const int64_t e0 = vec * 4;
+            if (mc_mirror && e0 >= bf16_begin && e0 < bf16_end)
+                multimem_st_b32x2(mc_mirror + (e0 - bf16_begin), pack_bf16x2(r.x, r.y), pack_bf16x2(r.z, r.w));
+        }
+    }
+    (void)inv_n;
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const uint32_t prev = atomicAdd(my_pad + PAD_COUNTER, 1u);
+        if (prev == gridDim.x - 1) {
+            my_pad[PAD_COUNTER] = 0;
+            __threadfence_system();
+            for (int k = 0; k < n; ++k) st_release_sys(a.pad[k] + PAD_DONE + rank, epoch);
+            for (int k = 0; k < n; ++k)
+                if (!spin_until_ge(my_pad + PAD_DONE + k, epoch)) my_pad[PAD_ERROR] = 1;
+        }
+    }
+}
+
 static int fill_args(FedArgs& fa, const void* const* arenas, const void* const* outs, const void* const* mirrors,
                      const void* const* pads, const float* weights, int n) {
     if (n < 1 || n > FED_MAX) return DCAD_ERR_TOO_LARGE;
@@ -285,6 +350,27 @@ extern "C" int dcad_fedavg_p2p(const void* const* arenas, const void* const* out
         fedavg_p2p_kernel<true><<<(int)blocks, 512, 0, s>>>(fa, rank, n_clients, num_vecs, mode, bf16_begin, bf16_end, epoch);
     else
         fedavg_p2p_kernel<false><<<(int)blocks, 512, 0, s>>>(fa, rank, n_clients, num_vecs, mode, bf16_begin, bf16_end, epoch);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dcad_fedavg_nvls(void* mc_arena, void* mc_mirror, const void* const* pads, int rank, int n_clients,
+                                int64_t count, int64_t bf16_begin, int64_t bf16_end, uint32_t epoch, int max_ctas,
+                                void* stream) {
+    if (count <= 0) return 0;
+    if (count % 4 || (bf16_begin & 3) || (bf16_end & 3)) return DCAD_ERR_BAD_ALIGNMENT;
+    if (rank < 0 || rank >= n_clients || pads == nullptr || mc_arena == nullptr) return DCAD_ERR_BAD_ARGUMENT;
+    FedArgs fa;
+    const void* dummy[DCAD_FED_MAX_CLIENTS] = {};
+    int rc = fill_args(fa, dummy, nullptr, nullptr, pads, nullptr, n_clients);
+    if (rc) return rc;
+    const int64_t num_vecs = count / 4;
+    int64_t blocks = ((num_vecs + n_clients - 1) / n_clients + 511) / 512;
+    const int64_t cap = max_ctas > 0 ? max_ctas : 148;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    fedavg_nvls_kernel<<<(int)blocks, 512, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        fa, reinterpret_cast<float*>(mc_arena), reinterpret_cast<__nv_bfloat16*>(mc_mirror), rank, n_clients, num_vecs,
+        bf16_begin, bf16_end, epoch);
     return (int)cudaGetLastError();
 }
 

@@ -95,6 +95,7 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("dcad_attn_bwd", [P, P, P, P, P, P, I, I, I, F, P, U32, P])
     sig("dcad_fedavg_local", [P, P, P, I, L64, I, P, L64, L64, I, P])
     sig("dcad_fedavg_p2p", [P, P, P, P, P, I, I, L64, I, I, L64, L64, U32, I, P])
+    sig("dcad_fedavg_nvls", [P, P, P, I, I, L64, L64, L64, U32, I, P])
     sig("dcad_p2p_alloc", [P, ctypes.c_size_t])
     sig("dcad_p2p_free", [P])
     sig("dcad_p2p_ipc_get", [P, P])
@@ -304,6 +305,12 @@ def fedavg_p2p(arena_ptrs, pad_ptrs, rank, count, epoch, *, out_ptrs=None, mirro
                                 _ptr_array(pad_ptrs), _float_array(weights), rank, len(arena_ptrs), count,
                                 1 if in_bf16 else 0, mode, bf16_begin, bf16_end, epoch, max_ctas,
                                 stream_ptr(stream)), "dcad_fedavg_p2p")
+
+
+def fedavg_nvls(mc_arena_ptr, mc_mirror_ptr, pad_ptrs, rank, count, epoch, *, bf16_begin=0, bf16_end=0, max_ctas=0,
+                stream=None):
+    check(lib().dcad_fedavg_nvls(mc_arena_ptr, mc_mirror_ptr, _ptr_array(pad_ptrs), rank, len(pad_ptrs), count,
+                                 bf16_begin, bf16_end, epoch, max_ctas, stream_ptr(stream)), "dcad_fedavg_nvls")
 
 
 def p2p_alloc(nbytes: int) -> int:

@@ -18,7 +18,7 @@ import torch
 from ..ops import native as nv
 
 PAD_BYTES = 64 * 4
-TWO_SHOT, ONE_SHOT = 0, 1
+TWO_SHOT, ONE_SHOT, NVLS = 0, 1, 2
 
 
 class PeerGroup:
@@ -99,6 +99,75 @@ class PeerGroup:
         for b in (self.arena_buf, self.mirror_buf, self.pad_buf, self.out_buf):
             if b is not None:
                 b.free()
+
+
+class SymmPeerGroup:
+    """Peer group whose buffers come from ``torch.distributed._symmetric_memory`` (used purely as an allocator and
+    handle exchange): one symmetric allocation per rank laid out as ``[fp32 arena | bf16 mirror | signal pad]``.  When
+    the host exposes NVLink multicast the handle carries a multicast address and ``fedavg(NVLS)`` reduces inside the
+    NVSwitch; the unicast peer pointers serve the two-shot kernel otherwise (or on request)."""
+
+    def __init__(self, rank: int, world: int, arena_elems: int, mirror_elems: int, dist_group=None):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+
+        self.rank, self.world = rank, world
+        self.arena_elems, self.mirror_elems = arena_elems, mirror_elems
+        self.arena_dtype = torch.float32
+        self._arena_bytes = arena_elems * 4
+        self._mirror_off = (self._arena_bytes + 255) // 256 * 256
+        self._pad_off = (self._mirror_off + max(mirror_elems, 8) * 2 + 255) // 256 * 256
+        total = self._pad_off + PAD_BYTES
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self._buf = symm.empty(total, dtype=torch.uint8, device=dev)
+        self._buf.zero_()
+        group = dist_group if dist_group is not None else dist.group.WORLD
+        self._hdl = symm.rendezvous(self._buf, group=group)
+        base = [int(p) for p in self._hdl.buffer_ptrs]
+        self.arena_ptrs = base
+        self.mirror_ptrs = [p + self._mirror_off for p in base]
+        self.pad_ptrs = [p + self._pad_off for p in base]
+        mc = int(self._hdl.multicast_ptr) if getattr(self._hdl, "has_multicast_support", True) else 0
+        self.multicast_ptr = mc
+        self.epoch = 0
+        torch.cuda.synchronize()
+        dist.barrier(group=dist_group)
+
+    @property
+    def has_nvls(self) -> bool:
+        return self.multicast_ptr != 0
+
+    def arena_tensor(self) -> torch.Tensor:
+        return self._buf[: self._arena_bytes].view(torch.float32)
+
+    def mirror_tensor(self) -> torch.Tensor:
+        return self._buf[self._mirror_off: self._mirror_off + self.mirror_elems * 2].view(torch.bfloat16)
+
+    def pad_tensor(self) -> torch.Tensor:
+        return self._buf[self._pad_off: self._pad_off + PAD_BYTES].view(torch.int32)
+
+    def out_tensor(self):
+        return None
+
+    def fedavg(self, mode: int = NVLS, weights: Optional[Sequence[float]] = None, with_mirror: bool = True,
+               max_ctas: int = 0, stream=None) -> None:
+        self.epoch += 1
+        if mode == NVLS and self.has_nvls and weights is None:
+            nv.fedavg_nvls(self.multicast_ptr, self.multicast_ptr + self._mirror_off if with_mirror else 0,
+                           self.pad_ptrs, self.rank, self.arena_elems, self.epoch, bf16_begin=0,
+                           bf16_end=self.mirror_elems if with_mirror else 0, max_ctas=max_ctas, stream=stream)
+        else:
+            nv.fedavg_p2p(self.arena_ptrs, self.pad_ptrs, self.rank, self.arena_elems, self.epoch,
+                          mirror_ptrs=self.mirror_ptrs if (with_mirror and self.mirror_elems) else None,
+                          weights=weights, mode=TWO_SHOT, bf16_begin=0,
+                          bf16_end=self.mirror_elems if with_mirror else 0, max_ctas=max_ctas, stream=stream)
+
+    def error_flag(self) -> int:
+        return int(self.pad_tensor()[33].item())
+
+    def close(self) -> None:
+        self._hdl = None
+        self._buf = None
 
 
 class LocalPeerGroup:

@@ -157,6 +157,13 @@ int dcad_fedavg_p2p(const void* const* arenas, const void* const* outs, const vo
                     int in_bf16, int mode, int64_t bf16_begin, int64_t bf16_end, uint32_t epoch, int max_ctas,
                     void* stream);
 
+/* NVLS variant: mc_arena / mc_mirror are MULTICAST addresses mapping every client's fp32 arena / bf16 mirror
+ * (cuMulticast* objects, e.g. from torch symmetric memory); the NVSwitch sums the N copies (multimem.ld_reduce) and
+ * replicates the averaged shard (multimem.st).  fp32 arenas only, unweighted; in-switch summation order is
+ * unspecified (fp32 tolerance vs the reference loop).  pads: unicast signal pads as for dcad_fedavg_p2p. */
+int dcad_fedavg_nvls(void* mc_arena, void* mc_mirror, const void* const* pads, int rank, int n_clients, int64_t count,
+                     int64_t bf16_begin, int64_t bf16_end, uint32_t epoch, int max_ctas, void* stream);
+
 /* ---- peer-memory runtime (set-up calls; these allocate / map) ---- */
 int dcad_p2p_alloc(void** ptr, size_t bytes);
 int dcad_p2p_free(void* ptr);

@@ -55,6 +55,21 @@ def main():
                             "arena_MB": nbytes / 1e6, "ingress_bytes_per_gpu": link,
                             "ingress_GBps": link / (ms * 1e-3) / 1e9, "roofline_ms_770GBps": link / 770e9 * 1e3,
                             "err": grp.error_flag()})
+        if dtype == torch.float32:
+            try:
+                sg = p2p.SymmPeerGroup(rank, world, elems, mirror)
+                sg.arena_tensor().copy_(grp.arena_tensor())
+                if sg.has_nvls:
+                    for ctas in (0, 64, 32):
+                        ms = timed(lambda: sg.fedavg(p2p.NVLS, max_ctas=ctas))
+                        link = nbytes / world + (world - 1) / world * (nbytes + mirror * 2)
+                        out.append({"world": world, "dtype": name, "kernel": "nvls_multimem", "max_ctas": ctas or 148,
+                                    "ms": ms, "arena_MB": nbytes / 1e6, "ingress_bytes_per_gpu": link,
+                                    "ingress_GBps": link / (ms * 1e-3) / 1e9, "roofline_ms_770GBps": link / 770e9 * 1e3,
+                                    "err": sg.error_flag()})
+                sg.close()
+            except Exception as e:  # noqa: BLE001
+                out.append({"world": world, "dtype": name, "kernel": "nvls_multimem", "unavailable": repr(e)[:120]})
         scratch = grp.arena_tensor().clone()
         m = torch.empty(max(mirror, 8), device=dev, dtype=torch.bfloat16)
         ms = timed(lambda: nccl_baseline.nccl_fedavg_(scratch, m if mirror else None, mirror))

@@ -47,6 +47,35 @@ def main():
     assert torch.allclose(arena.cpu(), exp, rtol=1e-5, atol=1e-6)
     dist.barrier()
     grp.close()
+    # symmetric-memory group: two-shot over its unicast pointers, NVLS when the host exposes multicast
+    try:
+        sg = p2p.SymmPeerGroup(rank, world, elems, mirror)
+    except Exception as e:  # noqa: BLE001
+        sg = None
+        if rank == 0:
+            print("SYMM_UNAVAILABLE", repr(e)[:200], flush=True)
+    if sg is not None:
+        for mode, name in ((p2p.TWO_SHOT, "two_shot"), (p2p.NVLS, "nvls")):
+            if mode == p2p.NVLS and not sg.has_nvls:
+                if rank == 0:
+                    print("NVLS_UNAVAILABLE (no multicast support on this host)", flush=True)
+                continue
+            sg.arena_tensor().copy_(mine)
+            torch.cuda.synchronize()
+            dist.barrier()
+            sg.fedavg(mode)
+            torch.cuda.synchronize()
+            assert sg.error_flag() == 0
+            got = sg.arena_tensor().cpu()
+            if mode == p2p.TWO_SHOT:
+                assert torch.equal(got, base), f"rank {rank}: symm two-shot mismatch"
+            else:
+                assert torch.allclose(got, base, rtol=1e-6, atol=1e-6), f"rank {rank}: nvls mismatch"
+            assert torch.allclose(sg.mirror_tensor().float().cpu(), base[:mirror].bfloat16().float(), rtol=1e-2, atol=1e-2)
+            if rank == 0:
+                print(f"SYMM_{name.upper()}_OK", flush=True)
+        dist.barrier()
+        sg.close()
     if rank == 0:
         print("FEDAVG_IPC_OK", flush=True)
     dist.destroy_process_group()
