@@ -51,6 +51,86 @@ adam_flat_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict
     }
 }
 
+// Sharded variant for intra-client data parallelism: this rank owns elements [begin, end) of the arena.  Gradients
+// were summed over the group (wgrad TMA reduce-add / reduce-scatter), so they are scaled by grad_scale = 1/G here.
+// The updated values are pushed to every peer of the group over NVLink in the same pass: the bf16 GEMM weights into
+// all peers' mirrors, and (for the region that kernels read in fp32: embeddings, LayerNorm, biases, classifier) the
+// fp32 values into all peers' parameter arenas -- the parameter all-gather, fused into the optimizer.
+struct AdamPeers {
+    float* p[16];
+    __nv_bfloat16* bf16[16];
+    int n;
+    int self;
+};
+
+__global__ void __launch_bounds__(256)
+adam_dp_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+               int64_t begin, int64_t end, int64_t bf16_begin, int64_t bf16_end, int64_t push32_begin,
+               int64_t push32_end, float lr, float beta1, float beta2, float eps, float grad_scale,
+               const uint64_t* __restrict__ state, const AdamPeers peers) {
+    __shared__ float s_c[2];
+    if (threadIdx.x == 0) {
+        const double t = static_cast<double>(state ? state[1] + 1 : 1);
+        const double bc1 = 1.0 - pow(static_cast<double>(beta1), t);
+        const double bc2 = 1.0 - pow(static_cast<double>(beta2), t);
+        s_c[0] = static_cast<float>(static_cast<double>(lr) / bc1);
+        s_c[1] = static_cast<float>(1.0 / sqrt(bc2));
+    }
+    __syncthreads();
+    const float step_size = s_c[0], inv_sqrt_bc2 = s_c[1];
+    const float omb1 = 1.0f - beta1, omb2 = 1.0f - beta2;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x * 4;
+    for (int64_t i = begin + (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 4; i < end; i += stride) {
+        float4 pp = *reinterpret_cast<const float4*>(p + i);
+        float4 gg = *reinterpret_cast<const float4*>(g + i);
+        float4 mm = *reinterpret_cast<const float4*>(m + i);
+        float4 vv = *reinterpret_cast<const float4*>(v + i);
+        gg.x *= grad_scale; gg.y *= grad_scale; gg.z *= grad_scale; gg.w *= grad_scale;
+#define DCAD_ADAM_ONE(c)                                                   \
+        mm.c = beta1 * mm.c + omb1 * gg.c;                                 \
+        vv.c = beta2 * vv.c + omb2 * gg.c * gg.c;                          \
+        pp.c -= step_size * (mm.c / (sqrtf(vv.c) * inv_sqrt_bc2 + eps));
+        DCAD_ADAM_ONE(x) DCAD_ADAM_ONE(y) DCAD_ADAM_ONE(z) DCAD_ADAM_ONE(w)
+#undef DCAD_ADAM_ONE
+        *reinterpret_cast<float4*>(p + i) = pp;
+        *reinterpret_cast<float4*>(m + i) = mm;
+        *reinterpret_cast<float4*>(v + i) = vv;
+        *reinterpret_cast<float4*>(g + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i >= push32_begin && i < push32_end) {
+            for (int k = 0; k < peers.n; ++k)
+                if (k != peers.self) *reinterpret_cast<float4*>(peers.p[k] + i) = pp;
+        }
+        if (i >= bf16_begin && i < bf16_end) {
+            uint2 o;
+            o.x = pack_bf16x2(pp.x, pp.y);
+            o.y = pack_bf16x2(pp.z, pp.w);
+            for (int k = 0; k < peers.n; ++k) *reinterpret_cast<uint2*>(peers.bf16[k] + (i - bf16_begin)) = o;
+        }
+    }
+}
+
+// One-block cross-GPU barrier over the group's signal pads (words [48, 64) of each pad, slot k written by rank k).
+// The epoch is derived from the device-side step counter so the launch is replayable inside a CUDA graph.
+__global__ void xgpu_barrier_kernel(uint32_t* const* pads_dev_unused, const uint64_t* state, uint32_t phase, int rank,
+                                    int n, uint32_t* p0, uint32_t* p1, uint32_t* p2, uint32_t* p3, uint32_t* p4,
+                                    uint32_t* p5, uint32_t* p6, uint32_t* p7) {
+    (void)pads_dev_unused;
+    uint32_t* pads[8] = {p0, p1, p2, p3, p4, p5, p6, p7};
+    const uint32_t epoch = static_cast<uint32_t>(state[1]) * 8u + phase + 1u;
+    __threadfence_system();
+    if (threadIdx.x < n) {
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(pads[threadIdx.x] + 48 + rank), "r"(epoch) : "memory");
+        const uint32_t* mine = pads[rank] + 48 + threadIdx.x;
+        uint32_t v = 0;
+        for (uint32_t it = 0; it < (1u << 26); ++it) {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+            if (static_cast<int32_t>(v - epoch) >= 0) break;
+            __nanosleep(32);
+        }
+        if (static_cast<int32_t>(v - epoch) < 0) pads[rank][33] = 1;  // error word, same as the FedAvg kernels
+    }
+}
+
 __global__ void step_advance_kernel(uint64_t* state) {
     if (threadIdx.x == 0 && blockIdx.x == 0) state[1] += 1;
 }
@@ -79,5 +159,43 @@ extern "C" int dcad_adam_step(float* p, float* g, float* m, float* v, void* p_bf
 
 extern "C" int dcad_step_advance(uint64_t* state, void* stream) {
     step_advance_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(state);
+    return (int)cudaGetLastError();
+}
+
+// Sharded Adam + fused parameter all-gather (see adam_dp_kernel).  peer_p / peer_bf16 are HOST arrays of n_peers
+// device pointers (this rank's own buffers included at index `self`).
+extern "C" int dcad_adam_step_dp(float* p, float* g, float* m, float* v, int64_t begin, int64_t end, int64_t bf16_begin,
+                                 int64_t bf16_end, int64_t push32_begin, int64_t push32_end, float lr, float beta1,
+                                 float beta2, float eps, float grad_scale, const uint64_t* state,
+                                 const void* const* peer_p, const void* const* peer_bf16, int n_peers, int self,
+                                 void* stream) {
+    if (end <= begin) return 0;
+    if ((begin | end | bf16_begin | bf16_end | push32_begin | push32_end) & 3) return DCAD_ERR_BAD_ALIGNMENT;
+    if (n_peers < 1 || n_peers > 16 || self < 0 || self >= n_peers) return DCAD_ERR_BAD_ARGUMENT;
+    AdamPeers peers;
+    for (int k = 0; k < 16; ++k) {
+        peers.p[k] = (k < n_peers && peer_p) ? reinterpret_cast<float*>(const_cast<void*>(peer_p[k])) : nullptr;
+        peers.bf16[k] = (k < n_peers && peer_bf16) ? reinterpret_cast<__nv_bfloat16*>(const_cast<void*>(peer_bf16[k])) : nullptr;
+    }
+    peers.n = n_peers;
+    peers.self = self;
+    if (!peer_p) { push32_begin = 0; push32_end = 0; }
+    if (!peer_bf16) { bf16_begin = 0; bf16_end = 0; }
+    int64_t blocks = ((end - begin) / 4 + 255) / 256;
+    const int64_t cap = 148 * 16;
+    if (blocks > cap) blocks = cap;
+    adam_dp_kernel<<<static_cast<int>(blocks), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        p, g, m, v, begin, end, bf16_begin, bf16_end, push32_begin, push32_end, lr, beta1, beta2, eps, grad_scale, state,
+        peers);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int dcad_xgpu_barrier(const void* const* pads, int rank, int n, const uint64_t* state, uint32_t phase,
+                                 void* stream) {
+    if (n < 1 || n > 8 || rank < 0 || rank >= n || phase > 7) return DCAD_ERR_BAD_ARGUMENT;
+    uint32_t* p[8];
+    for (int k = 0; k < 8; ++k) p[k] = k < n ? reinterpret_cast<uint32_t*>(const_cast<void*>(pads[k])) : nullptr;
+    xgpu_barrier_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(nullptr, state, phase, rank, n, p[0], p[1],
+                                                                                p[2], p[3], p[4], p[5], p[6], p[7]);
     return (int)cudaGetLastError();
 }

@@ -39,7 +39,7 @@ struct GemmParams {
     const __nv_bfloat16* aux;  // EPI_DGELU: pre-activation (same shape as D)
     int has_aux_out;           // EPI_BIAS_GELU: also store the pre-activation through tmAux
     int epi;
-    int out_fp32;
+    int out_fp32;              // 0 = bf16, 1 = fp32 store, 2 = fp32 TMA reduce-add even without split-K (D may be a peer GPU's buffer)
     int split_k;               // > 1: fp32 output accumulated with TMA reduce-add (output must be zero-initialised)
     int ws_row_stride;         // > 0: workspace mode, split s stores its fp32 partial tile at row s*ws_row_stride + m
     int num_m_blocks, num_n_blocks, num_k_blocks, kb_per_split;
@@ -332,7 +332,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                     epi_bar_sync();
                     if (ep_tid == 0) {
                         if (n_base + s * 32 < p.N) {
-                            if (p.split_k > 1 && p.ws_row_stride == 0) tma_reduce_add_2d(&tmD, sD, n_base + s * 32, out_row0);
+                            if ((p.split_k > 1 && p.ws_row_stride == 0) || p.out_fp32 == 2) tma_reduce_add_2d(&tmD, sD, n_base + s * 32, out_row0);
                             else tma_store_2d(&tmD, sD, n_base + s * 32, out_row0);
                         }
                         bulk_commit_group();

@@ -57,7 +57,7 @@ class B200Engine:
     def __init__(self, dims: ModelDims = ModelDims(), batch: int = 16, seq: int = 128, device: int | str = 0,
                  lr: float = 2e-5, betas: Tuple[float, float] = (0.9, 0.999), eps: float = 1e-8, seed: int = 0,
                  flat_params: Optional[torch.Tensor] = None, bf16_params: Optional[torch.Tensor] = None,
-                 plan: Optional[GemmPlan] = None, init_seed: Optional[int] = 0):
+                 plan: Optional[GemmPlan] = None, init_seed: Optional[int] = 0, dp=None):
         if not torch.cuda.is_available():
             raise nv.NativeError("B200Engine needs a CUDA device; use models.distilbert.DDoSClassifier on CPU")
         nv.lib()  # fail loudly if the native library is missing
@@ -70,11 +70,17 @@ class B200Engine:
         torch.cuda.set_device(self.device)
         self.lr, self.betas, self.eps = lr, betas, eps
         self.plan = plan or GemmPlan()
+        self.dp = dp  # parallel.dp.DPGroup when this client spans several GPUs
         dev = self.device
+        if dp is not None:
+            flat_params, bf16_params = dp.param_tensor(), dp.mirror_tensor()
         self.arena = ParamArena(dims, dev, flat=flat_params, with_optimizer_state=True, with_bf16=bf16_params is None)
         if bf16_params is not None:
             assert bf16_params.numel() == self.arena.layout.gemm_end and bf16_params.dtype == torch.bfloat16
             self.arena.bf16 = bf16_params
+        if dp is not None:
+            self.arena.grad = dp.grad_tensor()  # peers reduce-add into it and read it: must be peer-mappable
+            self.arena.grad.zero_()
         if init_seed is not None:
             self.arena.init_random_(init_seed)
         self.rng = torch.tensor([seed, 0], dtype=torch.int64, device=dev)  # {seed, step}
@@ -142,7 +148,7 @@ class B200Engine:
             off = lay.qkv_weight_offset(l)
             D = self.dims.dim
             self.p["wqkv"].append(a.bf16[off: off + 3 * D * D].view(3 * D, D))
-            self.p["d_wqkv"].append(a.qkv_weight(l, a.grad))
+            self.p["d_wqkv"].append(self._wgrad_target(off, (3 * D, D), a.qkv_weight(l, a.grad)))
             self.p["bqkv"].append(a.qkv_bias(l))
             self.p["d_bqkv"].append(a.qkv_bias(l, a.grad))
             for short, key, is_w in (("wo", "attention.out_lin.weight", True), ("bo", "attention.out_lin.bias", False),
@@ -151,7 +157,8 @@ class B200Engine:
                                      ("w2", "ffn.lin2.weight", True), ("bb2", "ffn.lin2.bias", False),
                                      ("g2", "output_layer_norm.weight", False), ("b2", "output_layer_norm.bias", False)):
                 self.p[short].append(a.bf16_view(p + key) if is_w else a.view(p + key))
-                self.p["d_" + short].append(a.view(p + key, a.grad))
+                local = a.view(p + key, a.grad)
+                self.p["d_" + short].append(self._wgrad_target(lay.offsets[p + key], tuple(local.shape), local) if is_w else local)
         e = "distilbert.embeddings."
         self.word, self.pos = a.view(e + "word_embeddings.weight"), a.view(e + "position_embeddings.weight")
         self.eg, self.eb = a.view(e + "LayerNorm.weight"), a.view(e + "LayerNorm.bias")
@@ -159,6 +166,11 @@ class B200Engine:
         self.d_eg, self.d_eb = a.view(e + "LayerNorm.weight", a.grad), a.view(e + "LayerNorm.bias", a.grad)
         self.cw, self.cb = a.view("classifier.weight"), a.view("classifier.bias")
         self.d_cw, self.d_cb = a.view("classifier.weight", a.grad), a.view("classifier.bias", a.grad)
+
+    def _wgrad_target(self, offset: int, shape, local: torch.Tensor) -> torch.Tensor:
+        """Where a weight-gradient GEMM writes: the local gradient arena, or (data-parallel client) the arena of the
+        GPU that owns this weight, reached through its peer mapping."""
+        return local if self.dp is None else self.dp.owner_grad_view(offset, tuple(shape))
 
     def state_dict(self, clone: bool = True):
         return self.arena.state_dict(clone=clone)
@@ -239,11 +251,11 @@ class B200Engine:
                     rng=self.rng, stream_id=_layer_stream(l, 1))
             # lin2: dW2 = da2^T hmid ; dpre = (da2 W2) * gelu'(pre)
             self._gemm(da2, hmid, P["d_w2"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_lin2[0],
-                       split_k=pl.wgrad_lin2[1])
+                       split_k=pl.wgrad_lin2[1], reduce_add=self.dp is not None)
             self._gemm(da2, P["w2"][l], self.g_wide, b_major=MN, aux=pre, epi=nv.EPI_DGELU, block_n=pl.lin2_dgrad)
             # lin1: dW1 = dpre^T sa ; db1 = colsum(dpre) ; dsa = dpre W1
             self._gemm(self.g_wide, sa, P["d_w1"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_lin1[0],
-                       split_k=pl.wgrad_lin1[1])
+                       split_k=pl.wgrad_lin1[1], reduce_add=self.dp is not None)
             self._k(nv.colsum_bf16, self.g_wide, P["d_bb1"][l])
             dsa = self.g_b  # dy1/dy2 of this layer (g_a/g_b) are dead after the LN backward above
             self._gemm_splitk(self.g_wide, P["w1"][l], dsa, pl.lin1_dgrad, b_major=MN)
@@ -253,7 +265,7 @@ class B200Engine:
                     P["d_b1"][l], P["d_bo"][l])
             # out_lin: dWo = dz1^T ctx ; dctx = dz1 Wo
             self._gemm(dz1, ctx, P["d_wo"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_out[0],
-                       split_k=pl.wgrad_out[1])
+                       split_k=pl.wgrad_out[1], reduce_add=self.dp is not None)
             dctx = self.g_c
             self._gemm(dz1, P["wo"][l], dctx, b_major=MN, block_n=pl.out_dgrad)
             # attention
@@ -261,7 +273,7 @@ class B200Engine:
                     p_drop=d.attention_dropout, rng=self.rng, stream_id=_layer_stream(l, 0))
             # QKV: dWqkv = dqkv^T x ; dbqkv = colsum(dqkv) ; dx = dqkv Wqkv
             self._gemm(self.g_qkv, x, P["d_wqkv"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_qkv[0],
-                       split_k=pl.wgrad_qkv[1])
+                       split_k=pl.wgrad_qkv[1], reduce_add=self.dp is not None)
             self._k(nv.colsum_bf16, self.g_qkv, P["d_bqkv"][l])
             dxq = self.g_b
             self._gemm(self.g_qkv, P["wqkv"][l], dxq, b_major=MN, block_n=pl.qkv_dgrad)
@@ -273,8 +285,34 @@ class B200Engine:
     def _optimizer(self) -> None:
         a = self.arena
         lay = a.layout
-        self._k(nv.adam_step, a.flat, a.grad, a.exp_avg, a.exp_avg_sq, a.bf16, lay.total, 0, lay.gemm_end,
-                0, lay.total, self.lr, self.betas[0], self.betas[1], self.eps, self.rng)
+        if self.dp is None:
+            self._k(nv.adam_step, a.flat, a.grad, a.exp_avg, a.exp_avg_sq, a.bf16, lay.total, 0, lay.gemm_end,
+                    0, lay.total, self.lr, self.betas[0], self.betas[1], self.eps, self.rng)
+            self._k(nv.step_advance, self.rng)
+            return
+        # ---- data-parallel client: reduce-scatter (already done tile by tile for the GEMM weights by the wgrad
+        # epilogues) -> sharded Adam with the parameter all-gather fused in -> barrier ----
+        dp = self.dp
+        G, r = dp.world, dp.rank
+        self._k(nv.xgpu_barrier, dp.pad_ptrs, r, self.rng, 0)          # every peer's backward (and its pushes) is done
+        lo, hi = dp.r2_range(r)
+        if hi > lo:  # biases / LayerNorm / embeddings / classifier: sum the G locally-accumulated copies of my range
+            self._k(nv.fedavg_local, [p + lo * 4 for p in dp.grad_ptrs], dp.grad_ptrs[r] + lo * 4, hi - lo,
+                    weights=[1.0] * G)
+        glo, ghi = dp.gemm_range(r)
+        scale = 1.0 / G
+        if ghi > glo:
+            self._k(nv.adam_step_dp, a.flat, a.grad, a.exp_avg, a.exp_avg_sq, glo, ghi, 0, lay.gemm_end, 0, 0, self.lr,
+                    self.betas[0], self.betas[1], self.eps, scale, self.rng, None, dp.mirror_ptrs, r)
+        if hi > lo:
+            self._k(nv.adam_step_dp, a.flat, a.grad, a.exp_avg, a.exp_avg_sq, lo, hi, 0, 0, lo, hi, self.lr,
+                    self.betas[0], self.betas[1], self.eps, scale, self.rng, dp.param_ptrs, None, r)
+        self._k(nv.xgpu_barrier, dp.pad_ptrs, r, self.rng, 1)          # all pushed parameters have landed everywhere
+        # the part of the locally accumulated gradients that other GPUs own has been consumed by them: clear it
+        if lo > lay.gemm_end:
+            a.grad[lay.gemm_end: lo].zero_()
+        if hi < lay.total:
+            a.grad[hi: lay.total].zero_()
         self._k(nv.step_advance, self.rng)
 
     # ------------------------------------------------------------------------------------------------ public API
@@ -326,6 +364,9 @@ class B200Engine:
             self.reset_optimizer()
             self.refresh_bf16()
             self.loss_accum.zero_()
+            if self.dp is not None:  # the step counter was rewound: the barrier epochs restart too
+                s.synchronize()
+                self.dp.reset_barrier_flags()
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize(self.device)
 

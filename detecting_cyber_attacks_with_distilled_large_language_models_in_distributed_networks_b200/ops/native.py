@@ -91,6 +91,8 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("dcad_cls_head_eval", [P, I, P, P, P, I, I, P, P, P, P, P])
     sig("dcad_adam_step", [P, P, P, P, P, L64, L64, L64, L64, L64, F, F, F, F, P, P])
     sig("dcad_step_advance", [P, P])
+    sig("dcad_adam_step_dp", [P, P, P, P, L64, L64, L64, L64, L64, L64, F, F, F, F, F, P, P, P, I, I, P])
+    sig("dcad_xgpu_barrier", [P, I, I, P, U32, P])
     sig("dcad_attn_fwd", [P, P, P, P, I, I, I, F, P, U32, P])
     sig("dcad_attn_bwd", [P, P, P, P, P, P, I, I, I, F, P, U32, P])
     sig("dcad_fedavg_local", [P, P, P, I, L64, I, P, L64, L64, I, P])
@@ -114,7 +116,7 @@ def _declare(L: ctypes.CDLL) -> None:
 def gemm_bf16(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_major: int = MAJOR_K, b_major: int = MAJOR_K,
               bias: Optional[torch.Tensor] = None, aux: Optional[torch.Tensor] = None,
               aux_out: Optional[torch.Tensor] = None, epi: int = EPI_NONE, split_k: int = 1,
-              block_n: int = 0, max_ctas: int = 0, stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
+              reduce_add: bool = False, block_n: int = 0, max_ctas: int = 0, stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
     """``out[M,N] = epilogue(A·Bᵀ)`` on the tcgen05 kernel.  ``a``/``b`` are 2-D bf16 with unit inner stride.
 
     ``a`` is ``[M,K]`` (MAJOR_K) or ``[K,M]`` (MAJOR_MN); ``b`` is ``[N,K]`` (MAJOR_K) or ``[K,N]`` (MAJOR_MN).
@@ -138,6 +140,8 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_major: i
     out_fp32 = 1 if out.dtype == torch.float32 else 0
     if not out_fp32:
         assert out.dtype == torch.bfloat16
+    elif reduce_add:
+        out_fp32 = 2  # accumulate into `out` with TMA reduce-add (it may live on a peer GPU)
     ldaux = 0
     if aux is not None:
         assert aux.dtype == torch.bfloat16 and aux.stride(1) == 1
@@ -249,6 +253,19 @@ def adam_step(p, g, m, v, p_bf16, n, bf16_begin, bf16_end, zero_begin, zero_end,
               stream=None):
     check(lib().dcad_adam_step(ptr(p), ptr(g), ptr(m), ptr(v), ptr(p_bf16), n, bf16_begin, bf16_end, zero_begin,
                                zero_end, lr, beta1, beta2, eps, ptr(state), stream_ptr(stream)), "dcad_adam_step")
+
+
+def adam_step_dp(p, g, m, v, begin, end, bf16_begin, bf16_end, push32_begin, push32_end, lr, beta1, beta2, eps,
+                 grad_scale, state, peer_p_ptrs, peer_bf16_ptrs, self_index, stream=None):
+    n = len(peer_p_ptrs) if peer_p_ptrs is not None else len(peer_bf16_ptrs)
+    check(lib().dcad_adam_step_dp(ptr(p), ptr(g), ptr(m), ptr(v), begin, end, bf16_begin, bf16_end, push32_begin,
+                                  push32_end, lr, beta1, beta2, eps, grad_scale, ptr(state), _ptr_array(peer_p_ptrs),
+                                  _ptr_array(peer_bf16_ptrs), n, self_index, stream_ptr(stream)), "dcad_adam_step_dp")
+
+
+def xgpu_barrier(pad_ptrs, rank, state, phase, stream=None):
+    check(lib().dcad_xgpu_barrier(_ptr_array(pad_ptrs), rank, len(pad_ptrs), ptr(state), phase, stream_ptr(stream)),
+          "dcad_xgpu_barrier")
 
 
 def step_advance(state, stream=None):

@@ -1,0 +1,161 @@
+"""Intra-client data parallelism (BASELINE.json config 4): one federated client spans G GPUs.
+
+The reference has no data parallelism at all; this is the B200-native addition.  Every GPU of the
+group runs the same step engine on its own micro-batch.  Communication is fused into the compute kernels instead of
+being separate NCCL collectives:
+
+* gradient reduce-scatter — each weight-gradient GEMM stores its output tile with a TMA reduce-add straight into
+  the gradient arena of the GPU that OWNS that weight (``cp.reduce.async.bulk.tensor`` on a peer-mapped address), tile by
+  tile, overlapping the rest of backward.  The small atomically-accumulated gradients (biases, LayerNorm,
+  embeddings, classifier) are reduce-scattered by one peer-read kernel after backward.
+* sharded Adam — each GPU updates only the arena elements it owns (ZeRO-1/2-like: optimizer state and reduced
+  gradients are not replicated).
+* parameter all-gather — fused into the optimizer kernel: the updated bf16 GEMM weights are stored into every peer's
+  mirror, the updated fp32 values that kernels read directly (embeddings, LayerNorm, biases) into every peer's arena.
+* two one-block cross-GPU barriers per step (signal pads), replayable from a CUDA graph.
+
+``torch.distributed`` is used only to exchange CUDA IPC handles at set-up.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Tuple
+
+import torch
+
+from ..models.arena import ArenaLayout
+from ..ops import native as nv
+
+PAD_BYTES = 64 * 4
+
+
+class DPGroup:
+    def __init__(self, rank: int, world: int, layout: ArenaLayout, dist_group=None):
+        import torch.distributed as dist
+
+        if world > 8:
+            raise ValueError("a data-parallel client group spans at most 8 GPUs")
+        self.rank, self.world, self.layout = rank, world, layout
+        self._dist_group = dist_group
+        n = layout.total
+        self.param_buf = nv.RawDeviceBuffer(nv.p2p_alloc(n * 4), n * 4)
+        self.grad_buf = nv.RawDeviceBuffer(nv.p2p_alloc(n * 4), n * 4)
+        self.mirror_buf = nv.RawDeviceBuffer(nv.p2p_alloc(layout.gemm_end * 2), layout.gemm_end * 2)
+        self.pad_buf = nv.RawDeviceBuffer(nv.p2p_alloc(PAD_BYTES), PAD_BYTES)
+        mine = {k: nv.p2p_ipc_get(b.ptr) for k, b in (("param", self.param_buf), ("grad", self.grad_buf),
+                                                      ("mirror", self.mirror_buf), ("pad", self.pad_buf))}
+        gathered: List[Optional[dict]] = [None] * world
+        dist.all_gather_object(gathered, mine, group=dist_group)
+        self._opened: List[nv.RawDeviceBuffer] = []
+        self.param_ptrs, self.grad_ptrs, self.mirror_ptrs, self.pad_ptrs = [], [], [], []
+        for r, h in enumerate(gathered):
+            for name, lst, own in (("param", self.param_ptrs, self.param_buf), ("grad", self.grad_ptrs, self.grad_buf),
+                                   ("mirror", self.mirror_ptrs, self.mirror_buf), ("pad", self.pad_ptrs, self.pad_buf)):
+                if r == rank:
+                    lst.append(own.ptr)
+                else:
+                    p = nv.p2p_ipc_open(h[name])
+                    self._opened.append(nv.RawDeviceBuffer(p, 0, owner=False, ipc=True))
+                    lst.append(p)
+        self._peer_grad_bufs = [nv.RawDeviceBuffer(p, n * 4, owner=False) for p in self.grad_ptrs]
+        self.gemm_bounds, self.r2_bounds = self._partition()
+        dist.barrier(group=dist_group)
+
+    # ---- ownership -----------------------------------------------------------------------------------------
+    def _gemm_units(self) -> List[Tuple[int, int]]:
+        """(offset, numel) of every GEMM weight in arena order, q|k|v fused into one unit (one wgrad GEMM each)."""
+        lay, d = self.layout, self.layout.dims
+        units = []
+        for l in range(d.n_layers):
+            p = f"distilbert.transformer.layer.{l}."
+            units.append((lay.qkv_weight_offset(l), 3 * d.dim * d.dim))
+            for name in ("attention.out_lin.weight", "ffn.lin1.weight", "ffn.lin2.weight"):
+                units.append((lay.offsets[p + name], lay.numel(p + name)))
+        return units
+
+    def _partition(self):
+        lay, G = self.layout, self.world
+        units = self._gemm_units()
+        total = lay.gemm_end
+        bounds = [0]
+        acc = 0
+        for off, n in units:  # contiguous, tensor-aligned ranges of roughly equal size
+            acc += n
+            while len(bounds) < G and acc >= total * len(bounds) / G:
+                bounds.append(off + n)
+        while len(bounds) < G:
+            bounds.append(total)
+        bounds.append(total)
+        bounds = bounds[: G + 1]
+        bounds[-1] = total
+        r2 = lay.total - lay.gemm_end
+        r2b = [lay.gemm_end + (r2 * r // G) // 4 * 4 for r in range(G)] + [lay.total]
+        return bounds, r2b
+
+    def gemm_range(self, r: int) -> Tuple[int, int]:
+        return self.gemm_bounds[r], self.gemm_bounds[r + 1]
+
+    def r2_range(self, r: int) -> Tuple[int, int]:
+        return self.r2_bounds[r], self.r2_bounds[r + 1]
+
+    def gemm_owner(self, offset: int) -> int:
+        for r in range(self.world):
+            if self.gemm_bounds[r] <= offset < self.gemm_bounds[r + 1]:
+                return r
+        raise ValueError(offset)
+
+    # ---- views ---------------------------------------------------------------------------------------------
+    def param_tensor(self) -> torch.Tensor:
+        return self.param_buf.view(torch.float32, numel=self.layout.total)
+
+    def grad_tensor(self) -> torch.Tensor:
+        return self.grad_buf.view(torch.float32, numel=self.layout.total)
+
+    def mirror_tensor(self) -> torch.Tensor:
+        return self.mirror_buf.view(torch.bfloat16, numel=self.layout.gemm_end)
+
+    def pad_tensor(self) -> torch.Tensor:
+        return self.pad_buf.view(torch.int32, numel=64)
+
+    def owner_grad_view(self, offset: int, shape: Tuple[int, ...]) -> torch.Tensor:
+        """View of the gradient of the GEMM weight at ``offset`` inside its OWNER's gradient arena (peer memory when
+        the owner is another GPU): the destination of the wgrad TMA reduce-add."""
+        owner = self.gemm_owner(offset)
+        numel = 1
+        for s in shape:
+            numel *= s
+        return self._peer_grad_bufs[owner].view(torch.float32, offset_bytes=offset * 4, numel=numel).view(shape)
+
+    # ---- collectives used outside the step -------------------------------------------------------------------
+    def allgather_fp32_gemm_params(self, stream=None) -> None:
+        """After training: every rank pushes the fp32 master values of the GEMM weights it owns to all peers, so that
+        each rank holds a complete fp32 ``state_dict`` (checkpoints, inter-client FedAvg)."""
+        import torch.distributed as dist
+
+        lo, hi = self.gemm_range(self.rank)
+        if hi > lo:
+            for k in range(self.world):
+                if k != self.rank:
+                    nv.fedavg_local([self.param_ptrs[self.rank] + lo * 4], self.param_ptrs[k] + lo * 4, hi - lo,
+                                    weights=[1.0], stream=stream)
+        torch.cuda.current_stream().synchronize()
+        dist.barrier(group=self._dist_group)
+
+    def reset_barrier_flags(self) -> None:
+        """Host-synchronised clear of the barrier words (needed whenever the device step counter is rewound)."""
+        import torch.distributed as dist
+
+        torch.cuda.synchronize()
+        dist.barrier(group=self._dist_group)
+        self.pad_tensor()[48:64].zero_()
+        torch.cuda.synchronize()
+        dist.barrier(group=self._dist_group)
+
+    def error_flag(self) -> int:
+        return int(self.pad_tensor()[33].item())
+
+    def close(self) -> None:
+        for b in self._opened:
+            b.free()
+        self._opened = []
+        for b in (self.param_buf, self.grad_buf, self.mirror_buf, self.pad_buf):
+            b.free()

@@ -42,7 +42,8 @@ int dcad_version(void);
  * epilogue).
  *   D[M,N] = epilogue( sum_k A(m,k) * B(n,k) )
  * A is [M][lda] when a_major == DCAD_MAJOR_K, [K][lda] when DCAD_MAJOR_MN; likewise B with N.
- * D is bf16 (out_fp32 == 0) or fp32 (out_fp32 == 1, epilogue must be DCAD_EPI_NONE).
+ * D is bf16 (out_fp32 == 0) or fp32 (out_fp32 == 1 store, 2 = TMA reduce-add into D even without split-K, so D may
+ * be a buffer on a peer GPU that several GPUs accumulate into); fp32 output requires DCAD_EPI_NONE.
  * split_k > 1 (fp32 D only): the reduction is split over several CTAs that accumulate into D with TMA reduce-add;
  * D must be zero on entry.  block_n: 0 = auto, else 64/128/192/256.  max_ctas: 0 = #SMs.
  * Replaces the cuBLAS calls behind nn.Linear forward/backward in the reference (client1.py:61,109).
@@ -131,6 +132,17 @@ int dcad_adam_step(float* p, float* g, float* m, float* v, void* p_bf16, int64_t
                    int64_t bf16_end, int64_t zero_begin, int64_t zero_end, float lr, float beta1, float beta2,
                    float eps, const uint64_t* state, void* stream);
 int dcad_step_advance(uint64_t* state, void* stream);
+/* Intra-client data parallelism (no counterpart in the reference, which has no DP): sharded Adam over the arena
+ * elements [begin, end) this rank owns, gradients scaled by grad_scale (1/G after a sum over the group), with the
+ * parameter all-gather fused in: updated bf16 GEMM weights are stored into every peer's mirror and updated fp32
+ * values in [push32_begin, push32_end) into every peer's arena.  peer_p / peer_bf16: HOST arrays of n_peers pointers. */
+int dcad_adam_step_dp(float* p, float* g, float* m, float* v, int64_t begin, int64_t end, int64_t bf16_begin,
+                      int64_t bf16_end, int64_t push32_begin, int64_t push32_end, float lr, float beta1, float beta2,
+                      float eps, float grad_scale, const uint64_t* state, const void* const* peer_p,
+                      const void* const* peer_bf16, int n_peers, int self, void* stream);
+/* One-block barrier across the GPUs of a group through their signal pads (words [48,64)); the epoch is
+ * state[1] * 8 + phase + 1, read on the device, so the launch can be replayed from a CUDA graph.  n <= 8. */
+int dcad_xgpu_barrier(const void* const* pads, int rank, int n, const uint64_t* state, uint32_t phase, void* stream);
 
 /* ---- fused attention, seq <= 128, head_dim 64 (HF modeling_distilbert.py:126-151 + attention dropout) ----
  * qkv [B*S, 3*H*64] bf16 (Q | K | V), ctx [B*S, H*64] bf16, lse2 [B*H*128] fp32, lens [B] valid key counts or NULL. */

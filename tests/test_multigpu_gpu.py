@@ -76,3 +76,15 @@ def test_multiprocess_ipc_fedavg_and_bench():
     r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-3000:])
     assert "FEDAVG_IPC_OK" in r.stdout
+
+
+def test_intra_client_data_parallel_matches_single_gpu():
+    """Fused DP (wgrad TMA reduce-add into the owner's arena, sharded Adam, fused all-gather) on 2 GPUs vs a
+    single-GPU step on the concatenated batch."""
+    _need(2)
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", str(29850 + os.getpid() % 100), os.path.join(ROOT, "tools", "mp_dp_check.py")]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-3000:])
+    assert "DP_OK" in r.stdout

@@ -1,0 +1,105 @@
+"""torchrun worker: intra-client data parallelism (fused wgrad reduce-scatter, sharded Adam, fused all-gather) checked
+against a single-GPU step on the concatenated batch.  Small model, dropout off.  Prints DP_OK on rank 0."""
+import dataclasses
+import os
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200.models.arena import ArenaLayout, ModelDims  # noqa: E402
+from detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200.models.engine import B200Engine  # noqa: E402
+from detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200.parallel.dp import DPGroup  # noqa: E402
+
+
+def batch(B, S, vocab, seed):
+    g = torch.Generator().manual_seed(seed)
+    ids = torch.randint(0, vocab, (B, S), generator=g)
+    lens = torch.randint(S // 4, S + 1, (B,), generator=g)
+    labels = torch.randint(0, 2, (B,), generator=g)
+    return ids.int(), lens.int(), labels.int()
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    full = os.environ.get("DP_FULL", "0") == "1"
+    dims = ModelDims() if full else ModelDims(vocab_size=1000, max_position=128, dim=256, n_layers=2, n_heads=4,
+                                              hidden_dim=512, dropout=0.0, attention_dropout=0.0, head_dropout=0.0)
+    if full:
+        dims = dataclasses.replace(dims, dropout=0.0, attention_dropout=0.0, head_dropout=0.0)
+    Bl, S = 8, 128
+    lay = ArenaLayout(dims)
+    grp = DPGroup(rank, world, lay)
+    assert grp.gemm_bounds[0] == 0 and grp.gemm_bounds[-1] == lay.gemm_end and grp.r2_bounds[-1] == lay.total
+    eng = B200Engine(dims, batch=Bl, seq=S, device=local, init_seed=11, lr=1e-3, dp=grp)
+    ids, lens, labels = batch(Bl * world, S, dims.vocab_size, seed=5)
+    sl = slice(rank * Bl, (rank + 1) * Bl)
+    eng.set_batch(ids[sl].to(dev), lens[sl].to(dev), labels[sl].to(dev))
+    p0 = eng.arena.flat.clone()
+
+    # single-GPU oracle on the concatenated batch (every rank computes it redundantly)
+    ref = B200Engine(dims, batch=Bl * world, seq=S, device=local, init_seed=11, lr=1e-3)
+    ref.set_batch(ids.to(dev), lens.to(dev), labels.to(dev))
+    assert torch.equal(ref.arena.flat, p0)
+
+    for step in range(3):
+        eng.train_step()
+        ref.train_step()
+    torch.cuda.synchronize()
+    dist.barrier()
+    assert grp.error_flag() == 0
+    grp.allgather_fp32_gemm_params()
+    got, exp = eng.arena.flat, ref.arena.flat
+    # Adam's first steps move every weight by ~lr regardless of the gradient's size, so compare the UPDATE directions:
+    # the fraction of parameters whose 3-step update differs by more than half a step is what matters
+    upd_g, upd_e = got - p0, exp - p0
+    moved = upd_e.abs() > 0.5e-3
+    bad = ((upd_g - upd_e).abs() > 1.0e-3) & moved
+    frac_bad = bad.float().mean().item()
+    cos = torch.nn.functional.cosine_similarity(upd_g[moved], upd_e[moved], dim=0).item()
+    # bf16 mirrors must be identical on every rank and equal to the owner's fp32 values rounded
+    mir = eng.arena.bf16.float()
+    allm = [torch.empty_like(mir) for _ in range(world)]
+    dist.all_gather(allm, mir)
+    same_mirror = all(torch.equal(allm[0], m) for m in allm)
+    r2 = slice(lay.gemm_end, lay.total)
+    allp = [torch.empty_like(got[r2]) for _ in range(world)]
+    dist.all_gather(allp, got[r2].contiguous())
+    same_r2 = all(torch.equal(allp[0], p) for p in allp)
+    loss_dp, _ = eng.read_loss()
+    loss_ref, _ = ref.read_loss()
+    ok = frac_bad < 0.02 and cos > 0.98 and same_mirror and same_r2
+    print(f"rank {rank}: frac_bad={frac_bad:.4f} cos={cos:.4f} same_mirror={same_mirror} same_r2={same_r2} "
+          f"loss_dp(local)={loss_dp:.4f} loss_ref={loss_ref:.4f} bounds={grp.gemm_bounds}", flush=True)
+    assert ok
+
+    # captured graph + timing
+    eng.capture()
+    for _ in range(5):
+        eng.train_step()
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(20):
+        eng.train_step()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / 20], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    assert grp.error_flag() == 0
+    if rank == 0:
+        print(f"DP graph step: {t.item():.3f} ms ({world} GPUs x batch {Bl})", flush=True)
+        print("DP_OK", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
