@@ -49,6 +49,7 @@ def parse_args():
     ap.add_argument("--seq", type=int, default=128)
     ap.add_argument("--pool", type=int, default=8, help="distinct synthetic batches cycled through")
     ap.add_argument("--no-fedavg", action="store_true")
+    ap.add_argument("--dp", type=int, default=1, help="GPUs per federated client (intra-client data parallelism)")
     ap.add_argument("--no-graph", action="store_true")
     return ap.parse_args()
 
@@ -83,16 +84,21 @@ def run_ours(args, rank: int, world: int, local_rank: int) -> dict:
     layout = arena_mod.ArenaLayout(dims)
 
     group = None
+    dpg = None
     flat = bf16 = None
-    if world > 1 and not args.no_fedavg:
+    if args.dp > 1:
+        dp_mod = importlib.import_module(f"{PKG}.parallel.dp")
+        dpg = dp_mod.DPGroup.build(rank, world, args.dp, layout)
+    elif world > 1 and not args.no_fedavg:
         p2p = importlib.import_module(f"{PKG}.parallel.p2p")
         try:  # symmetric-memory allocation also carries an NVLink multicast mapping (NVLS) when the host exposes it
             group = p2p.SymmPeerGroup(rank, world, layout.total, layout.gemm_end)
         except Exception:  # noqa: BLE001
             group = p2p.PeerGroup(rank, world, layout.total, layout.gemm_end)
         flat, bf16 = group.arena_tensor(), group.mirror_tensor()
-    eng = eng_mod.B200Engine(dims, batch=B, seq=S, device=local_rank, init_seed=rank, seed=1234 + rank,
-                             flat_params=flat, bf16_params=bf16)
+    client_id = rank // max(args.dp, 1)
+    eng = eng_mod.B200Engine(dims, batch=B, seq=S, device=local_rank, init_seed=client_id, seed=1234 + rank,
+                             flat_params=flat, bf16_params=bf16, dp=dpg)
 
     # synthetic CICIDS-shaped token batches: a device-resident pool (device-timed metric) and a pinned host pool
     # (end-to-end metric)
@@ -158,7 +164,10 @@ def run_ours(args, rank: int, world: int, local_rank: int) -> dict:
         "impl": "ours",
         "config": {"model": "DDoSClassifier (DistilBERT-base 6L/768d/12h + Linear(768,2)), 66.36M params",
                    "global_batch": B * world, "per_client_batch": B, "seq_len": S,
-                   "parallelism": f"fed{world} (one federated client per GPU, FedAvg over NVSwitch peer memory)",
+                   "parallelism": (f"fed{world} (one federated client per GPU, FedAvg over NVSwitch peer memory)"
+                                   if args.dp <= 1 else
+                                   f"fed{world // args.dp} x dp{args.dp} (each client spans {args.dp} GPUs: wgrad "
+                                   f"reduce-scatter by TMA reduce-add into the owner GPU, sharded Adam, fused all-gather)"),
                    "optimizer": "Adam lr 2e-5 fp32 master/moments, bf16 tensor-core compute, dropout 0.1/0.1/0.3 on",
                    "l2": "no explicit flush: each step streams ~1.4 GB (fp32 params/grads/moments 1.06 GB + bf16 "
                          "weights + saved activations) >> 126 MB L2",
@@ -172,6 +181,29 @@ def run_ours(args, rank: int, world: int, local_rank: int) -> dict:
         "final_loss": loss,
         "clocks": clk,
     }
+
+    if dpg is not None and world // args.dp > 1 and not args.no_fedavg:
+        # inter-client FedAvg for multi-GPU clients: gather the sharded fp32 GEMM weights, then the grouped kernel
+        iters = 5
+
+        def dp_round():
+            dpg.allgather_fp32_gemm_params()
+            dpg.fedavg_clients()
+
+        for _ in range(2):
+            dp_round()
+        barrier()
+        e0.record()
+        for _ in range(iters):
+            dp_round()
+        e1.record()
+        torch.cuda.synchronize(dev)
+        out["fedavg"] = {"round_latency_ms": max_over_ranks(e0.elapsed_time(e1) / iters),
+                         "kernel": "fp32 GEMM-weight all-gather inside each client group + fedavg_p2p_grouped "
+                                   f"({world // args.dp} source arenas -> {world} GPUs, bf16 mirrors fused)",
+                         "handshake_error_flag": dpg.error_flag()}
+    if dpg is not None:
+        out["dp_handshake_error_flag"] = dpg.error_flag()
 
     # ---- FedAvg round over NVSwitch (the other half of the headline metric) ----
     if group is not None:

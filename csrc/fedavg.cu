@@ -35,6 +35,8 @@ struct FedArgs {
     uint32_t* pad[FED_MAX];
     float weight[FED_MAX];
     int use_weights;
+    void* dst[FED_MAX];  // two-shot destinations (defaults to `arena`); may be a superset of the sources
+    int n_dst;           // number of ranks / destinations / pads
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -172,19 +174,23 @@ template <bool IN_BF16>
 __global__ void __launch_bounds__(512)
 fedavg_p2p_kernel(const FedArgs a, int rank, int n, int64_t num_vecs, int mode, int64_t bf16_begin, int64_t bf16_end,
                   uint32_t epoch) {
+    // n = number of SOURCE arenas that are averaged; a.n_dst = number of ranks (kernels) taking part: they share the
+    // shards, the handshake and -- two-shot -- all receive the result.  Normally the two coincide; a data-parallel
+    // client group contributes one source but several ranks.
     constexpr int E = VecIO<IN_BF16>::ELEMS;
+    const int nr = a.n_dst;
     uint32_t* my_pad = a.pad[rank];
     // start barrier: every peer's arena is final (their launch is stream-ordered after their local training)
-    if (blockIdx.x == 0 && threadIdx.x < n) st_release_sys(a.pad[threadIdx.x] + PAD_READY + rank, epoch);
-    if (threadIdx.x < n) {
+    if (blockIdx.x == 0 && threadIdx.x < nr) st_release_sys(a.pad[threadIdx.x] + PAD_READY + rank, epoch);
+    if (threadIdx.x < nr) {
         if (!spin_until_ge(my_pad + PAD_READY + threadIdx.x, epoch)) my_pad[PAD_ERROR] = 1;
     }
     __syncthreads();
 
     int64_t lo = 0, hi = num_vecs;
     if (mode == DCAD_FED_TWO_SHOT) {
-        lo = num_vecs * rank / n;
-        hi = num_vecs * (rank + 1) / n;
+        lo = num_vecs * rank / nr;
+        hi = num_vecs * (rank + 1) / nr;
     }
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
     for (int64_t v0 = lo + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; v0 < hi; v0 += stride * FED_U) {
@@ -198,8 +204,8 @@ fedavg_p2p_kernel(const FedArgs a, int rank, int n, int64_t num_vecs, int mode, 
         for (int u = 0; u < FED_U; ++u) {
             if (!ok[u]) continue;
             if (mode == DCAD_FED_TWO_SHOT) {
-                for (int k = 0; k < n; ++k) {
-                    VecIO<IN_BF16>::store(a.arena[k], vec[u], acc[u]);
+                for (int k = 0; k < nr; ++k) {
+                    VecIO<IN_BF16>::store(a.dst[k], vec[u], acc[u]);
                     store_mirror<IN_BF16>(a.mirror[k], vec[u] * E, bf16_begin, bf16_end, acc[u]);
                 }
             } else {
@@ -216,8 +222,8 @@ fedavg_p2p_kernel(const FedArgs a, int rank, int n, int64_t num_vecs, int mode, 
         if (prev == gridDim.x - 1) {
             my_pad[PAD_COUNTER] = 0;
             __threadfence_system();
-            for (int k = 0; k < n; ++k) st_release_sys(a.pad[k] + PAD_DONE + rank, epoch);
-            for (int k = 0; k < n; ++k)
+            for (int k = 0; k < nr; ++k) st_release_sys(a.pad[k] + PAD_DONE + rank, epoch);
+            for (int k = 0; k < nr; ++k)
                 if (!spin_until_ge(my_pad + PAD_DONE + k, epoch)) my_pad[PAD_ERROR] = 1;
         }
     }
@@ -299,6 +305,8 @@ static int fill_args(FedArgs& fa, const void* const* arenas, const void* const* 
         fa.weight[k] = (weights && k < n) ? weights[k] : 0.f;
     }
     fa.use_weights = weights ? 1 : 0;
+    for (int k = 0; k < FED_MAX; ++k) fa.dst[k] = fa.arena[k];
+    fa.n_dst = n;
     return 0;
 }
 
@@ -350,6 +358,41 @@ extern "C" int dcad_fedavg_p2p(const void* const* arenas, const void* const* out
         fedavg_p2p_kernel<true><<<(int)blocks, 512, 0, s>>>(fa, rank, n_clients, num_vecs, mode, bf16_begin, bf16_end, epoch);
     else
         fedavg_p2p_kernel<false><<<(int)blocks, 512, 0, s>>>(fa, rank, n_clients, num_vecs, mode, bf16_begin, bf16_end, epoch);
+    return (int)cudaGetLastError();
+}
+
+// Two-shot FedAvg where the averaged SOURCES (one arena per client) are a subset of the participating RANKS: every
+// rank reduces 1/n_ranks of the arena from the n_src sources and pushes it to all n_ranks destinations.  Used when a
+// client spans several GPUs (intra-client data parallelism): one representative arena per client is averaged, all
+// GPUs of all clients receive the result and its bf16 copy.  All arrays are HOST arrays.
+extern "C" int dcad_fedavg_p2p_grouped(const void* const* srcs, int n_src, const void* const* dsts,
+                                       const void* const* mirrors, const void* const* pads, int n_ranks,
+                                       const float* weights, int rank, int64_t count, int in_bf16, int64_t bf16_begin,
+                                       int64_t bf16_end, uint32_t epoch, int max_ctas, void* stream) {
+    if (count <= 0) return 0;
+    const int E = in_bf16 ? 8 : 4;
+    if (count % E || (bf16_begin & 3) || (bf16_end & 3)) return DCAD_ERR_BAD_ALIGNMENT;
+    if (n_src < 1 || n_src > FED_MAX || n_ranks < 1 || n_ranks > FED_MAX) return DCAD_ERR_TOO_LARGE;
+    if (rank < 0 || rank >= n_ranks || pads == nullptr || dsts == nullptr) return DCAD_ERR_BAD_ARGUMENT;
+    FedArgs fa;
+    int rc = fill_args(fa, srcs, nullptr, nullptr, nullptr, weights, n_src);
+    if (rc) return rc;
+    for (int k = 0; k < FED_MAX; ++k) {
+        fa.dst[k] = k < n_ranks ? const_cast<void*>(dsts[k]) : nullptr;
+        fa.mirror[k] = (mirrors && k < n_ranks) ? const_cast<void*>(mirrors[k]) : nullptr;
+        fa.pad[k] = k < n_ranks ? reinterpret_cast<uint32_t*>(const_cast<void*>(pads[k])) : nullptr;
+    }
+    fa.n_dst = n_ranks;
+    const int64_t num_vecs = count / E;
+    int64_t blocks = ((num_vecs + n_ranks - 1) / n_ranks + 511) / 512;
+    const int64_t cap = max_ctas > 0 ? max_ctas : 148;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (in_bf16)
+        fedavg_p2p_kernel<true><<<(int)blocks, 512, 0, s>>>(fa, rank, n_src, num_vecs, DCAD_FED_TWO_SHOT, bf16_begin, bf16_end, epoch);
+    else
+        fedavg_p2p_kernel<false><<<(int)blocks, 512, 0, s>>>(fa, rank, n_src, num_vecs, DCAD_FED_TWO_SHOT, bf16_begin, bf16_end, epoch);
     return (int)cudaGetLastError();
 }
 

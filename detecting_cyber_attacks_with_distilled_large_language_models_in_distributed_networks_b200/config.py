@@ -47,7 +47,7 @@ class FedConfig:
     timeout: float = 300.0
     accept_timeout: Optional[float] = None
     max_retries: int = 5
-    gzip_level: int = 1
+    gzip_level: int = 0
     min_clients: Optional[int] = None  # quorum for the socket server (default: all)
     # outputs
     out_dir: str = "."

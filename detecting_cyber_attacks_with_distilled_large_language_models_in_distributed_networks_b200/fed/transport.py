@@ -30,7 +30,7 @@ class SocketTransport(Transport):
     name = "socket"
 
     def __init__(self, host="localhost", port_recv=st.PORT_RECEIVE, port_send=st.PORT_SEND, timeout=st.TIMEOUT,
-                 max_retries=5, gzip_level=1, log: Optional[EventLog] = None):
+                 max_retries=5, gzip_level=0, log: Optional[EventLog] = None):
         self.host, self.port_recv, self.port_send = host, port_recv, port_send
         self.timeout, self.max_retries, self.gzip_level = timeout, max_retries, gzip_level
         self.log = log

@@ -97,6 +97,7 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("dcad_attn_bwd", [P, P, P, P, P, P, I, I, I, F, P, U32, P])
     sig("dcad_fedavg_local", [P, P, P, I, L64, I, P, L64, L64, I, P])
     sig("dcad_fedavg_p2p", [P, P, P, P, P, I, I, L64, I, I, L64, L64, U32, I, P])
+    sig("dcad_fedavg_p2p_grouped", [P, I, P, P, P, I, P, I, L64, I, L64, L64, U32, I, P])
     sig("dcad_fedavg_nvls", [P, P, P, I, I, L64, L64, L64, U32, I, P])
     sig("dcad_p2p_alloc", [P, ctypes.c_size_t])
     sig("dcad_p2p_free", [P])
@@ -322,6 +323,14 @@ def fedavg_p2p(arena_ptrs, pad_ptrs, rank, count, epoch, *, out_ptrs=None, mirro
                                 _ptr_array(pad_ptrs), _float_array(weights), rank, len(arena_ptrs), count,
                                 1 if in_bf16 else 0, mode, bf16_begin, bf16_end, epoch, max_ctas,
                                 stream_ptr(stream)), "dcad_fedavg_p2p")
+
+
+def fedavg_p2p_grouped(src_ptrs, dst_ptrs, mirror_ptrs, pad_ptrs, rank, count, epoch, *, weights=None, in_bf16=False,
+                       bf16_begin=0, bf16_end=0, max_ctas=0, stream=None):
+    check(lib().dcad_fedavg_p2p_grouped(_ptr_array(src_ptrs), len(src_ptrs), _ptr_array(dst_ptrs),
+                                        _ptr_array(mirror_ptrs), _ptr_array(pad_ptrs), len(dst_ptrs),
+                                        _float_array(weights), rank, count, 1 if in_bf16 else 0, bf16_begin, bf16_end,
+                                        epoch, max_ctas, stream_ptr(stream)), "dcad_fedavg_p2p_grouped")
 
 
 def fedavg_nvls(mc_arena_ptr, mc_mirror_ptr, pad_ptrs, rank, count, epoch, *, bf16_begin=0, bf16_end=0, max_ctas=0,

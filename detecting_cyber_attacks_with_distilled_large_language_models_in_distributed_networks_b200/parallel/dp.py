@@ -29,13 +29,25 @@ PAD_BYTES = 64 * 4
 
 
 class DPGroup:
-    def __init__(self, rank: int, world: int, layout: ArenaLayout, dist_group=None):
+    """Buffers and ownership map of one data-parallel client group.
+
+    ``members`` are the global ranks of this client's GPUs (this process must be one of them).  IPC handles are
+    exchanged over ``ipc_group`` (default: the world), so every rank maps every other rank's buffers once; the DP
+    kernels use the members' subset, the inter-client FedAvg uses all of them.
+    """
+
+    def __init__(self, rank: int, world: int, layout: ArenaLayout, dist_group=None, members: Optional[List[int]] = None,
+                 member_group=None):
         import torch.distributed as dist
 
-        if world > 8:
+        self.global_rank, self.global_world = rank, world
+        self.members = list(range(world)) if members is None else list(members)
+        if rank not in self.members:
+            raise ValueError("this rank is not a member of its own client group")
+        if len(self.members) > 8:
             raise ValueError("a data-parallel client group spans at most 8 GPUs")
-        self.rank, self.world, self.layout = rank, world, layout
-        self._dist_group = dist_group
+        self.rank, self.world, self.layout = self.members.index(rank), len(self.members), layout
+        self._dist_group = member_group if member_group is not None else dist_group
         n = layout.total
         self.param_buf = nv.RawDeviceBuffer(nv.p2p_alloc(n * 4), n * 4)
         self.grad_buf = nv.RawDeviceBuffer(nv.p2p_alloc(n * 4), n * 4)
@@ -46,19 +58,57 @@ class DPGroup:
         gathered: List[Optional[dict]] = [None] * world
         dist.all_gather_object(gathered, mine, group=dist_group)
         self._opened: List[nv.RawDeviceBuffer] = []
-        self.param_ptrs, self.grad_ptrs, self.mirror_ptrs, self.pad_ptrs = [], [], [], []
+        self.all_param_ptrs, self.all_grad_ptrs, self.all_mirror_ptrs, self.all_pad_ptrs = [], [], [], []
         for r, h in enumerate(gathered):
-            for name, lst, own in (("param", self.param_ptrs, self.param_buf), ("grad", self.grad_ptrs, self.grad_buf),
-                                   ("mirror", self.mirror_ptrs, self.mirror_buf), ("pad", self.pad_ptrs, self.pad_buf)):
+            for name, lst, own in (("param", self.all_param_ptrs, self.param_buf),
+                                   ("grad", self.all_grad_ptrs, self.grad_buf),
+                                   ("mirror", self.all_mirror_ptrs, self.mirror_buf),
+                                   ("pad", self.all_pad_ptrs, self.pad_buf)):
                 if r == rank:
                     lst.append(own.ptr)
+                elif name == "grad" and r not in self.members:
+                    lst.append(0)  # gradients are only ever exchanged inside a client group
                 else:
                     p = nv.p2p_ipc_open(h[name])
                     self._opened.append(nv.RawDeviceBuffer(p, 0, owner=False, ipc=True))
                     lst.append(p)
+        pick = lambda lst: [lst[g] for g in self.members]  # noqa: E731
+        self.param_ptrs, self.grad_ptrs = pick(self.all_param_ptrs), pick(self.all_grad_ptrs)
+        self.mirror_ptrs, self.pad_ptrs = pick(self.all_mirror_ptrs), pick(self.all_pad_ptrs)
         self._peer_grad_bufs = [nv.RawDeviceBuffer(p, n * 4, owner=False) for p in self.grad_ptrs]
         self.gemm_bounds, self.r2_bounds = self._partition()
+        self._fed_epoch = 0
+        self._world_group = dist_group
         dist.barrier(group=dist_group)
+
+    @classmethod
+    def build(cls, rank: int, world: int, gpus_per_client: int, layout: ArenaLayout) -> "DPGroup":
+        """Collective over the world: creates one process group per client and returns this rank's DPGroup."""
+        import torch.distributed as dist
+
+        if world % gpus_per_client:
+            raise ValueError("world size must be a multiple of gpus_per_client")
+        mine_members, mine_group = None, None
+        for c in range(world // gpus_per_client):
+            members = list(range(c * gpus_per_client, (c + 1) * gpus_per_client))
+            g = dist.new_group(members)  # every rank must take part in every new_group call
+            if rank in members:
+                mine_members, mine_group = members, g
+        return cls(rank, world, layout, dist_group=None, members=mine_members, member_group=mine_group)
+
+    @property
+    def num_clients(self) -> int:
+        return self.global_world // self.world
+
+    def fedavg_clients(self, weights=None, max_ctas: int = 0, stream=None) -> None:
+        """Inter-client FedAvg when clients span several GPUs: the first GPU of every client contributes its (complete)
+        fp32 arena, all GPUs of all clients receive the average and its bf16 copy.  Call
+        ``allgather_fp32_gemm_params()`` first so the contributed arenas are complete."""
+        self._fed_epoch += 1
+        reps = [self.all_param_ptrs[c * self.world] for c in range(self.num_clients)]
+        nv.fedavg_p2p_grouped(reps, self.all_param_ptrs, self.all_mirror_ptrs, self.all_pad_ptrs, self.global_rank,
+                              self.layout.total, self._fed_epoch, weights=weights, bf16_begin=0,
+                              bf16_end=self.layout.gemm_end, max_ctas=max_ctas, stream=stream)
 
     # ---- ownership -----------------------------------------------------------------------------------------
     def _gemm_units(self) -> List[Tuple[int, int]]:

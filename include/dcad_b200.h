@@ -169,6 +169,13 @@ int dcad_fedavg_p2p(const void* const* arenas, const void* const* outs, const vo
                     int in_bf16, int mode, int64_t bf16_begin, int64_t bf16_end, uint32_t epoch, int max_ctas,
                     void* stream);
 
+/* Two-shot FedAvg with separate source and destination sets: the n_src arenas in `srcs` (one per client) are
+ * averaged, all n_ranks participating GPUs (dsts / mirrors / pads, one entry per rank) receive the result.  For
+ * clients that span several GPUs. */
+int dcad_fedavg_p2p_grouped(const void* const* srcs, int n_src, const void* const* dsts, const void* const* mirrors,
+                            const void* const* pads, int n_ranks, const float* weights, int rank, int64_t count,
+                            int in_bf16, int64_t bf16_begin, int64_t bf16_end, uint32_t epoch, int max_ctas,
+                            void* stream);
 /* NVLS variant: mc_arena / mc_mirror are MULTICAST addresses mapping every client's fp32 arena / bf16 mirror
  * (cuMulticast* objects, e.g. from torch symmetric memory); the NVSwitch sums the N copies (multimem.ld_reduce) and
  * replicates the averaged shard (multimem.st).  fp32 arenas only, unweighted; in-switch summation order is

@@ -35,16 +35,18 @@ def main():
         dims = dataclasses.replace(dims, dropout=0.0, attention_dropout=0.0, head_dropout=0.0)
     Bl, S = 8, 128
     lay = ArenaLayout(dims)
-    grp = DPGroup(rank, world, lay)
+    G = int(os.environ.get("DP_GROUP", world))
+    grp = DPGroup.build(rank, world, G, lay) if G != world else DPGroup(rank, world, lay)
+    client = rank // G
     assert grp.gemm_bounds[0] == 0 and grp.gemm_bounds[-1] == lay.gemm_end and grp.r2_bounds[-1] == lay.total
     eng = B200Engine(dims, batch=Bl, seq=S, device=local, init_seed=11, lr=1e-3, dp=grp)
-    ids, lens, labels = batch(Bl * world, S, dims.vocab_size, seed=5)
-    sl = slice(rank * Bl, (rank + 1) * Bl)
+    ids, lens, labels = batch(Bl * G, S, dims.vocab_size, seed=5 + client)
+    sl = slice(grp.rank * Bl, (grp.rank + 1) * Bl)
     eng.set_batch(ids[sl].to(dev), lens[sl].to(dev), labels[sl].to(dev))
     p0 = eng.arena.flat.clone()
 
     # single-GPU oracle on the concatenated batch (every rank computes it redundantly)
-    ref = B200Engine(dims, batch=Bl * world, seq=S, device=local, init_seed=11, lr=1e-3)
+    ref = B200Engine(dims, batch=Bl * G, seq=S, device=local, init_seed=11, lr=1e-3)
     ref.set_batch(ids.to(dev), lens.to(dev), labels.to(dev))
     assert torch.equal(ref.arena.flat, p0)
 
@@ -67,11 +69,11 @@ def main():
     mir = eng.arena.bf16.float()
     allm = [torch.empty_like(mir) for _ in range(world)]
     dist.all_gather(allm, mir)
-    same_mirror = all(torch.equal(allm[0], m) for m in allm)
+    same_mirror = all(torch.equal(allm[client * G], m) for m in allm[client * G:(client + 1) * G])
     r2 = slice(lay.gemm_end, lay.total)
     allp = [torch.empty_like(got[r2]) for _ in range(world)]
     dist.all_gather(allp, got[r2].contiguous())
-    same_r2 = all(torch.equal(allp[0], p) for p in allp)
+    same_r2 = all(torch.equal(allp[client * G], p) for p in allp[client * G:(client + 1) * G])
     loss_dp, _ = eng.read_loss()
     loss_ref, _ = ref.read_loss()
     ok = frac_bad < 0.02 and cos > 0.98 and same_mirror and same_r2
@@ -79,6 +81,22 @@ def main():
           f"loss_dp(local)={loss_dp:.4f} loss_ref={loss_ref:.4f} bounds={grp.gemm_bounds}", flush=True)
     assert ok
 
+    if world // G > 1:
+        # inter-client FedAvg over client groups: every GPU must end with mean over clients of the clients' params
+        full_params = [torch.empty_like(got) for _ in range(world)]
+        dist.all_gather(full_params, got.contiguous())
+        expect = full_params[0].cpu().clone()
+        for c in range(1, world // G):
+            expect += full_params[c * G].cpu()
+        expect /= (world // G)
+        grp.fedavg_clients()
+        torch.cuda.synchronize()
+        dist.barrier()
+        assert grp.error_flag() == 0
+        assert torch.equal(eng.arena.flat.cpu(), expect), "grouped FedAvg mismatch"
+        assert torch.equal(eng.arena.bf16.cpu(), expect[: lay.gemm_end].bfloat16())
+        if rank == 0:
+            print("DP_FEDAVG_CLIENTS_OK", flush=True)
     # captured graph + timing
     eng.capture()
     for _ in range(5):
