@@ -51,7 +51,9 @@ def prepare_data(cfg: FedConfig, log: EventLog) -> Tuple[PackedSplit, PackedSpli
 
 
 def run_client(cfg: FedConfig, transport: Optional[Transport] = None, backend=None,
-               backend_kwargs: Optional[dict] = None) -> Dict[str, EvalResult]:
+               backend_kwargs: Optional[dict] = None, reporter: bool = True) -> Dict[str, EvalResult]:
+    """``reporter=False``: a non-leading GPU of a data-parallel client — it trains and aggregates (both are collective)
+    but leaves evaluation, CSV / PNG / checkpoint writing to the client's first GPU."""
     cid = cfg.client_id
     name = f"Client {cid}"
     os.makedirs(cfg.out_dir, exist_ok=True)
@@ -76,22 +78,28 @@ def run_client(cfg: FedConfig, transport: Optional[Transport] = None, backend=No
     for rnd in range(cfg.rounds):
         sfx = "" if rnd == 0 else f"_round{rnd + 1}"
         train_model(backend, train, cfg.local_epochs, seed=cfg.resolved_seed() + 1000 * rnd, log=log, name=name)
-        print(f"{name} evaluating local model on validation set...")
-        val_local = evaluate_model(backend, val, log, name, want_probs=False)
-        print(f"{name} evaluating local model on test set...")
-        local = evaluate_model(backend, test, log, name, want_probs=cfg.extra_curves)
-        save_metrics(local, out(f"client{cid}_local_metrics{sfx}.csv"))
-        if cfg.save_val_metrics:
-            save_metrics(val_local, out(f"client{cid}_local_val_metrics{sfx}.csv"))
-        torch.save(backend.state_dict(), model_path)
-        results[f"local{sfx}"] = local
+        sd = backend.state_dict()  # (collective inside a data-parallel client group)
+        local = None
+        if reporter:
+            print(f"{name} evaluating local model on validation set...")
+            val_local = evaluate_model(backend, val, log, name, want_probs=False)
+            print(f"{name} evaluating local model on test set...")
+            local = evaluate_model(backend, test, log, name, want_probs=cfg.extra_curves)
+            save_metrics(local, out(f"client{cid}_local_metrics{sfx}.csv"))
+            if cfg.save_val_metrics:
+                save_metrics(val_local, out(f"client{cid}_local_val_metrics{sfx}.csv"))
+            torch.save(sd, model_path)
+            results[f"local{sfx}"] = local
+        del sd
 
         aggregated: Optional[EvalResult] = None
         ok = False
         if transport is not None:
             with log.phase("federated aggregation", transport=transport.name, round=rnd + 1):
                 ok = transport.aggregate(backend)
-        if ok:
+        if ok and not reporter:
+            backend.state_dict()  # keep the collective call pattern of the reporter
+        if ok and reporter:
             log.say("updated with aggregated model")
             print(f"{name} evaluating aggregated model on validation set...")
             val_agg = evaluate_model(backend, val, log, name, want_probs=False)
@@ -104,7 +112,7 @@ def run_client(cfg: FedConfig, transport: Optional[Transport] = None, backend=No
             results[f"aggregated{sfx}"] = aggregated
         elif transport is not None:
             log.say("skipping aggregated model evaluation due to aggregation failure")
-        if cfg.plots:
+        if cfg.plots and reporter:
             with log.phase("plot generation"):
                 plot_evaluation(local, aggregated, out(f"client{cid}_plots{sfx}"), cid, extra_curves=cfg.extra_curves)
     log.say("Client shutdown")

@@ -18,7 +18,7 @@ from ..config import FedConfig
 from ..models.arena import ArenaLayout
 from ..ops import native as nv
 from .client import run_client
-from .transport import LoopbackTransport, NcclTransport, NvSwitchTransport, Transport
+from .transport import LoopbackTransport, NcclTransport, NvSwitchDPTransport, NvSwitchTransport, Transport
 
 
 def _env_int(k: str, d: int) -> int:
@@ -31,9 +31,10 @@ def _env_int(k: str, d: int) -> int:
 def launch(cfg: FedConfig) -> None:
     import torch.distributed as dist
 
-    if "RANK" not in os.environ and cfg.num_clients > 1:
+    G = max(1, cfg.gpus_per_client)
+    if "RANK" not in os.environ and cfg.num_clients * G > 1:
         port = 29600 + os.getpid() % 1000
-        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={cfg.num_clients}",
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={cfg.num_clients * G}",
                "--master-addr", "127.0.0.1", "--master-port", str(port), "-m", __package__.rsplit(".", 1)[0] + ".cli",
                "launch"] + sys.argv[2:]
         os.execv(sys.executable, cmd)
@@ -45,13 +46,24 @@ def launch(cfg: FedConfig) -> None:
             dist.init_process_group("nccl", device_id=torch.device("cuda", local))
         else:
             dist.init_process_group("gloo")
-    ccfg = dataclasses.replace(cfg, client_id=rank + 1, num_clients=world)
+    if world % G:
+        raise ValueError("world size must be a multiple of --gpus-per-client")
+    ccfg = dataclasses.replace(cfg, client_id=rank // G + 1, num_clients=world // G)
+    reporter = rank % G == 0
     transport: Transport
     backend_kwargs = {}
     group = None
     if use_cuda:
         backend_kwargs["device"] = local
-    if world > 1 and use_cuda and cfg.transport.startswith("nvswitch"):
+    if G > 1:
+        if not use_cuda:
+            raise RuntimeError("--gpus-per-client > 1 needs the B200 backend")
+        from ..parallel.dp import DPGroup
+
+        dpg = DPGroup.build(rank, world, G, ArenaLayout(ccfg.model_dims()))
+        backend_kwargs.update(dp=dpg, init_seed=ccfg.client_id)
+        transport = NvSwitchDPTransport(dpg) if world // G > 1 else LoopbackTransport(1)
+    elif world > 1 and use_cuda and cfg.transport.startswith("nvswitch"):
         from ..parallel.p2p import ONE_SHOT, TWO_SHOT, PeerGroup
 
         layout = ArenaLayout(ccfg.model_dims())
@@ -66,10 +78,10 @@ def launch(cfg: FedConfig) -> None:
     else:
         transport = LoopbackTransport(1)
     try:
-        run_client(ccfg, transport, backend_kwargs=backend_kwargs)
+        run_client(ccfg, transport, backend_kwargs=backend_kwargs, reporter=reporter)
         if world > 1:
             dist.barrier()
-        if rank == 0:
+        if rank == 0 and reporter:
             # the server artefact: the aggregated model as a reference-compatible state_dict
             pth = os.path.join(cfg.out_dir, f"client{ccfg.client_id}_model.pth")
             if os.path.exists(pth):

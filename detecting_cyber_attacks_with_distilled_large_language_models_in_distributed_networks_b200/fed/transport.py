@@ -67,6 +67,24 @@ class NvSwitchTransport(Transport):
         self.group.close()
 
 
+class NvSwitchDPTransport(Transport):
+    """Clients that span several GPUs (``parallel/dp.py``): gather the sharded fp32 GEMM weights inside every client
+    group, then one grouped FedAvg kernel per GPU averages one arena per client into all GPUs of all clients."""
+    name = "nvswitch-dp"
+
+    def __init__(self, dpg, weights: Optional[Sequence[float]] = None):
+        self.dpg, self.weights = dpg, weights
+
+    def aggregate(self, backend) -> bool:
+        self.dpg.allgather_fp32_gemm_params()
+        self.dpg.fedavg_clients(self.weights)
+        torch.cuda.current_stream().synchronize()
+        return self.dpg.error_flag() == 0
+
+    def close(self) -> None:
+        self.dpg.close()
+
+
 class NcclTransport(Transport):
     name = "nccl"
 

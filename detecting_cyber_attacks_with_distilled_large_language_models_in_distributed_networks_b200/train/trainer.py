@@ -88,17 +88,20 @@ class B200Backend:
 
     def __init__(self, dims: ModelDims = ModelDims(), batch: int = 16, seq: int = 128, device: int = 0,
                  lr: float = 2e-5, seed: int = 0, init_seed: Optional[int] = 0, flat_params=None, bf16_params=None,
-                 capture: bool = True):
+                 capture: bool = True, dp=None):
         from ..models.engine import B200Engine
 
         self.dims, self.B, self.S = dims, batch, seq
+        self.dp = dp
         self.engine = B200Engine(dims, batch, seq, device, lr=lr, seed=seed, init_seed=init_seed,
-                                 flat_params=flat_params, bf16_params=bf16_params)
+                                 flat_params=flat_params, bf16_params=bf16_params, dp=dp)
         self.device = self.engine.device
         if capture:
             self.engine.capture()
 
     def state_dict(self):
+        if self.dp is not None:  # collective inside the client group: owners publish their fp32 GEMM weights
+            self.dp.allgather_fp32_gemm_params()
         return self.engine.state_dict()
 
     def load_state_dict(self, sd) -> None:
@@ -107,12 +110,31 @@ class B200Backend:
     def train_epoch(self, split: PackedSplit, generator: Optional[torch.Generator]) -> float:
         eng = self.engine
         eng.loss_accum.zero_()
+        if self.dp is not None:
+            return self._train_epoch_dp(split, generator)
         for ids, lens, labels in iterate_batches(split, self.B, shuffle=True, generator=generator):
             if ids.shape[0] == self.B:
                 eng.set_batch(ids, lens, labels)
                 eng.train_step()
             else:  # ragged tail batch: pad by repeating rows is wrong for the mean loss; run a smaller eager step
                 self._tail_step(ids, lens, labels)
+        loss, _ = eng.read_loss()
+        return loss
+
+    def _train_epoch_dp(self, split: PackedSplit, generator: Optional[torch.Generator]) -> float:
+        """Data-parallel client: the G GPUs draw the SAME permutation (same seed) and GPU r takes every G-th batch
+        slot, so a global step consumes G*B distinct samples.  All GPUs must run the same number of steps (the step
+        contains cross-GPU barriers), so the ragged tail of the epoch is dropped."""
+        eng, dp = self.engine, self.dp
+        n = len(split)
+        dev = split.input_ids.device
+        perm = torch.randperm(n, generator=generator).to(dev)
+        per_step = self.B * dp.world
+        steps = n // per_step
+        for i in range(steps):
+            ix = perm[i * per_step + dp.rank * self.B: i * per_step + (dp.rank + 1) * self.B]
+            eng.set_batch(split.input_ids[ix], split.lens[ix], split.labels[ix])
+            eng.train_step()
         loss, _ = eng.read_loss()
         return loss
 

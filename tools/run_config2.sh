@@ -8,7 +8,7 @@ KEEP="gpurun_out/config2_n${N}"
 rm -rf "$OUT" "$KEEP"; mkdir -p "$OUT" "$KEEP"
 PKG=detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200
 python -m torch.distributed.run --nnodes=1 --nproc-per-node "$N" --master-addr 127.0.0.1 --master-port 29533 \
-  -m $PKG.cli launch --num-clients "$N" --transport nvswitch --synthetic-rows "$ROWS" --data-path "$OUT/none.csv" \
+  -m $PKG.cli launch --num-clients "$((N / ${GPC:-1}))" --gpus-per-client "${GPC:-1}" --transport nvswitch --synthetic-rows "$ROWS" --data-path "$OUT/none.csv" \
   --data-fraction 0.5 --local-epochs "$EPOCHS" --rounds "$ROUNDS" --out-dir "$OUT" --event-log "$OUT/events.jsonl" \
   > "$OUT/stdout.log" 2> "$OUT/stderr.log" || { tail -30 "$OUT/stderr.log"; exit 1; }
 grep -E "Average Loss|Test Accuracy|federated aggregation" "$OUT/stdout.log" | head -40
