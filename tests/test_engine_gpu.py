@@ -61,8 +61,8 @@ def test_gradients_match_autograd_without_dropout():
     ref.load_state_dict(eng.state_dict())
     ids, lens, labels, mask = _batch(B, S, dims.vocab_size, seed=1)
     eng.set_batch(ids.int(), lens.int(), labels.int())
-    h = eng._forward(B, train=True)
-    nv.cls_head_train(h, S * dims.dim, eng.cw, eng.cb, eng.labels, B, eng.loss_accum, eng.logits, eng.d_cw, eng.d_cb,
+    h, stride = eng._forward(B, train=True)
+    nv.cls_head_train(h, stride, eng.cw, eng.cb, eng.labels, B, eng.loss_accum, eng.logits, eng.d_cw, eng.d_cb,
                       eng.dcls, cols=dims.dim)
     eng._backward()
     torch.cuda.synchronize()
