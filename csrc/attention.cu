@@ -176,24 +176,32 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
 // ------------------------------------------------------------------------------------------------
 // backward (same thread mapping as forward)
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(AT_THREADS, 1)
+// Two CTAs are resident per SM (B*H = 192 CTAs run as ONE wave on 148 SMs): 112 KB of tiles + a few barrier words of
+// dynamic shared memory and 256 TMEM columns each.  To get there, P's first slab reuses V's tile (V is dead once
+// dP = dO V^T has been issued) and dV / dK / dQ reuse the TMEM columns of S / dP (dead once every thread has pulled
+// its chunks into registers).  No static shared memory: the dynamic buffer is 1024-byte aligned by declaration.
+extern __shared__ __align__(1024) uint8_t smem_attn_bwd[];
+
+__global__ void __launch_bounds__(AT_THREADS, 2)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_dctx,
                 const __nv_bfloat16* __restrict__ ctx, const __nv_bfloat16* __restrict__ dctx,
                 const float* __restrict__ lse2, __nv_bfloat16* __restrict__ dqkv, const int32_t* __restrict__ lens,
                 int S, int H, float scale, uint32_t thresh, float keep_scale, const uint64_t* __restrict__ rng,
                 uint32_t stream_id) {
-    extern __shared__ uint8_t smem_raw[];
-    __shared__ __align__(8) uint64_t bar_load, bar_mma1, bar_mma2;
-    __shared__ uint32_t tmem_base_smem;
-
+    uint8_t* smem = smem_attn_bwd;
+    if ((smem_u32(smem) & 1023u) != 0u) __trap();  // the swizzled tiles need the declared alignment
     const int bh = blockIdx.x, b = bh / H, h = bh % H;
     const int tid = threadIdx.x, warp = tid >> 5;
     const int row = tid & (AT_S - 1), hsel = tid >> 7;
-    uint8_t* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw));
-    uint8_t* sQ = smem; uint8_t* sK = smem + TILE_BYTES; uint8_t* sV = smem + 2 * TILE_BYTES;
-    uint8_t* sdO = smem + 3 * TILE_BYTES;
-    uint8_t* sP = smem + 4 * TILE_BYTES;   // 2 slabs: P (dropped, normalised)
-    uint8_t* sdS = smem + 6 * TILE_BYTES;  // 2 slabs: dS (scaled)
+    uint8_t* sQ = smem; uint8_t* sK = smem + TILE_BYTES; uint8_t* sdO = smem + 2 * TILE_BYTES;
+    uint8_t* sV = smem + 3 * TILE_BYTES;
+    uint8_t* sP = sV;                      // 2 slabs: P (dropped, normalised); slab 0 overwrites V
+    uint8_t* sdS = smem + 5 * TILE_BYTES;  // 2 slabs: dS (scaled)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 7 * TILE_BYTES);
+    uint64_t& bar_load = bars[0];
+    uint64_t& bar_mma1 = bars[1];
+    uint64_t& bar_mma2 = bars[2];
+    uint32_t& tmem_base_smem = *reinterpret_cast<uint32_t*>(bars + 3);
     const int HD = H * AT_D;
 
     if (tid == 0) {
@@ -204,12 +212,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         mbar_init(smem_u32(&bar_mma2), 1);
         fence_barrier_init();
     }
-    if (warp == 0) { tmem_alloc(smem_u32(&tmem_base_smem), 512); tmem_relinquish(); }
+    if (warp == 0) { tmem_alloc(smem_u32(&tmem_base_smem), 256); tmem_relinquish(); }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = tmem_base_smem;
-    const uint32_t tS = tmem, tdP = tmem + 128, tdV = tmem + 256, tdK = tmem + 320, tdQ = tmem + 384;
+    const uint32_t tS = tmem, tdP = tmem + 128;                       // phase 1
+    const uint32_t tdV = tmem, tdK = tmem + 64, tdQ = tmem + 128;     // phase 2 (reuses the columns of S / dP)
 
     if (tid == 0) {
         const uint32_t bar = smem_u32(&bar_load);
@@ -330,7 +339,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+    if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem, 256); }
 }
 
 static inline uint32_t drop_thresh_attn(float p) {
@@ -380,10 +389,12 @@ extern "C" int dcad_attn_bwd(const void* qkv, const void* ctx, const void* dctx,
     if (rc) return rc;
     rc = make_tensor_map_bf16_3d(&td, dctx, HD, S, B, HD, static_cast<uint64_t>(S) * HD, AT_D, AT_S);
     if (rc) return rc;
-    constexpr int SMEM = 8 * TILE_BYTES + 1024;
+    constexpr int SMEM = 7 * TILE_BYTES + 64;  // tiles + 3 mbarriers + the TMEM base word
     static bool attr = false;
     if (!attr) {
         DCAD_CUDA_TRY(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        DCAD_CUDA_TRY(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                           cudaSharedmemCarveoutMaxShared));
         attr = true;
     }
     const float ks = p_drop > 0.f ? 1.0f / (1.0f - p_drop) : 1.0f;
