@@ -16,6 +16,8 @@ adam_flat_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict
                  int64_t zero_begin, int64_t zero_end, float lr, float beta1, float beta2, float eps,
                  const uint64_t* __restrict__ state) {
     __shared__ float s_c[2];
+    pdl_trigger();
+    pdl_wait();
     if (threadIdx.x == 0) {
         const double t = static_cast<double>(state ? state[1] + 1 : 1);
         const double bc1 = 1.0 - pow(static_cast<double>(beta1), t);
@@ -132,6 +134,8 @@ __global__ void xgpu_barrier_kernel(uint32_t* const* pads_dev_unused, const uint
 }
 
 __global__ void step_advance_kernel(uint64_t* state) {
+    pdl_trigger();
+    pdl_wait();
     if (threadIdx.x == 0 && blockIdx.x == 0) state[1] += 1;
 }
 
@@ -151,15 +155,13 @@ extern "C" int dcad_adam_step(float* p, float* g, float* m, float* v, void* p_bf
     int64_t blocks = (n / 4 + 255) / 256;
     const int64_t cap = 148 * 16;
     if (blocks > cap) blocks = cap;
-    adam_flat_kernel<<<static_cast<int>(blocks), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-        p, g, m, v, reinterpret_cast<__nv_bfloat16*>(p_bf16), n, bf16_begin, bf16_end, zero_begin, zero_end, lr, beta1,
-        beta2, eps, state);
-    return (int)cudaGetLastError();
+    return (int)launch_pdl(adam_flat_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0,
+                           reinterpret_cast<cudaStream_t>(stream), p, g, m, v, reinterpret_cast<__nv_bfloat16*>(p_bf16),
+                           n, bf16_begin, bf16_end, zero_begin, zero_end, lr, beta1, beta2, eps, state);
 }
 
 extern "C" int dcad_step_advance(uint64_t* state, void* stream) {
-    step_advance_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(state);
-    return (int)cudaGetLastError();
+    return (int)launch_pdl(step_advance_kernel, dim3(1), dim3(32), 0, reinterpret_cast<cudaStream_t>(stream), state);
 }
 
 // Sharded Adam + fused parameter all-gather (see adam_dp_kernel).  peer_p / peer_bf16 are HOST arrays of n_peers

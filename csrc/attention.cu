@@ -71,10 +71,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
         fence_barrier_init();
     }
     if (warp == 0) { tmem_alloc(smem_u32(&tmem_base_smem), 256); tmem_relinquish(); }
+    pdl_trigger();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = tmem_base_smem;
+    pdl_wait();  // prologue above overlaps the previous kernel's tail
     const uint32_t tS = tmem, tO = tmem + 128;
 
     if (tid == 0) {
@@ -213,10 +215,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         fence_barrier_init();
     }
     if (warp == 0) { tmem_alloc(smem_u32(&tmem_base_smem), 256); tmem_relinquish(); }
+    pdl_trigger();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = tmem_base_smem;
+    pdl_wait();  // prologue above overlaps the previous kernel's tail
     const uint32_t tS = tmem, tdP = tmem + 128;                       // phase 1
     const uint32_t tdV = tmem, tdK = tmem + 64, tdQ = tmem + 128;     // phase 2 (reuses the columns of S / dP)
 
@@ -370,10 +374,9 @@ extern "C" int dcad_attn_fwd(const void* qkv, void* ctx, float* lse2, const int3
         attr = true;
     }
     const float ks = p_drop > 0.f ? 1.0f / (1.0f - p_drop) : 1.0f;
-    attn_fwd_kernel<<<B * H, AT_THREADS, SMEM, reinterpret_cast<cudaStream_t>(stream)>>>(
-        tm, reinterpret_cast<__nv_bfloat16*>(ctx), lse2, lens, S, H, 0.125f, drop_thresh_attn(p_drop), ks, rng,
-        stream_id);
-    return (int)cudaGetLastError();
+    return (int)launch_pdl(attn_fwd_kernel, dim3(B * H), dim3(AT_THREADS), SMEM, reinterpret_cast<cudaStream_t>(stream),
+                           tm, reinterpret_cast<__nv_bfloat16*>(ctx), lse2, lens, S, H, 0.125f,
+                           drop_thresh_attn(p_drop), ks, rng, stream_id);
 }
 
 // dctx: [B*S, H*64] bf16 gradient of ctx; dqkv: [B*S, 3*H*64] bf16 output
@@ -398,8 +401,8 @@ extern "C" int dcad_attn_bwd(const void* qkv, const void* ctx, const void* dctx,
         attr = true;
     }
     const float ks = p_drop > 0.f ? 1.0f / (1.0f - p_drop) : 1.0f;
-    attn_bwd_kernel<<<B * H, AT_THREADS, SMEM, reinterpret_cast<cudaStream_t>(stream)>>>(
-        tq, td, reinterpret_cast<const __nv_bfloat16*>(ctx), reinterpret_cast<const __nv_bfloat16*>(dctx), lse2,
-        reinterpret_cast<__nv_bfloat16*>(dqkv), lens, S, H, 0.125f, drop_thresh_attn(p_drop), ks, rng, stream_id);
-    return (int)cudaGetLastError();
+    return (int)launch_pdl(attn_bwd_kernel, dim3(B * H), dim3(AT_THREADS), SMEM, reinterpret_cast<cudaStream_t>(stream),
+                           tq, td, reinterpret_cast<const __nv_bfloat16*>(ctx),
+                           reinterpret_cast<const __nv_bfloat16*>(dctx), lse2, reinterpret_cast<__nv_bfloat16*>(dqkv),
+                           lens, S, H, 0.125f, drop_thresh_attn(p_drop), ks, rng, stream_id);
 }

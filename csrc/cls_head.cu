@@ -34,6 +34,8 @@ cls_head_train_kernel(const __nv_bfloat16* __restrict__ h, int sample_stride, co
                       uint32_t thresh, float keep_scale, const uint64_t* __restrict__ rng, uint32_t stream_id,
                       float* __restrict__ loss_accum, float* __restrict__ logits, float* __restrict__ dW,
                       float* __restrict__ db, __nv_bfloat16* __restrict__ dcls) {
+    pdl_trigger();
+    pdl_wait();
     constexpr int COLS = NV * 256;
     constexpr int WARPS = CLS_TRAIN_THREADS / 32;
     extern __shared__ float s_slot[];  // [WARPS][2*COLS]
@@ -185,10 +187,9 @@ static int launch_cls_train(const void* h, int sample_stride, const float* W, co
         DCAD_CUDA_TRY(cudaFuncSetAttribute(cls_head_train_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
         attr = true;
     }
-    cls_head_train_kernel<NV><<<1, CLS_TRAIN_THREADS, SMEM, s>>>(
-        reinterpret_cast<const __nv_bfloat16*>(h), sample_stride, W, bias, labels, batch, th, ks, rng, stream_id,
-        loss_accum, logits, dW, db, reinterpret_cast<__nv_bfloat16*>(dcls));
-    return (int)cudaGetLastError();
+    return (int)launch_pdl(cls_head_train_kernel<NV>, dim3(1), dim3(CLS_TRAIN_THREADS), SMEM, s,
+                           reinterpret_cast<const __nv_bfloat16*>(h), sample_stride, W, bias, labels, batch, th, ks, rng,
+                           stream_id, loss_accum, logits, dW, db, reinterpret_cast<__nv_bfloat16*>(dcls));
 }
 
 extern "C" int dcad_cls_head_train(const void* h, int sample_stride, const float* W, const float* bias,

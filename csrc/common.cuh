@@ -25,6 +25,35 @@ namespace dcad {
     } while (0)
 
 // ----------------------------------------------------------------------------------------------
+// programmatic dependent launch (PDL): every kernel of the training step is launched with
+// programmaticStreamSerializationAllowed, releases its successor at once (pdl_trigger) and orders itself
+// behind its predecessor with pdl_wait() before the first global-memory access.  The successor's launch
+// latency and prologue (barrier init, TMEM alloc, tensor-map prefetch) then overlap the predecessor's tail.
+// Ordering is transitive because every such kernel executes pdl_wait() on every thread that touches memory
+// and a grid only completes after all of its CTAs passed their wait.
+// ----------------------------------------------------------------------------------------------
+extern int g_pdl_enabled;  // misc.cu; dcad_set_pdl()
+
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = g_pdl_enabled ? 1 : 0;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
+// ----------------------------------------------------------------------------------------------
 // generic helpers
 // ----------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {

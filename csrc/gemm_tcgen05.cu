@@ -126,10 +126,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         tmem_alloc(smem_u32(&tmem_base_smem), Cfg::TMEM_COLS);
         tmem_relinquish();
     }
+    pdl_trigger();  // the next kernel may start its own prologue as soon as every CTA of this grid is resident
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_smem;
+    pdl_wait();  // everything above overlapped the previous kernel's tail; global memory is touched only below
 
     // work unit = (output tile, k-split); units are strided over the persistent CTAs
     const int num_units = p.num_m_blocks * p.num_n_blocks * p.split_k;
@@ -474,8 +476,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUt
     int grid = p.num_m_blocks * p.num_n_blocks * p.split_k;
     int cap = max_ctas > 0 ? max_ctas : num_sms();
     if (grid > cap) grid = cap;
-    kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, tmD, tmAux, p);
-    return (int)cudaGetLastError();
+    return (int)launch_pdl(kern, dim3(grid), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, tmA, tmB, tmD, tmAux, p);
 }
 
 }  // namespace dcad
@@ -574,6 +575,8 @@ __global__ void __launch_bounds__(256)
 splitk_reduce_kernel(const float* __restrict__ ws, int splits, int64_t slice_elems, int M, int N,
                      const float* __restrict__ bias, const __nv_bfloat16* __restrict__ aux, int ldaux,
                      __nv_bfloat16* __restrict__ aux_out, __nv_bfloat16* __restrict__ D, int ldd, int epi) {
+    pdl_trigger();
+    pdl_wait();
     const int vec_per_row = N >> 3;
     const int64_t total = static_cast<int64_t>(M) * vec_per_row;
     for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -634,11 +637,10 @@ static int gemm_splitk_run(const void* A, const void* B, void* D, int M, int N, 
     const int64_t total = static_cast<int64_t>(M) * (N >> 3);
     int blocks = static_cast<int>((total + 255) / 256);
     if (blocks > 148 * 8) blocks = 148 * 8;
-    splitk_reduce_kernel<<<blocks, 256, 0, s>>>(ws, sk, static_cast<int64_t>(m_pad) * N, M, N, bias,
-                                                reinterpret_cast<const __nv_bfloat16*>(aux), ldaux > 0 ? ldaux : ldd,
-                                                reinterpret_cast<__nv_bfloat16*>(aux_out),
-                                                reinterpret_cast<__nv_bfloat16*>(D), ldd, epi);
-    return (int)cudaGetLastError();
+    return (int)launch_pdl(splitk_reduce_kernel, dim3(blocks), dim3(256), 0, s, ws, sk,
+                           static_cast<int64_t>(m_pad) * N, M, N, bias, reinterpret_cast<const __nv_bfloat16*>(aux),
+                           ldaux > 0 ? ldaux : ldd, reinterpret_cast<__nv_bfloat16*>(aux_out),
+                           reinterpret_cast<__nv_bfloat16*>(D), ldd, epi);
 }
 
 }  // namespace dcad

@@ -46,6 +46,8 @@ add_ln_fwd_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __re
                   const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ out,
                   float* __restrict__ rstd_out, int rows, float eps, uint32_t thresh, float keep_scale,
                   const uint64_t* __restrict__ rng, uint32_t stream_id) {
+    pdl_trigger();
+    pdl_wait();
     constexpr int COLS = NV * 256;
     const int row = blockIdx.x * LN_WARPS + (threadIdx.x >> 5);
     if (row >= rows) return;
@@ -103,6 +105,8 @@ add_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy1, const __nv_bfloat16* __
                   __nv_bfloat16* __restrict__ da, float* __restrict__ dgamma, float* __restrict__ dbeta,
                   float* __restrict__ dbias, int rows, uint32_t thresh, float keep_scale,
                   const uint64_t* __restrict__ rng, uint32_t stream_id) {
+    pdl_trigger();
+    pdl_wait();
     constexpr int COLS = NV * 256;
     // one slot per warp: [warp][3][COLS] partial column sums (dgamma, dbeta, dbias); one row per warp
     extern __shared__ float s_part[];
@@ -182,6 +186,8 @@ embed_ln_fwd_kernel(const int32_t* __restrict__ ids, const float* __restrict__ w
                     const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ out,
                     float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows, int seq, float eps,
                     uint32_t thresh, float keep_scale, const uint64_t* __restrict__ rng, uint32_t stream_id) {
+    pdl_trigger();
+    pdl_wait();
     constexpr int COLS = NV * 256;
     const int row = blockIdx.x * LN_WARPS + (threadIdx.x >> 5);
     if (row >= rows) return;
@@ -239,6 +245,8 @@ embed_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy1, const __nv_bfloat16* 
                     float* __restrict__ dword, float* __restrict__ dpos, float* __restrict__ dgamma,
                     float* __restrict__ dbeta, const int32_t* __restrict__ lens, int rows, int seq, uint32_t thresh,
                     float keep_scale, const uint64_t* __restrict__ rng, uint32_t stream_id) {
+    pdl_trigger();
+    pdl_wait();
     constexpr int COLS = NV * 256;
     extern __shared__ float s_part[];  // [warp][2][COLS]
     const uint32_t warp = threadIdx.x >> 5, lane = lane_id();
@@ -313,6 +321,8 @@ __global__ void __launch_bounds__(256)
 colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, int rows, int cols, int ld,
                    int rows_per_cta) {
     // block (32 x 8): x-dim covers 32*8 = 256 columns (8 per thread), y-dim strides rows
+    pdl_trigger();
+    pdl_wait();
     __shared__ float s[8][256];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int col = blockIdx.x * 256 + tx * 8;
@@ -367,10 +377,11 @@ extern "C" int dcad_add_ln_fwd(const void* a, const void* res, const float* gamm
     const float ks = p_drop > 0.f ? 1.0f / (1.0f - p_drop) : 1.0f;
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     const int grid = (rows + LN_WARPS - 1) / LN_WARPS;
-    DCAD_NV_DISPATCH(cols, (add_ln_fwd_kernel<NV><<<grid, LN_WARPS * 32, 0, s>>>(
-        reinterpret_cast<const __nv_bfloat16*>(a), reinterpret_cast<const __nv_bfloat16*>(res), gamma, beta,
-        reinterpret_cast<__nv_bfloat16*>(out), rstd, rows, eps, th, ks, rng, stream_id)));
-    return (int)cudaGetLastError();
+    DCAD_NV_DISPATCH(cols, return (int)launch_pdl(
+        add_ln_fwd_kernel<NV>, dim3(grid), dim3(LN_WARPS * 32), 0, s, reinterpret_cast<const __nv_bfloat16*>(a),
+        reinterpret_cast<const __nv_bfloat16*>(res), gamma, beta, reinterpret_cast<__nv_bfloat16*>(out), rstd, rows,
+        eps, th, ks, rng, stream_id));
+    return 0;
 }
 
 extern "C" int dcad_add_ln_bwd(const void* dy1, const void* dy2, const void* y, const float* gamma, const float* beta,
@@ -392,13 +403,14 @@ extern "C" int dcad_add_ln_bwd(const void* dy1, const void* dy2, const void* y, 
                                                LN_WARPS * 3 * NV * 256 * (int)sizeof(float)));
             attr = true;
         }
-        add_ln_bwd_kernel<NV><<<grid, LN_WARPS * 32, smem, s>>>(
+        return (int)launch_pdl(
+            add_ln_bwd_kernel<NV>, dim3(grid), dim3(LN_WARPS * 32), smem, s,
             reinterpret_cast<const __nv_bfloat16*>(dy1), reinterpret_cast<const __nv_bfloat16*>(dy2),
             reinterpret_cast<const __nv_bfloat16*>(y), gamma, beta, rstd, reinterpret_cast<__nv_bfloat16*>(dz),
             reinterpret_cast<__nv_bfloat16*>(p_drop > 0.f ? da : nullptr), dgamma, dbeta, dbias, rows, th, ks, rng,
             stream_id);
     });
-    return (int)cudaGetLastError();
+    return 0;
 }
 
 extern "C" int dcad_embed_ln_fwd(const int32_t* ids, const float* word, const float* pos, const float* gamma,
@@ -411,10 +423,10 @@ extern "C" int dcad_embed_ln_fwd(const int32_t* ids, const float* word, const fl
     const float ks = p_drop > 0.f ? 1.0f / (1.0f - p_drop) : 1.0f;
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     const int grid = (rows + LN_WARPS - 1) / LN_WARPS;
-    DCAD_NV_DISPATCH(cols, (embed_ln_fwd_kernel<NV><<<grid, LN_WARPS * 32, 0, s>>>(
-        ids, word, pos, gamma, beta, reinterpret_cast<__nv_bfloat16*>(out), mean, rstd, rows, seq, eps, th, ks, rng,
-        stream_id)));
-    return (int)cudaGetLastError();
+    DCAD_NV_DISPATCH(cols, return (int)launch_pdl(
+        embed_ln_fwd_kernel<NV>, dim3(grid), dim3(LN_WARPS * 32), 0, s, ids, word, pos, gamma, beta,
+        reinterpret_cast<__nv_bfloat16*>(out), mean, rstd, rows, seq, eps, th, ks, rng, stream_id));
+    return 0;
 }
 
 extern "C" int dcad_embed_ln_bwd(const void* dy1, const void* dy2, const int32_t* ids, const float* word,
@@ -437,11 +449,12 @@ extern "C" int dcad_embed_ln_bwd(const void* dy1, const void* dy2, const int32_t
                                                LN_WARPS * 2 * NV * 256 * (int)sizeof(float)));
             attr = true;
         }
-        embed_ln_bwd_kernel<NV><<<grid, LN_WARPS * 32, smem, s>>>(
+        return (int)launch_pdl(
+            embed_ln_bwd_kernel<NV>, dim3(grid), dim3(LN_WARPS * 32), smem, s,
             reinterpret_cast<const __nv_bfloat16*>(dy1), reinterpret_cast<const __nv_bfloat16*>(dy2), ids, word, pos,
             gamma, mean, rstd, dword, dpos, dgamma, dbeta, lens, rows, seq, th, ks, rng, stream_id);
     });
-    return (int)cudaGetLastError();
+    return 0;
 }
 
 extern "C" int dcad_colsum_bf16(const void* x, float* out, int rows, int cols, int ld, void* stream) {
@@ -449,7 +462,6 @@ extern "C" int dcad_colsum_bf16(const void* x, float* out, int rows, int cols, i
     if (cols % 8 || ld % 8) return DCAD_ERR_BAD_ALIGNMENT;
     const int rows_per_cta = 64;
     dim3 grid((cols + 255) / 256, (rows + rows_per_cta - 1) / rows_per_cta);
-    colsum_bf16_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-        reinterpret_cast<const __nv_bfloat16*>(x), out, rows, cols, ld, rows_per_cta);
-    return (int)cudaGetLastError();
+    return (int)launch_pdl(colsum_bf16_kernel, grid, dim3(256), 0, reinterpret_cast<cudaStream_t>(stream),
+                           reinterpret_cast<const __nv_bfloat16*>(x), out, rows, cols, ld, rows_per_cta);
 }

@@ -11,6 +11,7 @@ by the CPU plumbing tests.
 from __future__ import annotations
 
 import ctypes
+import os
 from ctypes import c_int, c_void_p, c_float, c_uint64, c_int64, c_uint32
 from pathlib import Path
 from typing import Optional
@@ -51,7 +52,15 @@ def lib() -> ctypes.CDLL:
                 "(the CUDA path has no PyTorch fallback on a GPU machine)")
         _LIB = ctypes.CDLL(str(_LIB_PATH))
         _declare(_LIB)
+        if os.environ.get("DCAD_PDL", "1") == "0":
+            _LIB.dcad_set_pdl(0)
     return _LIB
+
+
+def set_pdl(enabled: bool) -> bool:
+    """Switch programmatic dependent launch of the step kernels on/off (default on; ``DCAD_PDL=0`` in the
+    environment turns it off at load).  Returns the previous setting; affects launches and captures made afterwards."""
+    return bool(lib().dcad_set_pdl(1 if enabled else 0))
 
 
 def check(rc: int, what: str) -> None:
@@ -79,6 +88,7 @@ def _declare(L: ctypes.CDLL) -> None:
 
     P, I, F, L64, U32 = c_void_p, c_int, c_float, c_int64, c_uint32
     sig("dcad_version", [])
+    sig("dcad_set_pdl", [I])
     sig("dcad_gemm_bf16", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, I, I, P])
     sig("dcad_gemm_splitk_workspace_bytes", [I, I, I], ctypes.c_size_t)
     sig("dcad_gemm_bf16_splitk", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, I, P, ctypes.c_size_t, P])

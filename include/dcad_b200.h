@@ -38,6 +38,12 @@ extern "C" {
 
 int dcad_version(void);
 
+/* Programmatic dependent launch for the training-step kernels (default on): each kernel releases its successor at
+ * once and waits for its predecessor right before its first global-memory access, so launch latency and prologues
+ * overlap the previous kernel's tail.  Returns the previous setting.  Takes effect for launches (and graph captures)
+ * made after the call. */
+int dcad_set_pdl(int enabled);
+
 /* bf16 x bf16 -> fp32-accumulated GEMM on tcgen05 tensor cores (TMA-fed, TMEM accumulators, persistent, TMA-store
  * epilogue).
  *   D[M,N] = epilogue( sum_k A(m,k) * B(n,k) )

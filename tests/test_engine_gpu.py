@@ -124,3 +124,38 @@ def test_full_size_model_step_runs():
     assert n == 3 and 0.1 < loss < 3.0
     sd = eng.state_dict()
     assert len(sd) == 102 and sum(v.numel() for v in sd.values()) == 66_364_418
+
+
+def test_pdl_overlap_does_not_change_gradients():
+    """Programmatic dependent launch only moves prologues ahead of the predecessor's tail: the gradients of the
+    full-size model must agree with the fully serialised launch order (differences: atomic/reduce-add order only)."""
+    eng_mod, arena_mod, db = _mods()
+    from importlib import import_module
+    nv = import_module(f"{PKG}.ops.native")
+    dims = arena_mod.ModelDims()
+    B, S = 16, 128
+    eng = eng_mod.B200Engine(dims, batch=B, seq=S, init_seed=7)
+    ids, lens, labels, _ = _batch(B, S, dims.vocab_size, seed=5)
+    eng.set_batch(ids.int(), lens.int(), labels.int())
+
+    def grads():
+        eng.arena.grad.zero_()
+        eng.loss_accum.zero_()
+        h, stride = eng._forward(B, train=True)
+        nv.cls_head_train(h, stride, eng.cw, eng.cb, eng.labels, B, eng.loss_accum, eng.logits, eng.d_cw, eng.d_cb,
+                          eng.dcls, cols=dims.dim, p_drop=dims.head_dropout, rng=eng.rng)
+        eng._backward()
+        torch.cuda.synchronize()
+        return eng.arena.grad.clone(), float(eng.loss_accum[0].item())
+
+    prev = nv.set_pdl(False)
+    try:
+        g_off, l_off = grads()
+        nv.set_pdl(True)
+        outs = [grads() for _ in range(3)]
+    finally:
+        nv.set_pdl(prev)
+    for g_on, l_on in outs:
+        assert abs(l_on - l_off) < 1e-5
+        err = (g_on - g_off).abs().max().item()
+        assert err <= 1e-3 * g_off.abs().max().item() + 1e-6, err
