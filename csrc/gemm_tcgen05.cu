@@ -52,12 +52,18 @@ __host__ __device__ constexpr int pow2_ceil(int v) {
     return p;
 }
 
-template <int BN>
+// CG = 1: one CTA per 128 x BN tile.  CG = 2: a CTA pair (cluster of 2, one TPC) per 256 x BN tile with
+// tcgen05.mma.cta_group::2 -- each CTA stages its own 128 A rows and only BN/2 of the B rows, so the operand bytes
+// read from smem per MMA (and fetched from L2 per tile) drop by a third for BN = 256.
+template <int BN, int CG = 1>
 struct GemmCfg {
     static constexpr int A_BYTES = BM * BK * 2;
-    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int B_ROWS = BN / CG;          // B rows (N) staged by one CTA
+    static constexpr int B_BYTES = B_ROWS * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES_RAW = (160 * 1024) / STAGE_BYTES;
+    // 227 KB per CTA minus the staging slabs, the alignment slack and the static part (bias copy + barriers)
+    static constexpr int RING_BYTES = 232448 - NUM_STAGING * STAGING_BYTES - 1024 - (2 * BN * 4 + 512);
+    static constexpr int STAGES_RAW = RING_BYTES / STAGE_BYTES;
     static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
     static constexpr int ACC_STRIDE = pow2_ceil(BN);  // TMEM columns per accumulator stage
     static constexpr int TMEM_COLS = 2 * ACC_STRIDE;  // two accumulator stages
@@ -80,14 +86,16 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t
     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
-template <int BN, int A_MAJOR, int B_MAJOR>
+template <int BN, int A_MAJOR, int B_MAJOR, int CG>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmAux,
                          const GemmParams p) {
-    using Cfg = GemmCfg<BN>;
+    using Cfg = GemmCfg<BN, CG>;
     constexpr int STAGES = Cfg::STAGES;
     static_assert(BN % 64 == 0 && BN >= 64 && BN <= 256, "BLOCK_N must be a multiple of 64 in [64,256]");
+    static_assert(CG == 1 || CG == 2, "cta_group is 1 or 2");
+    static_assert(CG == 1 || B_MAJOR == kMajorK || Cfg::B_ROWS % 64 == 0, "MN-major B halves are whole 64-column slabs");
     static_assert(STAGES >= 2, "need at least a double-buffered operand ring");
 
     extern __shared__ uint8_t smem_raw[];
@@ -100,6 +108,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t lane = lane_id();
+    const uint32_t cta_rank = (CG == 2) ? cluster_ctarank() : 0u;  // 0 = leader (issues the MMAs), 1 = peer
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024-B alignment
     const uint32_t staging_base = smem_base + STAGES * Cfg::STAGE_BYTES;
 
@@ -118,32 +127,41 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
             mbar_init(smem_u32(&tmem_full_bar[s]), 1);
-            mbar_init(smem_u32(&tmem_empty_bar[s]), EPI_THREADS);
+            // CG 1: every epilogue thread arrives; CG 2: one lane per epilogue warp of BOTH CTAs arrives on the leader
+            mbar_init(smem_u32(&tmem_empty_bar[s]), CG == 1 ? EPI_THREADS : 2 * (EPI_THREADS / 32));
         }
         fence_barrier_init();
     }
     if (warp == 2) {
-        tmem_alloc(smem_u32(&tmem_base_smem), Cfg::TMEM_COLS);
-        tmem_relinquish();
+        if constexpr (CG == 1) {
+            tmem_alloc(smem_u32(&tmem_base_smem), Cfg::TMEM_COLS);
+            tmem_relinquish();
+        } else {  // collective over the pair: the same columns in both SMs
+            tmem_alloc_cg2(smem_u32(&tmem_base_smem), Cfg::TMEM_COLS);
+            tmem_relinquish_cg2();
+        }
     }
     pdl_trigger();  // the next kernel may start its own prologue as soon as every CTA of this grid is resident
     tc_fence_before();
-    __syncthreads();
+    if constexpr (CG == 1) __syncthreads();
+    else cluster_sync_all();  // the peer's barriers must be initialised before anything signals them
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_smem;
     pdl_wait();  // everything above overlapped the previous kernel's tail; global memory is touched only below
 
-    // work unit = (output tile, k-split); units are strided over the persistent CTAs
+    // work unit = (output tile of BM*CG x BN, k-split); units are strided over the persistent CTAs (CTA pairs)
     const int num_units = p.num_m_blocks * p.num_n_blocks * p.split_k;
+    const int unit0 = static_cast<int>(blockIdx.x) / CG, unit_step = static_cast<int>(gridDim.x) / CG;
     if (warp == 0) DCAD_STAMP(0);
 
     if (warp == 0) {
         // ===================== TMA producer =====================
         uint32_t stage = 0, phase = 0;
-        for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+        for (int unit = unit0; unit < num_units; unit += unit_step) {
             const int tile = unit / p.split_k, split = unit % p.split_k;
-            const int m_blk = tile % p.num_m_blocks;
+            const int m_blk = (tile % p.num_m_blocks) * CG + static_cast<int>(cta_rank);
             const int n_blk = tile / p.num_m_blocks;
+            const int n_row0 = n_blk * BN + static_cast<int>(cta_rank) * Cfg::B_ROWS;  // this CTA's share of B
             const int kb0 = split * p.kb_per_split;
             const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
             for (int kb = kb0; kb < kb1; ++kb) {
@@ -152,20 +170,24 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                     const uint32_t bar = smem_u32(&full_bar[stage]);
                     const uint32_t sA = smem_base + stage * Cfg::STAGE_BYTES;
                     const uint32_t sB = sA + Cfg::A_BYTES;
-                    mbar_arrive_expect_tx(bar, Cfg::STAGE_BYTES);
+                    // CG 2: both CTAs' loads are credited to the leader's barrier, which expects both stages
+                    auto load = [&](uint32_t dst, const CUtensorMap* tm, int c0, int c1) {
+                        if constexpr (CG == 1) tma_load_2d(dst, tm, bar, c0, c1);
+                        else tma_load_2d_cg2(dst, tm, bar, c0, c1);
+                    };
+                    if (CG == 1 || cta_rank == 0) mbar_arrive_expect_tx(bar, CG * Cfg::STAGE_BYTES);
                     if constexpr (A_MAJOR == kMajorK) {
-                        tma_load_2d(sA, &tmA, bar, kb * BK, m_blk * BM);
+                        load(sA, &tmA, kb * BK, m_blk * BM);
                     } else {
 #pragma unroll
-                        for (int c = 0; c < BM / 64; ++c)
-                            tma_load_2d(sA + c * SLAB_BYTES, &tmA, bar, m_blk * BM + c * 64, kb * BK);
+                        for (int c = 0; c < BM / 64; ++c) load(sA + c * SLAB_BYTES, &tmA, m_blk * BM + c * 64, kb * BK);
                     }
                     if constexpr (B_MAJOR == kMajorK) {
-                        tma_load_2d(sB, &tmB, bar, kb * BK, n_blk * BN);
+                        load(sB, &tmB, kb * BK, n_row0);
                     } else {
 #pragma unroll
-                        for (int c = 0; c < BN / 64; ++c)
-                            tma_load_2d(sB + c * SLAB_BYTES, &tmB, bar, n_blk * BN + c * 64, kb * BK);
+                        for (int c = 0; c < Cfg::B_ROWS / 64; ++c)
+                            load(sB + c * SLAB_BYTES, &tmB, n_row0 + c * 64, kb * BK);
                     }
                 }
                 __syncwarp();
@@ -173,10 +195,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             }
         }
         DCAD_STAMP(1);
-    } else if (warp == 1) {
-        // ===================== MMA issuer (one thread) =====================
+    } else if (warp == 1 && (CG == 1 || cta_rank == 0)) {
+        // ===================== MMA issuer (one thread; of the leader CTA when CG = 2) =====================
         // Descriptors are built once; per MMA only the 14-bit start-address field (16-byte units) advances.
-        constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MAJOR, B_MAJOR);
+        constexpr uint32_t idesc = make_idesc_bf16(BM * CG, BN, A_MAJOR, B_MAJOR);
         constexpr uint32_t A_KSTEP = (A_MAJOR == kMajorK ? UMMA_K * 2 : UMMA_K * 128) >> 4;
         constexpr uint32_t B_KSTEP = (B_MAJOR == kMajorK ? UMMA_K * 2 : UMMA_K * 128) >> 4;
         const uint64_t a_desc0 = (A_MAJOR == kMajorK) ? make_smem_desc_sw128(smem_base, 16, 1024)
@@ -187,7 +209,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         const uint32_t a_lo0 = static_cast<uint32_t>(a_desc0), b_lo0 = static_cast<uint32_t>(b_desc0);
         uint32_t stage = 0, phase = 0, acc_stage = 0, acc_phase = 0;
         bool first = true;
-        for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+        for (int unit = unit0; unit < num_units; unit += unit_step) {
             const int split = unit % p.split_k;
             const int kb0 = split * p.kb_per_split;
             const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
@@ -205,10 +227,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                     for (int k = 0; k < BK / UMMA_K; ++k) {
                         const uint64_t adesc = (static_cast<uint64_t>(a_hi) << 32) | (a_lo + k * A_KSTEP);
                         const uint64_t bdesc = (static_cast<uint64_t>(b_hi) << 32) | (b_lo + k * B_KSTEP);
-                        umma_bf16_ss(tmem_d, adesc, bdesc, idesc, (kb != kb0 || k != 0) ? 1u : 0u);
+                        if constexpr (CG == 1) umma_bf16_ss(tmem_d, adesc, bdesc, idesc, (kb != kb0 || k != 0) ? 1u : 0u);
+                        else umma_bf16_ss_cg2(tmem_d, adesc, bdesc, idesc, (kb != kb0 || k != 0) ? 1u : 0u);
                     }
-                    umma_commit(smem_u32(&empty_bar[stage]));  // frees the smem slot when the MMAs retire
-                    if (kb == kb1 - 1) umma_commit(smem_u32(&tmem_full_bar[acc_stage]));
+                    if constexpr (CG == 1) {
+                        umma_commit(smem_u32(&empty_bar[stage]));  // frees the smem slot when the MMAs retire
+                        if (kb == kb1 - 1) umma_commit(smem_u32(&tmem_full_bar[acc_stage]));
+                    } else {  // both CTAs' producers / epilogues are released
+                        umma_commit_cg2(smem_u32(&empty_bar[stage]));
+                        if (kb == kb1 - 1) umma_commit_cg2(smem_u32(&tmem_full_bar[acc_stage]));
+                    }
                 }
                 __syncwarp();
                 if (++stage == STAGES) { stage = 0; phase ^= 1u; }
@@ -228,11 +256,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         const bool has_bias = (p.epi == DCAD_EPI_BIAS || p.epi == DCAD_EPI_BIAS_GELU);
         const int r_in_tile = q * 32 + lane;
         uint32_t acc_stage = 0, acc_phase = 0, slab_ctr = 0;
-        for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+        for (int unit = unit0; unit < num_units; unit += unit_step) {
             const int tile = unit / p.split_k;
-            const int m_blk = tile % p.num_m_blocks;
+            const int m_blk = (tile % p.num_m_blocks) * CG + static_cast<int>(cta_rank);
             const int n_blk = tile / p.num_m_blocks;
             const int n_base = n_blk * BN;
+            const bool tile_ok = m_blk * BM < p.M;  // the peer's half of a pair tile may lie wholly past M
             const int out_row0 = (unit % p.split_k) * p.ws_row_stride + m_blk * BM;  // ws_row_stride == 0 unless workspace mode
             const int row = m_blk * BM + r_in_tile;
             const bool row_ok = row < p.M;
@@ -305,7 +334,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                     fence_proxy_async_smem();
                     epi_bar_sync();
                     if (ep_tid == 0) {
-                        if (n_base + s * 64 < p.N) {
+                        if (tile_ok && n_base + s * 64 < p.N) {
                             tma_store_2d(&tmD, sD, n_base + s * 64, m_blk * BM);
                             if (p.epi == DCAD_EPI_BIAS_GELU && p.has_aux_out)
                                 tma_store_2d(&tmAux, staging_base + (2 + buf) * STAGING_BYTES, n_base + s * 64, m_blk * BM);
@@ -333,7 +362,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                     fence_proxy_async_smem();
                     epi_bar_sync();
                     if (ep_tid == 0) {
-                        if (n_base + s * 32 < p.N) {
+                        if (tile_ok && n_base + s * 32 < p.N) {
                             if ((p.split_k > 1 && p.ws_row_stride == 0) || p.out_fp32 == 2) tma_reduce_add_2d(&tmD, sD, n_base + s * 32, out_row0);
                             else tma_store_2d(&tmD, sD, n_base + s * 32, out_row0);
                         }
@@ -343,7 +372,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                 }
             }
             tc_fence_before();
-            mbar_arrive(smem_u32(&tmem_empty_bar[acc_stage]));
+            if constexpr (CG == 1) {
+                mbar_arrive(smem_u32(&tmem_empty_bar[acc_stage]));
+            } else {  // the leader's MMA thread waits for the epilogues of both CTAs
+                __syncwarp();
+                if (lane == 0) mbar_arrive_remote(smem_u32(&tmem_empty_bar[acc_stage]), 0);
+            }
             if (warp == 4) DCAD_STAMP(5);
             if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1u; }
         }
@@ -351,11 +385,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     }
 
     tc_fence_before();
-    __syncthreads();
+    if constexpr (CG == 1) __syncthreads();
+    else cluster_sync_all();  // neither CTA may retire while the other can still read its smem or signal its barriers
     if (warp == 0) DCAD_STAMP(6);
     if (warp == 2) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+        if constexpr (CG == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+        else tmem_dealloc_cg2(tmem_base, Cfg::TMEM_COLS);
     }
 }
 
@@ -463,20 +499,22 @@ static int num_sms() {
     return n;
 }
 
-template <int BN, int A_MAJOR, int B_MAJOR>
+template <int BN, int A_MAJOR, int B_MAJOR, int CG>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmD,
                        const CUtensorMap& tmAux, const GemmParams& p, int max_ctas, cudaStream_t stream) {
-    using Cfg = GemmCfg<BN>;
-    auto kern = gemm_bf16_tcgen05_kernel<BN, A_MAJOR, B_MAJOR>;
+    using Cfg = GemmCfg<BN, CG>;
+    auto kern = gemm_bf16_tcgen05_kernel<BN, A_MAJOR, B_MAJOR, CG>;
     static bool attr_set = false;
     if (!attr_set) {
         DCAD_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
         attr_set = true;
     }
-    int grid = p.num_m_blocks * p.num_n_blocks * p.split_k;
-    int cap = max_ctas > 0 ? max_ctas : num_sms();
+    int grid = p.num_m_blocks * p.num_n_blocks * p.split_k;  // work units = CTAs (CG 1) or CTA pairs (CG 2)
+    int cap = (max_ctas > 0 ? max_ctas : num_sms()) / CG;
+    if (cap < 1) cap = 1;
     if (grid > cap) grid = cap;
-    return (int)launch_pdl(kern, dim3(grid), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, tmA, tmB, tmD, tmAux, p);
+    return (int)launch_pdl_cluster(kern, dim3(grid * CG), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, CG, tmA, tmB,
+                                   tmD, tmAux, p);
 }
 
 }  // namespace dcad
@@ -500,7 +538,8 @@ static int gemm_dispatch(const void* A, const void* B, void* D, int M, int N, in
     if (split_k > 1 && (!out_fp32 || epi != DCAD_EPI_NONE)) return DCAD_ERR_BAD_ARGUMENT;
     if (out_fp32 && epi != DCAD_EPI_NONE) return DCAD_ERR_BAD_ARGUMENT;
 
-    int bn = block_n;
+    const int cg = (block_n > 0 && (block_n & DCAD_TILE_PAIR)) ? 2 : 1;
+    int bn = block_n > 0 ? (block_n & ~DCAD_TILE_PAIR) : 0;
     if (bn <= 0) bn = (N >= 256) ? 256 : (N > 128 ? 192 : (N > 64 ? 128 : 64));
 
     GemmParams p;
@@ -509,7 +548,7 @@ static int gemm_dispatch(const void* A, const void* B, void* D, int M, int N, in
     p.aux = reinterpret_cast<const __nv_bfloat16*>(aux);
     p.has_aux_out = (epi == DCAD_EPI_BIAS_GELU && aux_out != nullptr) ? 1 : 0;
     p.epi = epi; p.out_fp32 = out_fp32;
-    p.num_m_blocks = (M + BM - 1) / BM;
+    p.num_m_blocks = (M + BM * cg - 1) / (BM * cg);  // tile rows: 128 (one CTA) or 256 (a CTA pair)
     p.num_n_blocks = (N + bn - 1) / bn;
     p.num_k_blocks = (K + BK - 1) / BK;
     if (split_k > p.num_k_blocks) split_k = p.num_k_blocks;
@@ -524,7 +563,7 @@ static int gemm_dispatch(const void* A, const void* B, void* D, int M, int N, in
     if (a_major == kMajorK) rc = make_tensor_map_2d(&tmA, A, M, K, lda, BM, BK, 2);   // A stored [M][lda]
     else                    rc = make_tensor_map_2d(&tmA, A, K, M, lda, BK, 64, 2);   // A stored [K][lda]
     if (rc) return rc;
-    if (b_major == kMajorK) rc = make_tensor_map_2d(&tmB, B, N, K, ldb, bn, BK, 2);   // B stored [N][ldb]
+    if (b_major == kMajorK) rc = make_tensor_map_2d(&tmB, B, N, K, ldb, bn / cg, BK, 2);  // B stored [N][ldb]
     else                    rc = make_tensor_map_2d(&tmB, B, K, N, ldb, BK, 64, 2);   // B stored [K][ldb]
     if (rc) return rc;
     const uint64_t d_rows = ws_row_stride > 0 ? static_cast<uint64_t>(ws_row_stride) * split_k : static_cast<uint64_t>(M);
@@ -538,7 +577,19 @@ static int gemm_dispatch(const void* A, const void* B, void* D, int M, int N, in
     }
 
 #define DCAD_GEMM_CASE(BN_, AM_, BM_) \
-    if (bn == BN_ && a_major == AM_ && b_major == BM_) return launch_gemm<BN_, AM_, BM_>(tmA, tmB, tmD, tmAux, p, max_ctas, s);
+    if (cg == 1 && bn == BN_ && a_major == AM_ && b_major == BM_) \
+        return launch_gemm<BN_, AM_, BM_, 1>(tmA, tmB, tmD, tmAux, p, max_ctas, s);
+#define DCAD_GEMM_CASE2(BN_, AM_, BM_) \
+    if (cg == 2 && bn == BN_ && a_major == AM_ && b_major == BM_) \
+        return launch_gemm<BN_, AM_, BM_, 2>(tmA, tmB, tmD, tmAux, p, max_ctas, s);
+    DCAD_GEMM_CASE2(128, 0, 0)
+    DCAD_GEMM_CASE2(192, 0, 0)
+    DCAD_GEMM_CASE2(256, 0, 0)
+    DCAD_GEMM_CASE2(128, 0, 1)
+    DCAD_GEMM_CASE2(256, 0, 1)
+    DCAD_GEMM_CASE2(128, 1, 1)
+    DCAD_GEMM_CASE2(256, 1, 1)
+#undef DCAD_GEMM_CASE2
     DCAD_GEMM_CASE(64, 0, 0)
     DCAD_GEMM_CASE(128, 0, 0)
     DCAD_GEMM_CASE(192, 0, 0)

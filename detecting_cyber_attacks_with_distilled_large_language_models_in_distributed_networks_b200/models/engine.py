@@ -17,10 +17,12 @@ per epoch / evaluation, not twice per step.
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass, field
 from typing import Dict, Optional, Tuple
 
 import torch
+from types import SimpleNamespace
 
 from ..ops import native as nv
 from .arena import ModelDims, ParamArena
@@ -58,7 +60,7 @@ class B200Engine:
                  lr: float = 2e-5, betas: Tuple[float, float] = (0.9, 0.999), eps: float = 1e-8, seed: int = 0,
                  flat_params: Optional[torch.Tensor] = None, bf16_params: Optional[torch.Tensor] = None,
                  plan: Optional[GemmPlan] = None, init_seed: Optional[int] = 0, dp=None,
-                 prune_last_layer: bool = True):
+                 prune_last_layer: bool = True, overlap_wgrad: bool = True):
         if not torch.cuda.is_available():
             raise nv.NativeError("B200Engine needs a CUDA device; use models.distilbert.DDoSClassifier on CPU")
         nv.lib()  # fail loudly if the native library is missing
@@ -77,6 +79,12 @@ class B200Engine:
         # the B CLS rows instead of all B*S tokens, forward and backward.  Same math, ~12 % fewer FLOPs per step.
         self.prune_last_layer = prune_last_layer
         dev = self.device
+        # Weight-gradient GEMMs and bias column sums are off the critical path of the backward pass (nothing in the
+        # same step reads them before Adam), so they are enqueued on a second, lower-priority stream: in the captured
+        # graph they become a parallel branch whose CTAs fill the SMs that the data-gradient chain leaves idle
+        # (partial waves, prologue/epilogue tails of its small dependent kernels).
+        self.overlap_wgrad = overlap_wgrad = overlap_wgrad and os.environ.get("DCAD_OVERLAP_WGRAD", "1") != "0"
+        self._side = torch.cuda.Stream(device=dev) if overlap_wgrad else None
         if dp is not None:
             flat_params, bf16_params = dp.param_tensor(), dp.mirror_tensor()
         self.arena = ParamArena(dims, dev, flat=flat_params, with_optimizer_state=True, with_bf16=bf16_params is None)
@@ -115,12 +123,14 @@ class B200Engine:
         self.emb_rstd = torch.empty(T, **f32)
         # transient forward / backward buffers
         self.tmp_d = torch.empty(T, D, **bf)        # attn_out / ffn_out
-        self.g_a = torch.empty(T, D, **bf)          # gradient wrt a layer output, branch 1
-        self.g_b = torch.empty(T, D, **bf)          # gradient wrt a layer output, branch 2 (residual)
-        self.g_c = torch.empty(T, D, **bf)
-        self.g_d = torch.empty(T, D, **bf)
-        self.g_wide = torch.empty(T, Fh, **bf)      # dpre
-        self.g_qkv = torch.empty(T, 3 * D, **bf)
+        # Two sets of backward scratch, alternated by layer parity: the weight-gradient branch of layer l may still be
+        # reading set l%2 while layer l-1 (other set) runs; layer l-2 waits for it before reusing the set.
+        #   a: dz1 (grad wrt attn_out / residual x)   b: dsa, then dx via QKV   c: dz2   d: da2 (dropped dz2)
+        #   e: dctx   wide: dpre   qkv: dqkv
+        self.gset = [SimpleNamespace(a=torch.empty(T, D, **bf), b=torch.empty(T, D, **bf), c=torch.empty(T, D, **bf),
+                                     d=torch.empty(T, D, **bf), e=torch.empty(T, D, **bf),
+                                     wide=torch.empty(T, Fh, **bf), qkv=torch.empty(T, 3 * D, **bf))
+                     for _ in range(2)]
         self.dcls = torch.empty(batch, D, **bf)
         # compact (one row per sample) buffers for the pruned tail of the last block
         self.c_x, self.c_ctx, self.c_tmp, self.c_sa, self.c_out = (torch.empty(batch, D, **bf) for _ in range(5))
@@ -264,71 +274,105 @@ class B200Engine:
         return outc
 
     # ------------------------------------------------------------------------------------------------ backward
-    def _backward(self) -> None:
+    def _fork(self, fn) -> None:
+        """Enqueue ``fn()`` (weight-gradient work that nothing on the main chain waits for) on the side stream, ordered
+        after everything issued on the current stream so far."""
+        if self._side is None:
+            fn()
+            return
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        self._side.wait_event(ev)
+        with torch.cuda.stream(self._side):
+            fn()
+
+    def _side_mark(self):
+        if self._side is None:
+            return None
+        ev = torch.cuda.Event()
+        ev.record(self._side)
+        return ev
+
+    @staticmethod
+    def _join(ev) -> None:
+        if ev is not None:
+            torch.cuda.current_stream().wait_event(ev)
+
+    def _wgrad(self, dy, act, dw, cfg, dbias_src=None, dbias=None) -> None:
+        """dW += dy^T act (fp32, TMA reduce-add split-K) and optionally dbias = colsum(dbias_src)."""
+        self._gemm(dy, act, dw, a_major=nv.MAJOR_MN, b_major=nv.MAJOR_MN, block_n=cfg[0], split_k=cfg[1],
+                   reduce_add=self.dp is not None)
+        if dbias is not None:
+            self._k(nv.colsum_bf16, dbias_src, dbias)
+
+    def _backward(self, early_adam: bool = False) -> None:
+        """Backward pass.  With ``early_adam`` (training step, single-GPU client, side stream on) the Adam update of a
+        block's GEMM weights is enqueued on the side stream as soon as that block's last data-gradient GEMM has been
+        issued: the HBM-bound optimizer pass then runs underneath the tensor-bound backward of the earlier blocks, and
+        ``_optimizer`` only has the embeddings / biases / LayerNorm / classifier region left."""
         d, S, B, pl = self.dims, self.S, self.B, self.plan
+        early_adam = early_adam and self._side is not None and self.dp is None
+        self._adam_early_done = early_adam
         H, D = d.n_heads, d.dim
         MN = nv.MAJOR_MN
         top = d.n_layers - 1
+        P = self.p
+        side_done = {}  # layer -> event marking the end of its side-stream work
         if self.prune_last_layer:
             dy1, dy2 = self._backward_tail_pruned(top)
         else:
             # gradient wrt the last hidden states: only the CLS rows are non-zero
-            self._k(nv.scatter_rows_bf16, self.dcls, self.g_a, B, D, S)
-            dy1, dy2 = self.g_a, None
+            dy1, dy2 = self.gset[(top + 1) % 2].a, None
+            self._k(nv.scatter_rows_bf16, self.dcls, dy1, B, D, S)
         for l in reversed(range(d.n_layers)):
             x, qkv, ctx, sa, pre, hmid = self.x[l], self.qkv[l], self.ctx[l], self.sa[l], self.pre[l], self.hmid[l]
-            P = self.p
+            G = self.gset[l % 2]
+            self._join(side_done.pop(l + 2, None))  # the side work of layer l+2 read this scratch set
             if self.prune_last_layer and l == top:
                 # the tail of this block already ran on the CLS rows: dy1 = d(ctx) scattered to all tokens, dy2 = the
                 # residual gradient wrt x (non-zero on the CLS rows only)
                 dctx, dz1 = dy1, dy2
-                self._k(nv.attn_bwd, qkv, ctx, dctx, self.lse2[l], self.g_qkv, self.lens, B, S, H,
-                        p_drop=d.attention_dropout, rng=self.rng, stream_id=_layer_stream(l, 0))
-                self._gemm(self.g_qkv, x, P["d_wqkv"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_qkv[0],
-                           split_k=pl.wgrad_qkv[1], reduce_add=self.dp is not None)
-                self._k(nv.colsum_bf16, self.g_qkv, P["d_bqkv"][l])
-                dxq = self.g_b
-                self._gemm(self.g_qkv, P["wqkv"][l], dxq, b_major=MN, block_n=pl.qkv_dgrad)
-                dy1, dy2 = dxq, dz1
-                continue
-            # output_layer_norm(dropout(ffn_out) + sa)
-            dz2 = self.g_c
-            da2 = self.g_d if d.dropout > 0 else dz2  # without dropout the two gradients coincide
-            self._k(nv.add_ln_bwd, dy1, dy2, self.x[l + 1], P["g2"][l], P["b2"][l], self.rstd2[l], dz2,
-                    da2 if d.dropout > 0 else None, P["d_g2"][l], P["d_b2"][l], P["d_bb2"][l], p_drop=d.dropout,
-                    rng=self.rng, stream_id=_layer_stream(l, 1))
-            # lin2: dW2 = da2^T hmid ; dpre = (da2 W2) * gelu'(pre)
-            self._gemm(da2, hmid, P["d_w2"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_lin2[0],
-                       split_k=pl.wgrad_lin2[1], reduce_add=self.dp is not None)
-            self._gemm(da2, P["w2"][l], self.g_wide, b_major=MN, aux=pre, epi=nv.EPI_DGELU, block_n=pl.lin2_dgrad)
-            # lin1: dW1 = dpre^T sa ; db1 = colsum(dpre) ; dsa = dpre W1
-            self._gemm(self.g_wide, sa, P["d_w1"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_lin1[0],
-                       split_k=pl.wgrad_lin1[1], reduce_add=self.dp is not None)
-            self._k(nv.colsum_bf16, self.g_wide, P["d_bb1"][l])
-            dsa = self.g_b  # dy1/dy2 of this layer (g_a/g_b) are dead after the LN backward above
-            self._gemm_splitk(self.g_wide, P["w1"][l], dsa, pl.lin1_dgrad, b_major=MN)
-            # sa_layer_norm(attn_out + x): dz1 is the gradient wrt both attn_out and the residual x
-            dz1 = self.g_a
-            self._k(nv.add_ln_bwd, dsa, dz2, sa, P["g1"][l], P["b1"][l], self.rstd1[l], dz1, None, P["d_g1"][l],
-                    P["d_b1"][l], P["d_bo"][l])
-            # out_lin: dWo = dz1^T ctx ; dctx = dz1 Wo
-            self._gemm(dz1, ctx, P["d_wo"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_out[0],
-                       split_k=pl.wgrad_out[1], reduce_add=self.dp is not None)
-            dctx = self.g_c
-            self._gemm(dz1, P["wo"][l], dctx, b_major=MN, block_n=pl.out_dgrad)
+            else:
+                # output_layer_norm(dropout(ffn_out) + sa)
+                dz2 = G.c
+                da2 = G.d if d.dropout > 0 else dz2  # without dropout the two gradients coincide
+                self._k(nv.add_ln_bwd, dy1, dy2, self.x[l + 1], P["g2"][l], P["b2"][l], self.rstd2[l], dz2,
+                        da2 if d.dropout > 0 else None, P["d_g2"][l], P["d_b2"][l], P["d_bb2"][l], p_drop=d.dropout,
+                        rng=self.rng, stream_id=_layer_stream(l, 1))
+                # lin2: dW2 = da2^T hmid (side) ; dpre = (da2 W2) * gelu'(pre)
+                self._fork(lambda: self._wgrad(da2, hmid, P["d_w2"][l], pl.wgrad_lin2))
+                self._gemm(da2, P["w2"][l], G.wide, b_major=MN, aux=pre, epi=nv.EPI_DGELU, block_n=pl.lin2_dgrad)
+                # lin1: dW1 = dpre^T sa, db1 = colsum(dpre) (side) ; dsa = dpre W1
+                self._fork(lambda: self._wgrad(G.wide, sa, P["d_w1"][l], pl.wgrad_lin1, G.wide, P["d_bb1"][l]))
+                dsa = G.b
+                self._gemm_splitk(G.wide, P["w1"][l], dsa, pl.lin1_dgrad, b_major=MN)
+                # sa_layer_norm(attn_out + x): dz1 is the gradient wrt both attn_out and the residual x
+                dz1 = G.a
+                self._k(nv.add_ln_bwd, dsa, dz2, sa, P["g1"][l], P["b1"][l], self.rstd1[l], dz1, None, P["d_g1"][l],
+                        P["d_b1"][l], P["d_bo"][l])
+                # out_lin: dWo = dz1^T ctx (side) ; dctx = dz1 Wo
+                self._fork(lambda: self._wgrad(dz1, ctx, P["d_wo"][l], pl.wgrad_out))
+                dctx = G.e
+                self._gemm(dz1, P["wo"][l], dctx, b_major=MN, block_n=pl.out_dgrad)
             # attention
-            self._k(nv.attn_bwd, qkv, ctx, dctx, self.lse2[l], self.g_qkv, self.lens, B, S, H,
+            self._k(nv.attn_bwd, qkv, ctx, dctx, self.lse2[l], G.qkv, self.lens, B, S, H,
                     p_drop=d.attention_dropout, rng=self.rng, stream_id=_layer_stream(l, 0))
-            # QKV: dWqkv = dqkv^T x ; dbqkv = colsum(dqkv) ; dx = dqkv Wqkv
-            self._gemm(self.g_qkv, x, P["d_wqkv"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_qkv[0],
-                       split_k=pl.wgrad_qkv[1], reduce_add=self.dp is not None)
-            self._k(nv.colsum_bf16, self.g_qkv, P["d_bqkv"][l])
-            dxq = self.g_b
-            self._gemm(self.g_qkv, P["wqkv"][l], dxq, b_major=MN, block_n=pl.qkv_dgrad)
+            # QKV: dWqkv = dqkv^T x, dbqkv = colsum(dqkv) (side) ; dx = dqkv Wqkv
+            self._fork(lambda: self._wgrad(G.qkv, x, P["d_wqkv"][l], pl.wgrad_qkv, G.qkv, P["d_bqkv"][l]))
+            dxq = G.b
+            self._gemm(G.qkv, P["wqkv"][l], dxq, b_major=MN, block_n=pl.qkv_dgrad)
+            if early_adam:  # nothing reads this block's weights any more, and its weight gradients precede on the side stream
+                lay = self.arena.layout
+                lo = lay.qkv_weight_offset(l)
+                hi = lay.qkv_weight_offset(l + 1) if l + 1 < d.n_layers else lay.gemm_end
+                self._fork(lambda: self._adam_range(lo, hi))
+            side_done[l] = self._side_mark()
             dy1, dy2 = dxq, dz1  # gradient wrt x_l = via QKV projection + via the residual
         self._k(nv.embed_ln_bwd, dy1, dy2, self.ids, self.word, self.pos, self.eg, self.emb_mean, self.emb_rstd,
                 self.d_word, self.d_pos, self.d_eg, self.d_eb, S, lens=self.lens, p_drop=d.dropout, rng=self.rng,
                 stream_id=_STREAM_EMBED)
+        for ev in side_done.values():  # every weight gradient is complete before the optimizer reads it
+            self._join(ev)
 
     def _backward_tail_pruned(self, l: int):
         """Backward of the pruned tail (LN2, FFN, LN1, out_lin of the last block) on the B CLS rows.  Returns
@@ -336,6 +380,7 @@ class B200Engine:
         d, S, B, pl, P = self.dims, self.S, self.B, self.plan, self.p
         D = d.dim
         MN = nv.MAJOR_MN
+        G = self.gset[l % 2]
         dz2, da2 = self.c_gc, (self.c_gd if d.dropout > 0 else self.c_gc)
         self._k(nv.add_ln_bwd, self.dcls, None, self.c_out, P["g2"][l], P["b2"][l], self.c_rstd2, dz2,
                 da2 if d.dropout > 0 else None, P["d_g2"][l], P["d_b2"][l], P["d_bb2"][l], p_drop=d.dropout,
@@ -355,16 +400,25 @@ class B200Engine:
                    reduce_add=self.dp is not None or pl.wgrad_out[1] > 1)
         dctx_c = self.c_gc  # dz2 is dead by now
         self._gemm(dz1, P["wo"][l], dctx_c, b_major=MN, block_n=pl.out_dgrad)
-        self._k(nv.scatter_rows_bf16, dctx_c, self.g_c, B, D, S)
-        self._k(nv.scatter_rows_bf16, dz1, self.g_a, B, D, S)
-        return self.g_c, self.g_a
+        self._k(nv.scatter_rows_bf16, dctx_c, G.e, B, D, S)
+        self._k(nv.scatter_rows_bf16, dz1, G.a, B, D, S)
+        return G.e, G.a
+
+    def _adam_range(self, lo: int, hi: int) -> None:
+        """Adam + zero_grad (+ bf16 mirror refresh for the GEMM-weight part) on arena elements [lo, hi)."""
+        a = self.arena
+        bf_hi = min(hi, a.layout.gemm_end)
+        self._k(nv.adam_step, a.flat[lo:hi], a.grad[lo:hi], a.exp_avg[lo:hi], a.exp_avg_sq[lo:hi],
+                a.bf16[lo:bf_hi] if bf_hi > lo else None, hi - lo, 0, max(bf_hi - lo, 0), 0, hi - lo, self.lr,
+                self.betas[0], self.betas[1], self.eps, self.rng)
 
     def _optimizer(self) -> None:
         a = self.arena
         lay = a.layout
         if self.dp is None:
-            self._k(nv.adam_step, a.flat, a.grad, a.exp_avg, a.exp_avg_sq, a.bf16, lay.total, 0, lay.gemm_end,
-                    0, lay.total, self.lr, self.betas[0], self.betas[1], self.eps, self.rng)
+            # GEMM weights were already updated block by block under the backward pass when early_adam was on
+            self._adam_range(lay.gemm_end if getattr(self, "_adam_early_done", False) else 0, lay.total)
+            self._adam_early_done = False
             self._k(nv.step_advance, self.rng)
             return
         # ---- data-parallel client: reduce-scatter (already done tile by tile for the GEMM weights by the wgrad
@@ -399,7 +453,7 @@ class B200Engine:
         self._k(nv.cls_head_train, h, stride, self.cw, self.cb, self.labels, self.B, self.loss_accum,
                 self.logits, self.d_cw, self.d_cb, self.dcls, cols=self.dims.dim, p_drop=self.dims.head_dropout,
                 rng=self.rng, stream_id=_STREAM_HEAD)
-        self._backward()
+        self._backward(early_adam=True)
         self._optimizer()
         self.launches_per_train_step = self._n_launch
 
@@ -417,7 +471,7 @@ class B200Engine:
 
     def capture(self) -> None:
         """Warm up eagerly, then capture the training step (and its end-to-end variant) into CUDA graphs."""
-        s = torch.cuda.Stream(device=self.device)
+        s = torch.cuda.Stream(device=self.device, priority=-1)  # the critical chain outranks the weight-gradient branch
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
             saved = (self.arena.flat.clone(), self.rng.clone())

@@ -28,6 +28,7 @@ ERRORS = {
 
 EPI_NONE, EPI_BIAS, EPI_BIAS_GELU, EPI_DGELU = 0, 1, 2, 3
 MAJOR_K, MAJOR_MN = 0, 1
+TILE_PAIR = 0x1000  # OR into block_n: 256 x block_n tile on a CTA pair (tcgen05.mma.cta_group::2)
 
 
 class NativeError(RuntimeError):

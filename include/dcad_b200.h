@@ -36,6 +36,10 @@ extern "C" {
 #define DCAD_MAJOR_K 0  /* operand stored [MN][K]: reduction dimension contiguous */
 #define DCAD_MAJOR_MN 1 /* operand stored [K][MN]: M (or N) dimension contiguous  */
 
+/* OR into block_n: run the tile on a CTA pair (cluster of two SMs, tcgen05.mma.cta_group::2, 256 x block_n tile);
+ * each SM then stages only half of the B operand.  block_n must be 128, 192 (K-major B only) or 256. */
+#define DCAD_TILE_PAIR 0x1000
+
 int dcad_version(void);
 
 /* Programmatic dependent launch for the training-step kernels (default on): each kernel releases its successor at

@@ -44,6 +44,50 @@ def test_gemm_matches_matmul(nv, a_major, b_major, bn):
     assert _rel(out, ref) < 1e-3
 
 
+@pytest.mark.parametrize("a_major,b_major,bn", [(0, 0, 128), (0, 0, 192), (0, 0, 256), (0, 1, 128), (0, 1, 256),
+                                                (1, 1, 128), (1, 1, 256)])
+def test_gemm_cta_pair_matches_matmul(nv, a_major, b_major, bn):
+    """cta_group::2 tiles (256 x bn on a CTA pair): odd number of 128-row blocks, ragged N, several tiles per pair."""
+    torch.manual_seed(1)
+    for (M, N, K) in [(384, 768, 320), (1152, 1304, 192), (16, 768, 768)]:
+        a = torch.randn((M, K) if a_major == 0 else (K, M), device="cuda").bfloat16()
+        b = torch.randn((N, K) if b_major == 0 else (K, N), device="cuda").bfloat16()
+        A = a.float() if a_major == 0 else a.float().t()
+        B = b.float() if b_major == 0 else b.float().t()
+        ref = A @ B.t()
+        for dt in (torch.float32, torch.bfloat16):
+            out = torch.full((M, N), float("nan"), device="cuda", dtype=dt)
+            nv.gemm_bf16(a, b, out, a_major=a_major, b_major=b_major, block_n=bn | nv.TILE_PAIR, max_ctas=8)
+            assert _rel(out, ref) < (1e-3 if dt == torch.float32 else 1e-2), (M, N, K, dt)
+
+
+def test_gemm_cta_pair_epilogues_and_splitk(nv):
+    torch.manual_seed(2)
+    M, N, K = 520, 768, 1536
+    a = torch.randn(M, K, device="cuda").bfloat16()
+    w = (torch.randn(N, K, device="cuda") * 0.05).bfloat16()
+    bias = torch.randn(N, device="cuda")
+    pre = a.float() @ w.float().t() + bias
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    aux_out = torch.empty_like(out)
+    nv.gemm_bf16(a, w, out, bias=bias, aux_out=aux_out, epi=nv.EPI_BIAS_GELU, block_n=256 | nv.TILE_PAIR)
+    assert _rel(out, F.gelu(pre)) < 1e-2 and _rel(aux_out, pre) < 1e-2
+    for split in (2, 3):
+        ws = torch.empty(nv.gemm_splitk_workspace_bytes(M, N, split) // 4, device="cuda")
+        out2 = torch.full((M, N), float("nan"), device="cuda", dtype=torch.bfloat16)
+        nv.gemm_bf16_splitk(a, w, out2, ws, split_k=split, epi=nv.EPI_BIAS, bias=bias, block_n=256 | nv.TILE_PAIR)
+        assert _rel(out2, pre) < 1e-2, split
+    # weight-gradient form with TMA reduce-add split-K
+    T, Nw, Kw = 2048, 768, 512
+    dy = torch.randn(T, Nw, device="cuda").bfloat16()
+    x = torch.randn(T, Kw, device="cuda").bfloat16()
+    ref = dy.float().t() @ x.float()
+    for split in (1, 2, 4):
+        g = torch.zeros(Nw, Kw, device="cuda")
+        nv.gemm_bf16(dy, x, g, a_major=nv.MAJOR_MN, b_major=nv.MAJOR_MN, block_n=256 | nv.TILE_PAIR, split_k=split)
+        assert _rel(g, ref) < 1e-3, split
+
+
 def test_gemm_split_k_reduce_add(nv):
     torch.manual_seed(11)
     T, Nw, Kw = 2048, 768, 512      # dW[Nw, Kw] = dY[T, Nw]^T X[T, Kw]

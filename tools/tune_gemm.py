@@ -67,28 +67,33 @@ def main():
         B = b if bm == 0 else b.t()
         cub = time_graph(lambda: torch.matmul(A, B.t()))
         row = {"name": name, "M": M, "N": N, "K": K, "cublas_us": cub, "bn": {}}
+        P = nv.TILE_PAIR  # "p" prefix below = 256 x bn tile on a CTA pair (cta_group::2)
+        lab = lambda bn: ("p" if bn & P else "") + str(bn & ~P)  # noqa: E731
         cands = [(bn, 1) for bn in (64, 128, 192, 256) if N % bn == 0]
+        cands += [(bn | P, 1) for bn in (128, 192, 256) if N % bn == 0 and not (bn == 192 and bm == 1)]
         if wgrad:
-            cands = [(bn, sk) for bn in (128, 256) for sk in (1, 2, 3, 4, 8)]
+            cands = [(bn, sk) for bn in (128, 256, 128 | P, 256 | P) for sk in (1, 2, 3, 4, 8)]
         for bn, sk in cands:
+            key = f"{lab(bn)}/{sk}" if wgrad else lab(bn)
             try:
                 if wgrad:
                     out.zero_()
                 us = time_graph(lambda: nv.gemm_bf16(a, b, out, a_major=am, b_major=bm, bias=bias, aux=aux,
                                                      aux_out=aux_out, epi=epi, block_n=bn, split_k=sk))
-                row["bn"][f"{bn}/{sk}" if wgrad else bn] = us
+                row["bn"][key] = us
             except Exception as e:  # noqa: BLE001
-                row["bn"][f"{bn}/{sk}"] = None
-                row.setdefault("errors", {})[f"{bn}/{sk}"] = repr(e)[:120]
-        if name in ("lin2_fwd", "lin1_dgrad", "out_fwd", "out_dgrad"):
-            for bn, sk in ((256, 2), (256, 3), (256, 4), (128, 2), (128, 3)):
+                row["bn"][key] = None
+                row.setdefault("errors", {})[key] = repr(e)[:120]
+        if name in ("lin2_fwd", "lin1_dgrad", "out_fwd", "out_dgrad", "qkv_dgrad"):
+            for bn, sk in ((256, 2), (256, 3), (256, 4), (128, 2), (128, 3), (256 | P, 2), (256 | P, 3), (256 | P, 4),
+                           (256 | P, 6), (128 | P, 2), (128 | P, 3)):
                 ws = torch.empty(nv.gemm_splitk_workspace_bytes(M, N, sk) // 4, device=dev)
                 try:
                     us = time_graph(lambda: nv.gemm_bf16_splitk(a, b, out, ws, split_k=sk, a_major=am, b_major=bm,
                                                                 bias=bias, aux=aux, aux_out=aux_out, epi=epi, block_n=bn))
-                    row["bn"][f"ws{bn}/{sk}"] = us
+                    row["bn"][f"ws{lab(bn)}/{sk}"] = us
                 except Exception as e:  # noqa: BLE001
-                    row["bn"][f"ws{bn}/{sk}"] = None
+                    row["bn"][f"ws{lab(bn)}/{sk}"] = None
         ok = {k: v for k, v in row["bn"].items() if v}
         row["best_bn"] = min(ok, key=ok.get) if ok else None
         row["best_us"] = ok[row["best_bn"]] if ok else None
