@@ -14,7 +14,8 @@ __global__ void __launch_bounds__(256)
 adam_flat_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                  __nv_bfloat16* __restrict__ p_bf16, int64_t n, int64_t bf16_begin, int64_t bf16_end,
                  int64_t zero_begin, int64_t zero_end, float lr, float beta1, float beta2, float eps,
-                 const uint64_t* __restrict__ state) {
+                 const uint64_t* __restrict__ state, const uint8_t* __restrict__ row_flags, int64_t rows_begin,
+                 int64_t rows_end, int row_len) {
     __shared__ float s_c[2];
     pdl_trigger();
     pdl_wait();
@@ -30,6 +31,8 @@ adam_flat_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict
     const float omb1 = 1.0f - beta1, omb2 = 1.0f - beta2;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x * 4;
     for (int64_t i = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 4; i < n; i += stride) {
+        // embedding rows that never received a gradient have g = m = v = 0: the update is the identity
+        if (row_flags && i >= rows_begin && i < rows_end && !row_flags[(i - rows_begin) / row_len]) continue;
         float4 pp = *reinterpret_cast<const float4*>(p + i);
         const float4 gg = *reinterpret_cast<const float4*>(g + i);
         float4 mm = *reinterpret_cast<const float4*>(m + i);
@@ -144,10 +147,13 @@ __global__ void step_advance_kernel(uint64_t* state) {
 using namespace dcad;
 
 // n, bf16_begin/end, zero_begin/end are element offsets into the arena and must be multiples of 4.
-extern "C" int dcad_adam_step(float* p, float* g, float* m, float* v, void* p_bf16, int64_t n, int64_t bf16_begin,
-                              int64_t bf16_end, int64_t zero_begin, int64_t zero_end, float lr, float beta1,
-                              float beta2, float eps, const uint64_t* state, void* stream) {
+extern "C" int dcad_adam_step_rows(float* p, float* g, float* m, float* v, void* p_bf16, int64_t n,
+                                   int64_t bf16_begin, int64_t bf16_end, int64_t zero_begin, int64_t zero_end,
+                                   float lr, float beta1, float beta2, float eps, const uint64_t* state,
+                                   const uint8_t* row_flags, int64_t rows_begin, int64_t rows_end, int row_len,
+                                   void* stream) {
     if (n <= 0) return 0;
+    if (row_flags && (row_len <= 0 || (row_len & 3) || (rows_begin & 3))) return DCAD_ERR_BAD_ALIGNMENT;
     if ((n | bf16_begin | bf16_end | zero_begin | zero_end) & 3) return DCAD_ERR_BAD_ALIGNMENT;
     if ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) |
          reinterpret_cast<uintptr_t>(v)) & 15u)
@@ -157,7 +163,15 @@ extern "C" int dcad_adam_step(float* p, float* g, float* m, float* v, void* p_bf
     if (blocks > cap) blocks = cap;
     return (int)launch_pdl(adam_flat_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0,
                            reinterpret_cast<cudaStream_t>(stream), p, g, m, v, reinterpret_cast<__nv_bfloat16*>(p_bf16),
-                           n, bf16_begin, bf16_end, zero_begin, zero_end, lr, beta1, beta2, eps, state);
+                           n, bf16_begin, bf16_end, zero_begin, zero_end, lr, beta1, beta2, eps, state, row_flags,
+                           rows_begin, rows_end, row_len);
+}
+
+extern "C" int dcad_adam_step(float* p, float* g, float* m, float* v, void* p_bf16, int64_t n, int64_t bf16_begin,
+                              int64_t bf16_end, int64_t zero_begin, int64_t zero_end, float lr, float beta1,
+                              float beta2, float eps, const uint64_t* state, void* stream) {
+    return dcad_adam_step_rows(p, g, m, v, p_bf16, n, bf16_begin, bf16_end, zero_begin, zero_end, lr, beta1, beta2,
+                               eps, state, nullptr, 0, 0, 1, stream);
 }
 
 extern "C" int dcad_step_advance(uint64_t* state, void* stream) {

@@ -244,7 +244,8 @@ embed_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy1, const __nv_bfloat16* 
                     const float* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ rstd,
                     float* __restrict__ dword, float* __restrict__ dpos, float* __restrict__ dgamma,
                     float* __restrict__ dbeta, const int32_t* __restrict__ lens, int rows, int seq, uint32_t thresh,
-                    float keep_scale, const uint64_t* __restrict__ rng, uint32_t stream_id) {
+                    float keep_scale, const uint64_t* __restrict__ rng, uint32_t stream_id,
+                    uint8_t* __restrict__ touched) {
     pdl_trigger();
     pdl_wait();
     constexpr int COLS = NV * 256;
@@ -258,6 +259,7 @@ embed_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy1, const __nv_bfloat16* 
     if (active) {
         const int id = ids[row];
         const int ps = row % seq;
+        if (touched && lane == 0) touched[id] = 1;  // this vocabulary row now has optimizer state (see adam.cu)
         const float mu = mean[row], rs = rstd[row];
         float g[NV][8], xh[NV][8], d[NV][8];
         float c1 = 0.f, c2 = 0.f;
@@ -433,7 +435,7 @@ extern "C" int dcad_embed_ln_bwd(const void* dy1, const void* dy2, const int32_t
                                  const float* pos, const float* gamma, const float* mean, const float* rstd,
                                  float* dword, float* dpos, float* dgamma, float* dbeta, const int32_t* lens, int rows,
                                  int seq, int cols, float p_drop, const uint64_t* rng, uint32_t stream_id,
-                                 void* stream) {
+                                 uint8_t* touched_rows, void* stream) {
     if (rows <= 0) return 0;
     if (cols % 256 || cols > 1024 || seq <= 0) return DCAD_ERR_BAD_SHAPE;
     if (p_drop > 0.f && rng == nullptr) return DCAD_ERR_BAD_ARGUMENT;
@@ -452,7 +454,7 @@ extern "C" int dcad_embed_ln_bwd(const void* dy1, const void* dy2, const int32_t
         return (int)launch_pdl(
             embed_ln_bwd_kernel<NV>, dim3(grid), dim3(LN_WARPS * 32), smem, s,
             reinterpret_cast<const __nv_bfloat16*>(dy1), reinterpret_cast<const __nv_bfloat16*>(dy2), ids, word, pos,
-            gamma, mean, rstd, dword, dpos, dgamma, dbeta, lens, rows, seq, th, ks, rng, stream_id);
+            gamma, mean, rstd, dword, dpos, dgamma, dbeta, lens, rows, seq, th, ks, rng, stream_id, touched_rows);
     });
     return 0;
 }

@@ -32,6 +32,9 @@ _STREAM_EMBED = 1
 _STREAM_HEAD = 2
 
 
+_WORD_EMB = "distilbert.embeddings.word_embeddings.weight"
+
+
 def _layer_stream(layer: int, site: int) -> int:
     return 16 + layer * 4 + site  # site 0 = attention probs, 1 = FFN output
 
@@ -53,6 +56,11 @@ class GemmPlan:
     wgrad_lin2: tuple = (256, 2)   # [768, 3072]
     wgrad_qkv: tuple = (256, 2)    # [2304, 768]
     wgrad_out: tuple = (128, 4)    # [768, 768]
+    # CLS-row tail of the last block (M = batch rows): latency-bound, so narrow tiles spread the weight matrix over
+    # many SMs and the K = 3072 reductions are cut eight ways (TOKENS=16 tools/tune_gemm.py)
+    tail_bn: int = 64
+    tail_long_k: tuple = (64, 8)
+    tail_wgrad_bn: int = 128
 
 
 class B200Engine:
@@ -140,8 +148,14 @@ class B200Engine:
         self.logits = torch.empty(batch, dims.n_classes, **f32)
         # scratch for the split-K GEMMs (fp32 partial tiles), sized for the larger of the two users
         sk = max(self.plan.lin2_fwd[1], self.plan.lin1_dgrad[1], 2)
-        self.splitk_ws = torch.empty(nv.gemm_splitk_workspace_bytes(T, D, sk) // 4, **f32)
+        ws_bytes = max(nv.gemm_splitk_workspace_bytes(T, D, sk),
+                       nv.gemm_splitk_workspace_bytes(batch, D, self.plan.tail_long_k[1]))
+        self.splitk_ws = torch.empty(ws_bytes // 4, **f32)
         # device-side accumulators
+        # vocabulary rows that have ever received a gradient since the optimizer state was last reset: Adam skips the
+        # others (their g, m and v are exactly zero, so the update is the identity) -- flow sentences use a small
+        # part of the 30522-row table, which is more than a third of all parameters
+        self.touched_rows = torch.zeros(dims.vocab_size, device=dev, dtype=torch.uint8)
         self.loss_accum = torch.zeros(2, **f32)                       # {sum of batch-mean losses, #batches}
         self.eval_loss_accum = torch.zeros(2, **f32)
         self.confusion = torch.zeros(4, device=dev, dtype=torch.int32)  # [true*2 + pred]
@@ -205,24 +219,39 @@ class B200Engine:
         self.arena.exp_avg.zero_()
         self.arena.exp_avg_sq.zero_()
         self.arena.grad.zero_()
+        self.touched_rows.zero_()
         self.rng[1] = 0
 
     # ------------------------------------------------------------------------------------------------ helpers
-    def _gemm(self, *args, **kw):
-        self._n_launch += 1
-        return nv.gemm_bf16(*args, **kw)
+    # Every launch goes through _count(): it keeps the per-step launch count, and -- profiling aid used by
+    # tools/prefix_profile.py -- can log launch names or cut the step short after ``_launch_limit`` launches.
+    _launch_limit: Optional[int] = None
+    _launch_log: Optional[list] = None
+
+    def _count(self, n: int, name: str) -> bool:
+        if self._launch_limit is not None and self._n_launch + n > self._launch_limit:
+            return False
+        self._n_launch += n
+        if self._launch_log is not None:
+            side = self._side is not None and torch.cuda.current_stream() == self._side
+            self._launch_log.extend([name + (" [side]" if side else "")] * n)
+        return True
+
+    def _gemm(self, a, b, out, **kw):
+        if self._count(1, f"gemm {tuple(out.shape)} k={a.shape[1] if kw.get('a_major', 0) == 0 else a.shape[0]}"):
+            nv.gemm_bf16(a, b, out, **kw)
 
     def _gemm_splitk(self, a, b, out, cfg, **kw):
         """(BLOCK_N, split_k) GEMM: plain persistent GEMM when split_k == 1, else two launches through the workspace."""
         bn, sk = cfg
         if sk <= 1:
             return self._gemm(a, b, out, block_n=bn, **kw)
-        self._n_launch += 2
-        return nv.gemm_bf16_splitk(a, b, out, self.splitk_ws, split_k=sk, block_n=bn, **kw)
+        if self._count(2, f"gemm_splitk{sk} {tuple(out.shape)} k={a.shape[1]}"):
+            nv.gemm_bf16_splitk(a, b, out, self.splitk_ws, split_k=sk, block_n=bn, **kw)
 
     def _k(self, fn, *args, **kw):
-        self._n_launch += 1
-        return fn(*args, **kw)
+        if self._count(1, fn.__name__):
+            return fn(*args, **kw)
 
     # ------------------------------------------------------------------------------------------------ forward
     def _forward(self, rows_b: int, train: bool):
@@ -262,11 +291,11 @@ class B200Engine:
         prec, hmidc = self.c_pre[:Bc], self.c_hmid[:Bc]
         self._k(nv.gather_rows_bf16, self.ctx[l], ctxc, Bc, d.dim, S)
         self._k(nv.gather_rows_bf16, self.x[l], xc, Bc, d.dim, S)
-        self._gemm(ctxc, P["wo"][l], tmpc, bias=P["bo"][l], epi=nv.EPI_BIAS, block_n=pl.out_fwd)
+        self._gemm(ctxc, P["wo"][l], tmpc, bias=P["bo"][l], epi=nv.EPI_BIAS, block_n=pl.tail_bn)
         self._k(nv.add_ln_fwd, tmpc, xc, P["g1"][l], P["b1"][l], sac, self.c_rstd1[:Bc], eps=d.ln_eps)
         self._gemm(sac, P["w1"][l], hmidc, bias=P["bb1"][l], aux_out=prec if train else None, epi=nv.EPI_BIAS_GELU,
-                   block_n=pl.lin1_fwd)
-        self._gemm(hmidc, P["w2"][l], tmpc, bias=P["bb2"][l], epi=nv.EPI_BIAS, block_n=pl.lin2_fwd[0])
+                   block_n=pl.tail_bn)
+        self._gemm_splitk(hmidc, P["w2"][l], tmpc, pl.tail_long_k, bias=P["bb2"][l], epi=nv.EPI_BIAS)
         # dropout indices differ from the unpruned layout (row = sample instead of token); masks stay consistent
         # between forward and backward because both use the compact indexing
         self._k(nv.add_ln_fwd, tmpc, sac, P["g2"][l], P["b2"][l], outc, self.c_rstd2[:Bc], eps=d.ln_eps, p_drop=p_h,
@@ -370,7 +399,7 @@ class B200Engine:
             dy1, dy2 = dxq, dz1  # gradient wrt x_l = via QKV projection + via the residual
         self._k(nv.embed_ln_bwd, dy1, dy2, self.ids, self.word, self.pos, self.eg, self.emb_mean, self.emb_rstd,
                 self.d_word, self.d_pos, self.d_eg, self.d_eb, S, lens=self.lens, p_drop=d.dropout, rng=self.rng,
-                stream_id=_STREAM_EMBED)
+                stream_id=_STREAM_EMBED, touched=self.touched_rows)
         for ev in side_done.values():  # every weight gradient is complete before the optimizer reads it
             self._join(ev)
 
@@ -385,21 +414,23 @@ class B200Engine:
         self._k(nv.add_ln_bwd, self.dcls, None, self.c_out, P["g2"][l], P["b2"][l], self.c_rstd2, dz2,
                 da2 if d.dropout > 0 else None, P["d_g2"][l], P["d_b2"][l], P["d_bb2"][l], p_drop=d.dropout,
                 rng=self.rng, stream_id=_layer_stream(l, 1))
-        self._gemm(da2, self.c_hmid, P["d_w2"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_lin2[0],
-                   reduce_add=self.dp is not None or pl.wgrad_lin2[1] > 1)
-        self._gemm(da2, P["w2"][l], self.c_gwide, b_major=MN, aux=self.c_pre, epi=nv.EPI_DGELU, block_n=pl.lin2_dgrad)
-        self._gemm(self.c_gwide, self.c_sa, P["d_w1"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_lin1[0],
-                   reduce_add=self.dp is not None or pl.wgrad_lin1[1] > 1)
+        # weight gradients of this block come from the CLS rows only: plain stores (reduce-add into the owner GPU's
+        # arena for a data-parallel client)
+        self._gemm(da2, self.c_hmid, P["d_w2"][l], a_major=MN, b_major=MN, block_n=pl.tail_wgrad_bn,
+                   reduce_add=self.dp is not None)
+        self._gemm(da2, P["w2"][l], self.c_gwide, b_major=MN, aux=self.c_pre, epi=nv.EPI_DGELU, block_n=pl.tail_bn)
+        self._gemm(self.c_gwide, self.c_sa, P["d_w1"][l], a_major=MN, b_major=MN, block_n=pl.tail_wgrad_bn,
+                   reduce_add=self.dp is not None)
         self._k(nv.colsum_bf16, self.c_gwide, P["d_bb1"][l])
         dsa = self.c_gb
-        self._gemm(self.c_gwide, P["w1"][l], dsa, b_major=MN, block_n=pl.lin1_dgrad[0])
+        self._gemm_splitk(self.c_gwide, P["w1"][l], dsa, pl.tail_long_k, b_major=MN)
         dz1 = self.c_ga
         self._k(nv.add_ln_bwd, dsa, dz2, self.c_sa, P["g1"][l], P["b1"][l], self.c_rstd1, dz1, None, P["d_g1"][l],
                 P["d_b1"][l], P["d_bo"][l])
-        self._gemm(dz1, self.c_ctx, P["d_wo"][l], a_major=MN, b_major=MN, block_n=pl.wgrad_out[0],
-                   reduce_add=self.dp is not None or pl.wgrad_out[1] > 1)
+        self._gemm(dz1, self.c_ctx, P["d_wo"][l], a_major=MN, b_major=MN, block_n=pl.tail_wgrad_bn,
+                   reduce_add=self.dp is not None)
         dctx_c = self.c_gc  # dz2 is dead by now
-        self._gemm(dz1, P["wo"][l], dctx_c, b_major=MN, block_n=pl.out_dgrad)
+        self._gemm(dz1, P["wo"][l], dctx_c, b_major=MN, block_n=pl.tail_bn)
         self._k(nv.scatter_rows_bf16, dctx_c, G.e, B, D, S)
         self._k(nv.scatter_rows_bf16, dz1, G.a, B, D, S)
         return G.e, G.a
@@ -408,9 +439,15 @@ class B200Engine:
         """Adam + zero_grad (+ bf16 mirror refresh for the GEMM-weight part) on arena elements [lo, hi)."""
         a = self.arena
         bf_hi = min(hi, a.layout.gemm_end)
-        self._k(nv.adam_step, a.flat[lo:hi], a.grad[lo:hi], a.exp_avg[lo:hi], a.exp_avg_sq[lo:hi],
+        w0 = a.layout.offsets[_WORD_EMB]
+        w1 = w0 + a.layout.numel(_WORD_EMB)
+        args = (a.flat[lo:hi], a.grad[lo:hi], a.exp_avg[lo:hi], a.exp_avg_sq[lo:hi],
                 a.bf16[lo:bf_hi] if bf_hi > lo else None, hi - lo, 0, max(bf_hi - lo, 0), 0, hi - lo, self.lr,
                 self.betas[0], self.betas[1], self.eps, self.rng)
+        if lo <= w0 and w1 <= hi:  # the range holds the word-embedding table: skip rows without optimizer state
+            self._k(nv.adam_step_rows, *args, self.touched_rows, w0 - lo, w1 - lo, self.dims.dim)
+        else:
+            self._k(nv.adam_step, *args)
 
     def _optimizer(self) -> None:
         a = self.arena

@@ -96,11 +96,12 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("dcad_add_ln_fwd", [P, P, P, P, P, P, I, I, F, F, P, U32, P])
     sig("dcad_add_ln_bwd", [P, P, P, P, P, P, P, P, P, P, P, I, I, F, P, U32, P])
     sig("dcad_embed_ln_fwd", [P, P, P, P, P, P, P, P, I, I, I, F, F, P, U32, P])
-    sig("dcad_embed_ln_bwd", [P, P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, F, P, U32, P])
+    sig("dcad_embed_ln_bwd", [P, P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, F, P, U32, P, P])
     sig("dcad_colsum_bf16", [P, P, I, I, I, P])
     sig("dcad_cls_head_train", [P, I, P, P, P, I, F, P, U32, P, P, P, P, P, I, P])
     sig("dcad_cls_head_eval", [P, I, P, P, P, I, I, P, P, P, P, P])
     sig("dcad_adam_step", [P, P, P, P, P, L64, L64, L64, L64, L64, F, F, F, F, P, P])
+    sig("dcad_adam_step_rows", [P, P, P, P, P, L64, L64, L64, L64, L64, F, F, F, F, P, P, L64, L64, I, P])
     sig("dcad_step_advance", [P, P])
     sig("dcad_adam_step_dp", [P, P, P, P, L64, L64, L64, L64, L64, L64, F, F, F, F, F, P, P, P, I, I, P])
     sig("dcad_xgpu_barrier", [P, I, I, P, U32, P])
@@ -226,11 +227,14 @@ def embed_ln_fwd(ids, word, pos, gamma, beta, out, mean, rstd, seq, *, eps=1e-12
 
 
 def embed_ln_bwd(dy1, dy2, ids, word, pos, gamma, mean, rstd, dword, dpos, dgamma, dbeta, seq, *, lens=None,
-                 p_drop=0.0, rng=None, stream_id=0, stream=None):
+                 p_drop=0.0, rng=None, stream_id=0, touched=None, stream=None):
+    """``touched`` (uint8 [vocab], optional): set to 1 for every vocabulary row that receives a gradient."""
     rows, cols = dy1.shape
+    assert touched is None or touched.dtype == torch.uint8
     check(lib().dcad_embed_ln_bwd(ptr(dy1), ptr(dy2), ptr(ids), ptr(word), ptr(pos), ptr(gamma), ptr(mean),
                                   ptr(rstd), ptr(dword), ptr(dpos), ptr(dgamma), ptr(dbeta), ptr(lens), rows, seq,
-                                  cols, p_drop, ptr(rng), stream_id, stream_ptr(stream)), "dcad_embed_ln_bwd")
+                                  cols, p_drop, ptr(rng), stream_id, ptr(touched), stream_ptr(stream)),
+          "dcad_embed_ln_bwd")
 
 
 def colsum_bf16(x, out, stream=None):
@@ -265,6 +269,16 @@ def adam_step(p, g, m, v, p_bf16, n, bf16_begin, bf16_end, zero_begin, zero_end,
               stream=None):
     check(lib().dcad_adam_step(ptr(p), ptr(g), ptr(m), ptr(v), ptr(p_bf16), n, bf16_begin, bf16_end, zero_begin,
                                zero_end, lr, beta1, beta2, eps, ptr(state), stream_ptr(stream)), "dcad_adam_step")
+
+
+def adam_step_rows(p, g, m, v, p_bf16, n, bf16_begin, bf16_end, zero_begin, zero_end, lr, beta1, beta2, eps, state,
+                   row_flags, rows_begin, rows_end, row_len, stream=None):
+    """Adam over ``n`` elements where [rows_begin, rows_end) is a table of ``row_len``-element rows and rows whose
+    byte in ``row_flags`` is 0 (never received a gradient: g = m = v = 0) are skipped -- an exact no-op for them."""
+    assert row_flags.dtype == torch.uint8
+    check(lib().dcad_adam_step_rows(ptr(p), ptr(g), ptr(m), ptr(v), ptr(p_bf16), n, bf16_begin, bf16_end, zero_begin,
+                                    zero_end, lr, beta1, beta2, eps, ptr(state), ptr(row_flags), rows_begin, rows_end,
+                                    row_len, stream_ptr(stream)), "dcad_adam_step_rows")
 
 
 def adam_step_dp(p, g, m, v, begin, end, bf16_begin, bf16_end, push32_begin, push32_end, lr, beta1, beta2, eps,

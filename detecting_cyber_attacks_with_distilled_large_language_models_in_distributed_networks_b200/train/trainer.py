@@ -152,6 +152,7 @@ class B200Backend:
                            flat_params=main.arena.flat, bf16_params=main.arena.bf16, init_seed=None)
             e.arena.grad, e.arena.exp_avg, e.arena.exp_avg_sq = main.arena.grad, main.arena.exp_avg, main.arena.exp_avg_sq
             e.rng, e.loss_accum = main.rng, main.loss_accum
+            e.touched_rows = main.touched_rows  # part of the optimizer state (which vocabulary rows have moments)
             e._bind_params()
             cache[b] = e
         e = cache[b]

@@ -115,11 +115,12 @@ int dcad_embed_ln_fwd(const int32_t* ids, const float* word, const float* pos, c
                       const uint64_t* rng, uint32_t stream_id, void* stream);
 /* backward: scatter-adds into dword [vocab, cols] / dpos [max_pos, cols] and accumulates dgamma / dbeta.
  * lens [rows / seq] (may be NULL): rows at or past a sample's valid length are padding with an exactly-zero
- * gradient and are skipped. */
+ * gradient and are skipped.  touched_rows [vocab] (may be NULL): byte flags, set to 1 for every vocabulary row that
+ * receives a gradient -- dcad_adam_step_rows() uses them to skip rows that never had one. */
 int dcad_embed_ln_bwd(const void* dy1, const void* dy2, const int32_t* ids, const float* word, const float* pos,
                       const float* gamma, const float* mean, const float* rstd, float* dword, float* dpos,
                       float* dgamma, float* dbeta, const int32_t* lens, int rows, int seq, int cols, float p_drop,
-                      const uint64_t* rng, uint32_t stream_id, void* stream);
+                      const uint64_t* rng, uint32_t stream_id, uint8_t* touched_rows, void* stream);
 /* out[c] += sum_r x[r, c]  (bf16 in, fp32 accumulate): bias gradients (autograd of nn.Linear bias). */
 int dcad_colsum_bf16(const void* x, float* out, int rows, int cols, int ld, void* stream);
 
@@ -141,6 +142,13 @@ int dcad_cls_head_eval(const void* h, int sample_stride, const float* W, const f
 int dcad_adam_step(float* p, float* g, float* m, float* v, void* p_bf16, int64_t n, int64_t bf16_begin,
                    int64_t bf16_end, int64_t zero_begin, int64_t zero_end, float lr, float beta1, float beta2,
                    float eps, const uint64_t* state, void* stream);
+/* Same update, but elements [rows_begin, rows_end) form a table of rows of row_len elements (the word embeddings) and
+ * a row is skipped while row_flags[row] == 0.  Exact, not an approximation: a row that never received a gradient has
+ * g = m = v = 0, so Adam leaves it unchanged (no weight decay in the reference, client1.py:380). */
+int dcad_adam_step_rows(float* p, float* g, float* m, float* v, void* p_bf16, int64_t n, int64_t bf16_begin,
+                        int64_t bf16_end, int64_t zero_begin, int64_t zero_end, float lr, float beta1, float beta2,
+                        float eps, const uint64_t* state, const uint8_t* row_flags, int64_t rows_begin,
+                        int64_t rows_end, int row_len, void* stream);
 int dcad_step_advance(uint64_t* state, void* stream);
 /* Intra-client data parallelism (no counterpart in the reference, which has no DP): sharded Adam over the arena
  * elements [begin, end) this rank owns, gradients scaled by grad_scale (1/G after a sum over the group), with the

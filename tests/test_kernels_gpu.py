@@ -262,7 +262,12 @@ def test_embed_ln_fwd_bwd(nv):
     dpos = torch.zeros(512, cols, device="cuda")
     dg = torch.zeros(cols, device="cuda")
     db = torch.zeros(cols, device="cuda")
-    nv.embed_ln_bwd(dy, None, ids, word.detach(), pos.detach(), gamma.detach(), mean, rstd, dword, dpos, dg, db, S)
+    touched = torch.zeros(vocab, device="cuda", dtype=torch.uint8)
+    nv.embed_ln_bwd(dy, None, ids, word.detach(), pos.detach(), gamma.detach(), mean, rstd, dword, dpos, dg, db, S,
+                    touched=touched)
+    exp_touched = torch.zeros(vocab, device="cuda", dtype=torch.uint8)
+    exp_touched[ids.long()] = 1
+    assert torch.equal(touched, exp_touched)
     assert _rel(dword, word.grad) < 1e-2
     assert _rel(dpos, pos.grad) < 1e-2
     assert _rel(dg, gamma.grad) < 1e-2
@@ -338,6 +343,38 @@ def test_adam_matches_torch(nv):
     assert torch.allclose(p, ref_p.detach(), rtol=1e-5, atol=1e-7)
     assert torch.equal(pb, p[n // 2:].bfloat16())
     assert state[1].item() == 5
+
+
+def test_adam_row_skipping_is_exact(nv):
+    """Rows of an embedding-like table without a gradient so far are skipped; the result equals dense torch Adam."""
+    torch.manual_seed(5)
+    head, rows, cols, tailn = 1024, 300, 256, 512        # [head | table rows x cols | tail]
+    n = head + rows * cols + tailn
+    p0 = torch.randn(n, device="cuda")
+    p, m, v = p0.clone(), torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    state = _rng_state(step=0)
+    flags = torch.zeros(rows, device="cuda", dtype=torch.uint8)
+    ref_p = p0.clone().requires_grad_(True)
+    opt = torch.optim.Adam([ref_p], lr=1e-3)
+    for step in range(6):
+        g = torch.randn(n, device="cuda")
+        hit = torch.randperm(rows, device="cuda")[: 40 if step < 4 else 0]  # later steps: moments only
+        mask = torch.zeros(rows, device="cuda", dtype=torch.bool)
+        mask[hit] = True
+        g[head: head + rows * cols].view(rows, cols)[~mask] = 0.0
+        flags[hit] = 1
+        ref_p.grad = g.clone()
+        opt.step()
+        gk = g.clone()
+        nv.adam_step_rows(p, gk, m, v, None, n, 0, 0, 0, n, 1e-3, 0.9, 0.999, 1e-8, state, flags, head,
+                          head + rows * cols, cols)
+        nv.step_advance(state)
+        assert torch.all(gk == 0)
+    assert torch.allclose(p, ref_p.detach(), rtol=1e-5, atol=1e-7)
+    untouched = flags == 0
+    assert untouched.any()
+    assert torch.equal(p[head: head + rows * cols].view(rows, cols)[untouched],
+                       p0[head: head + rows * cols].view(rows, cols)[untouched])
 
 
 # ---------------------------------------------------------------- attention

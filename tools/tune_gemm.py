@@ -84,9 +84,13 @@ def main():
             except Exception as e:  # noqa: BLE001
                 row["bn"][key] = None
                 row.setdefault("errors", {})[key] = repr(e)[:120]
-        if name in ("lin2_fwd", "lin1_dgrad", "out_fwd", "out_dgrad", "qkv_dgrad"):
-            for bn, sk in ((256, 2), (256, 3), (256, 4), (128, 2), (128, 3), (256 | P, 2), (256 | P, 3), (256 | P, 4),
-                           (256 | P, 6), (128 | P, 2), (128 | P, 3)):
+        if name in ("lin2_fwd", "lin1_dgrad", "out_fwd", "out_dgrad", "qkv_dgrad") or (T <= 128 and not wgrad):
+            ws_cands = ((256, 2), (256, 3), (256, 4), (128, 2), (128, 3), (256 | P, 2), (256 | P, 3), (256 | P, 4),
+                        (256 | P, 6), (128 | P, 2), (128 | P, 3))
+            if T <= 128:  # the CLS-row tail of the last block: few output tiles, latency-bound
+                ws_cands = ((64, 2), (64, 4), (64, 8), (128, 4), (128, 8), (128, 12), (256, 4), (256, 8), (256, 12),
+                            (256, 16))
+            for bn, sk in ws_cands:
                 ws = torch.empty(nv.gemm_splitk_workspace_bytes(M, N, sk) // 4, device=dev)
                 try:
                     us = time_graph(lambda: nv.gemm_bf16_splitk(a, b, out, ws, split_k=sk, a_major=am, b_major=bm,
@@ -106,7 +110,7 @@ def main():
     totc = sum(r["cublas_us"] for r in res) * 6
     print(f"sum over 6 layers: ours(best) {tot:.0f} us, cuBLAS (no epilogues) {totc:.0f} us")
     os.makedirs(ROOT / "gpurun_out", exist_ok=True)
-    (ROOT / "gpurun_out" / "tune_gemm.json").write_text(json.dumps(res, indent=1))
+    (ROOT / "gpurun_out" / (f"tune_gemm_T{T}.json" if T != 2048 else "tune_gemm.json")).write_text(json.dumps(res, indent=1))
 
 
 if __name__ == "__main__":
