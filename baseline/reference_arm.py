@@ -85,9 +85,7 @@ def make_model_dir(path: str) -> str:
 
 def run(args, rank: int, world: int, local_rank: int):
     def unavailable(why: str):
-        if rank == 0:
-            print(json.dumps({"impl": "reference", "unavailable": why}), flush=True)
-        return None
+        return {"impl": "reference", "unavailable": why}  # bench.py prints it on rank 0 and exits 0
 
     if find_reference() is None:
         return unavailable("baseline/_ref/client1.py not found (run baseline/install_reference.sh)")
@@ -130,7 +128,8 @@ def run(args, rank: int, world: int, local_rank: int):
         texts = df.apply(ref.features_to_text, axis=1).tolist()               # the reference's own text rendering
         labels = [1 if x == "DDoS" else 0 for x in df["Label"]]
         nw = args.warmup * B
-        warm = DataLoader(ref.CICIDS2017Dataset(texts[:nw], labels[:nw], tokenizer), batch_size=B, shuffle=True)
+        warm = (DataLoader(ref.CICIDS2017Dataset(texts[:nw], labels[:nw], tokenizer), batch_size=B, shuffle=True)
+                if nw > 0 else None)
         timed = DataLoader(ref.CICIDS2017Dataset(texts[nw:], labels[nw:], tokenizer), batch_size=B, shuffle=True)
         model = ref.DDoSClassifier(model_dir).to(device)                      # client1.py:374
         opt = torch.optim.Adam(model.parameters(), lr=2e-5)                   # client1.py:380

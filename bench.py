@@ -268,6 +268,11 @@ def main() -> None:
     args = parse_args()
     maybe_spawn(args)
     rank, world, local_rank = _env_int("RANK", 0), _env_int("WORLD_SIZE", 1), _env_int("LOCAL_RANK", 0)
+    # stdout carries exactly ONE JSON line: everything else a library prints on fd 1 (NCCL's version banner, progress
+    # bars of the reference) is sent to stderr for the duration of the run
+    sys.stdout.flush()
+    json_out = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         sys.path.insert(0, os.path.join(ROOT, "baseline"))
         import reference_arm
@@ -275,8 +280,9 @@ def main() -> None:
         out = reference_arm.run(args, rank, world, local_rank)
     else:
         out = run_ours(args, rank, world, local_rank)
+    sys.stdout.flush()
     if rank == 0 and out is not None:
-        print(json.dumps(out), flush=True)
+        print(json.dumps(out), file=json_out, flush=True)
 
 
 if __name__ == "__main__":
