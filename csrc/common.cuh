@@ -133,9 +133,17 @@ __device__ __forceinline__ uint32_t mix32(uint64_t z) {
     z ^= z >> 33;
     return static_cast<uint32_t>(z);
 }
-// returns 4 independent 8-bit lanes worth of randomness per call when needed; here: one u32 per index
+// One u32 per (seed, stream, index).  The 64-bit mix is spent once per call site on the (seed, stream) key -- it is
+// loop-invariant, the compiler hoists it -- and each element costs a 32-bit multiply-xorshift finaliser
+// (2 IMAD + 3 shift-xor) instead of two 64-bit multiplies: the attention softmax and the LayerNorm kernels draw one
+// number per element and were ALU-bound on the hash.
 __device__ __forceinline__ uint32_t rng_u32(uint64_t seed, uint32_t stream, uint32_t idx) {
-    return mix32(seed + (static_cast<uint64_t>(stream) << 32 | idx) * 0x9E3779B97F4A7C15ULL);
+    const uint32_t key = mix32(seed + static_cast<uint64_t>(stream) * 0x9E3779B97F4A7C15ULL);
+    uint32_t x = idx * 0x9E3779B1u + key;
+    x ^= x >> 16; x *= 0x7feb352du;
+    x ^= x >> 15; x *= 0x846ca68bu;
+    x ^= x >> 16;
+    return x;
 }
 // keep with probability (1-p): threshold = p * 2^32
 __device__ __forceinline__ bool dropout_keep(uint64_t seed, uint32_t stream, uint32_t idx, uint32_t thresh) {
