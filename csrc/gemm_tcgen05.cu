@@ -714,6 +714,27 @@ extern "C" int dcad_gemm_bf16_splitk(const void* A, const void* B, void* D, int 
                            block_n, max_ctas, reinterpret_cast<float*>(workspace), reinterpret_cast<cudaStream_t>(stream));
 }
 
+// Pass 1 only: leaves the fp32 partial tiles in the workspace for a consumer that sums them itself (the fused
+// residual + LayerNorm kernels read them directly, which removes the reduce launch and a bf16 round trip).
+// Slice s of the result is workspace[s * slice_elems + m * N + n]; *splits_out slices were written.
+extern "C" int dcad_gemm_bf16_splitk_partials(const void* A, const void* B, int M, int N, int K, int a_major,
+                                              int b_major, int lda, int ldb, int split_k, int block_n, int max_ctas,
+                                              void* workspace, size_t workspace_bytes, int* splits_out,
+                                              int64_t* slice_elems_out, void* stream) {
+    if (split_k < 1) return DCAD_ERR_BAD_ARGUMENT;
+    if (workspace == nullptr || (reinterpret_cast<uintptr_t>(workspace) & 255u)) return DCAD_ERR_BAD_ALIGNMENT;
+    if (workspace_bytes < dcad_gemm_splitk_workspace_bytes(M, N, split_k)) return DCAD_ERR_TOO_LARGE;
+    const int m_pad = (M + BM - 1) / BM * BM;
+    const int kb = (K + BK - 1) / BK;
+    int sk = split_k > kb ? kb : split_k;
+    const int per = (kb + sk - 1) / sk;
+    sk = (kb + per - 1) / per;  // the split count the GEMM actually uses
+    if (splits_out) *splits_out = sk;
+    if (slice_elems_out) *slice_elems_out = static_cast<int64_t>(m_pad) * N;
+    return gemm_dispatch(A, B, workspace, M, N, K, a_major, b_major, lda, ldb, N, nullptr, nullptr, nullptr, 0,
+                         DCAD_EPI_NONE, 1, split_k, m_pad, block_n, max_ctas, reinterpret_cast<cudaStream_t>(stream));
+}
+
 // ------------------------------------------------------------------------------------------------
 // Split-K GEMM for hosts that cannot hand over a workspace.
 //

@@ -24,6 +24,28 @@ __device__ __forceinline__ void load8f(const float* p, float (&v)[8]) {
     const float4 b = __ldg(reinterpret_cast<const float4*>(p + 4));
     v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
 }
+// sum of `splits` fp32 partial tiles left by a split-K GEMM (slice s at part + s * slice_elems), plus an optional bias
+struct PartialIn {
+    const float* part;   // null: the operand is the bf16 tensor instead
+    const float* bias;   // [cols] or null
+    int64_t slice_elems;
+    int splits;
+};
+__device__ __forceinline__ void load8_partials(const PartialIn& in, size_t off, int col, float (&v)[8]) {
+    const float4 a = *reinterpret_cast<const float4*>(in.part + off);
+    const float4 b = *reinterpret_cast<const float4*>(in.part + off + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    for (int s = 1; s < in.splits; ++s) {
+        const float4 c = *reinterpret_cast<const float4*>(in.part + s * in.slice_elems + off);
+        const float4 d = *reinterpret_cast<const float4*>(in.part + s * in.slice_elems + off + 4);
+        v[0] += c.x; v[1] += c.y; v[2] += c.z; v[3] += c.w; v[4] += d.x; v[5] += d.y; v[6] += d.z; v[7] += d.w;
+    }
+    if (in.bias) {
+        const float4 c = __ldg(reinterpret_cast<const float4*>(in.bias + col));
+        const float4 d = __ldg(reinterpret_cast<const float4*>(in.bias + col + 4));
+        v[0] += c.x; v[1] += c.y; v[2] += c.z; v[3] += c.w; v[4] += d.x; v[5] += d.y; v[6] += d.z; v[7] += d.w;
+    }
+}
 __device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&v)[8]) {
     uint4 o;
     o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
@@ -42,7 +64,7 @@ __device__ __forceinline__ float safe_gamma(float g) {
 // ------------------------------------------------------------------------------------------------
 template <int NV>
 __global__ void __launch_bounds__(LN_WARPS * 32)
-add_ln_fwd_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ res,
+add_ln_fwd_kernel(const __nv_bfloat16* __restrict__ a, const PartialIn a_part, const __nv_bfloat16* __restrict__ res,
                   const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ out,
                   float* __restrict__ rstd_out, int rows, float eps, uint32_t thresh, float keep_scale,
                   const uint64_t* __restrict__ rng, uint32_t stream_id) {
@@ -58,7 +80,8 @@ add_ln_fwd_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __re
 #pragma unroll
     for (int v = 0; v < NV; ++v) {
         const int col = (v * 32 + lane) * 8;
-        load8(a + static_cast<size_t>(row) * COLS + col, x[v]);
+        if (a_part.part) load8_partials(a_part, static_cast<size_t>(row) * COLS + col, col, x[v]);
+        else load8(a + static_cast<size_t>(row) * COLS + col, x[v]);
         if (thresh) {
 #pragma unroll
             for (int j = 0; j < 8; ++j)
@@ -99,7 +122,8 @@ add_ln_fwd_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __re
 // ------------------------------------------------------------------------------------------------
 template <int NV>
 __global__ void __launch_bounds__(LN_WARPS * 32)
-add_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy1, const __nv_bfloat16* __restrict__ dy2,
+add_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy1, const PartialIn dy1_part,
+                  const __nv_bfloat16* __restrict__ dy2,
                   const __nv_bfloat16* __restrict__ y, const float* __restrict__ gamma,
                   const float* __restrict__ beta, const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dz,
                   __nv_bfloat16* __restrict__ da, float* __restrict__ dgamma, float* __restrict__ dbeta,
@@ -122,7 +146,8 @@ add_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy1, const __nv_bfloat16* __
             const int col = (v * 32 + lane) * 8;
             const size_t off = static_cast<size_t>(row) * COLS + col;
             float yy[8], gm[8], bt[8];
-            load8(dy1 + off, d[v]);
+            if (dy1_part.part) load8_partials(dy1_part, off, col, d[v]);
+            else load8(dy1 + off, d[v]);
             if (dy2) {
                 float d2[8];
                 load8(dy2 + off, d2);
@@ -369,9 +394,9 @@ using namespace dcad;
         default: return DCAD_ERR_BAD_SHAPE;                    \
     }
 
-extern "C" int dcad_add_ln_fwd(const void* a, const void* res, const float* gamma, const float* beta, void* out,
-                               float* rstd, int rows, int cols, float eps, float p_drop, const uint64_t* rng,
-                               uint32_t stream_id, void* stream) {
+static int add_ln_fwd_run(const void* a, PartialIn a_part, const void* res, const float* gamma, const float* beta,
+                          void* out, float* rstd, int rows, int cols, float eps, float p_drop, const uint64_t* rng,
+                          uint32_t stream_id, void* stream) {
     if (rows <= 0) return 0;
     if (cols % 256 || cols > 1024) return DCAD_ERR_BAD_SHAPE;
     if (p_drop > 0.f && rng == nullptr) return DCAD_ERR_BAD_ARGUMENT;
@@ -381,15 +406,33 @@ extern "C" int dcad_add_ln_fwd(const void* a, const void* res, const float* gamm
     const int grid = (rows + LN_WARPS - 1) / LN_WARPS;
     DCAD_NV_DISPATCH(cols, return (int)launch_pdl(
         add_ln_fwd_kernel<NV>, dim3(grid), dim3(LN_WARPS * 32), 0, s, reinterpret_cast<const __nv_bfloat16*>(a),
-        reinterpret_cast<const __nv_bfloat16*>(res), gamma, beta, reinterpret_cast<__nv_bfloat16*>(out), rstd, rows,
-        eps, th, ks, rng, stream_id));
+        a_part, reinterpret_cast<const __nv_bfloat16*>(res), gamma, beta, reinterpret_cast<__nv_bfloat16*>(out), rstd,
+        rows, eps, th, ks, rng, stream_id));
     return 0;
 }
 
-extern "C" int dcad_add_ln_bwd(const void* dy1, const void* dy2, const void* y, const float* gamma, const float* beta,
-                               const float* rstd, void* dz, void* da, float* dgamma, float* dbeta, float* dbias,
-                               int rows, int cols, float p_drop, const uint64_t* rng, uint32_t stream_id,
-                               void* stream) {
+extern "C" int dcad_add_ln_fwd(const void* a, const void* res, const float* gamma, const float* beta, void* out,
+                               float* rstd, int rows, int cols, float eps, float p_drop, const uint64_t* rng,
+                               uint32_t stream_id, void* stream) {
+    return add_ln_fwd_run(a, PartialIn{nullptr, nullptr, 0, 0}, res, gamma, beta, out, rstd, rows, cols, eps, p_drop,
+                          rng, stream_id, stream);
+}
+
+extern "C" int dcad_add_ln_fwd_partials(const float* a_partials, int splits, int64_t slice_elems, const float* a_bias,
+                                        const void* res, const float* gamma, const float* beta, void* out,
+                                        float* rstd, int rows, int cols, float eps, float p_drop, const uint64_t* rng,
+                                        uint32_t stream_id, void* stream) {
+    if (a_partials == nullptr || splits < 1 || (slice_elems & 3) ||
+        (reinterpret_cast<uintptr_t>(a_partials) & 15u))
+        return DCAD_ERR_BAD_ARGUMENT;
+    return add_ln_fwd_run(nullptr, PartialIn{a_partials, a_bias, slice_elems, splits}, res, gamma, beta, out, rstd,
+                          rows, cols, eps, p_drop, rng, stream_id, stream);
+}
+
+static int add_ln_bwd_run(const void* dy1, PartialIn dy1_part, const void* dy2, const void* y, const float* gamma,
+                          const float* beta, const float* rstd, void* dz, void* da, float* dgamma, float* dbeta,
+                          float* dbias, int rows, int cols, float p_drop, const uint64_t* rng, uint32_t stream_id,
+                          void* stream) {
     if (rows <= 0) return 0;
     if (cols % 256 || cols > 1024) return DCAD_ERR_BAD_SHAPE;
     if (p_drop > 0.f && (rng == nullptr || da == nullptr)) return DCAD_ERR_BAD_ARGUMENT;
@@ -407,12 +450,32 @@ extern "C" int dcad_add_ln_bwd(const void* dy1, const void* dy2, const void* y, 
         }
         return (int)launch_pdl(
             add_ln_bwd_kernel<NV>, dim3(grid), dim3(LN_WARPS * 32), smem, s,
-            reinterpret_cast<const __nv_bfloat16*>(dy1), reinterpret_cast<const __nv_bfloat16*>(dy2),
+            reinterpret_cast<const __nv_bfloat16*>(dy1), dy1_part, reinterpret_cast<const __nv_bfloat16*>(dy2),
             reinterpret_cast<const __nv_bfloat16*>(y), gamma, beta, rstd, reinterpret_cast<__nv_bfloat16*>(dz),
             reinterpret_cast<__nv_bfloat16*>(p_drop > 0.f ? da : nullptr), dgamma, dbeta, dbias, rows, th, ks, rng,
             stream_id);
     });
     return 0;
+}
+
+extern "C" int dcad_add_ln_bwd(const void* dy1, const void* dy2, const void* y, const float* gamma, const float* beta,
+                               const float* rstd, void* dz, void* da, float* dgamma, float* dbeta, float* dbias,
+                               int rows, int cols, float p_drop, const uint64_t* rng, uint32_t stream_id,
+                               void* stream) {
+    return add_ln_bwd_run(dy1, PartialIn{nullptr, nullptr, 0, 0}, dy2, y, gamma, beta, rstd, dz, da, dgamma, dbeta,
+                          dbias, rows, cols, p_drop, rng, stream_id, stream);
+}
+
+extern "C" int dcad_add_ln_bwd_partials(const float* dy1_partials, int splits, int64_t slice_elems, const void* dy2,
+                                        const void* y, const float* gamma, const float* beta, const float* rstd,
+                                        void* dz, void* da, float* dgamma, float* dbeta, float* dbias, int rows,
+                                        int cols, float p_drop, const uint64_t* rng, uint32_t stream_id,
+                                        void* stream) {
+    if (dy1_partials == nullptr || splits < 1 || (slice_elems & 3) ||
+        (reinterpret_cast<uintptr_t>(dy1_partials) & 15u))
+        return DCAD_ERR_BAD_ARGUMENT;
+    return add_ln_bwd_run(nullptr, PartialIn{dy1_partials, nullptr, slice_elems, splits}, dy2, y, gamma, beta, rstd,
+                          dz, da, dgamma, dbeta, dbias, rows, cols, p_drop, rng, stream_id, stream);
 }
 
 extern "C" int dcad_embed_ln_fwd(const int32_t* ids, const float* word, const float* pos, const float* gamma,

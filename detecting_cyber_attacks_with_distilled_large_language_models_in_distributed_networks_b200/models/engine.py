@@ -61,6 +61,9 @@ class GemmPlan:
     tail_bn: int = 64
     tail_long_k: tuple = (64, 8)
     tail_wgrad_bn: int = 128
+    # which split-K GEMMs hand their fp32 partial tiles straight to the LayerNorm kernels (see _gemm_then):
+    # 0 none, 1 the CLS-row tail only, 2 all
+    fuse_ln_partials: int = field(default_factory=lambda: int(os.environ.get("DCAD_FUSE_LN", "2")))
 
 
 class B200Engine:
@@ -249,6 +252,25 @@ class B200Engine:
         if self._count(2, f"gemm_splitk{sk} {tuple(out.shape)} k={a.shape[1]}"):
             nv.gemm_bf16_splitk(a, b, out, self.splitk_ws, split_k=sk, block_n=bn, **kw)
 
+    def _gemm_then(self, a, b, M, N, cfg, scratch, fuse: bool, **kw):
+        """GEMM whose consumer is a residual + LayerNorm kernel.  With ``fuse`` and split_k > 1 only pass 1 runs and
+        the consumer sums the fp32 partial tiles itself (returns ops.native.Partials); otherwise the result lands in
+        the bf16 ``scratch`` (returned).  ``bias`` is applied by whoever produces the final sum.
+
+        Measured back to back on one B200 (box-to-box spread is ~1 %): fusing everywhere 1.660 ms per step, no fusion
+        1.675 ms: one launch and one bf16 round trip less per LayerNorm, against more loads per LayerNorm warp."""
+        bn, sk = cfg
+        epi = nv.EPI_BIAS if kw.get("bias") is not None else nv.EPI_NONE
+        if sk <= 1:
+            self._gemm(a, b, scratch, block_n=bn, epi=epi, **kw)
+            return scratch
+        if not fuse:
+            self._gemm_splitk(a, b, scratch, cfg, epi=epi, **kw)
+            return scratch
+        if not self._count(1, f"gemm_partials{sk} ({M}, {N}) k={a.shape[1]}"):
+            return scratch
+        return nv.gemm_bf16_splitk_partials(a, b, M, N, self.splitk_ws, split_k=sk, block_n=bn, **kw)
+
     def _k(self, fn, *args, **kw):
         if self._count(1, fn.__name__):
             return fn(*args, **kw)
@@ -278,8 +300,9 @@ class B200Engine:
             self._k(nv.add_ln_fwd, tmp, x, self.p["g1"][l], self.p["b1"][l], sa, self.rstd1[l][:T], eps=d.ln_eps)
             self._gemm(sa, self.p["w1"][l], hmid, bias=self.p["bb1"][l], aux_out=pre if train else None,
                        epi=nv.EPI_BIAS_GELU, block_n=pl.lin1_fwd)
-            self._gemm_splitk(hmid, self.p["w2"][l], tmp, pl.lin2_fwd, bias=self.p["bb2"][l], epi=nv.EPI_BIAS)
-            self._k(nv.add_ln_fwd, tmp, sa, self.p["g2"][l], self.p["b2"][l], self.x[l + 1][:T], self.rstd2[l][:T],
+            ffn = self._gemm_then(hmid, self.p["w2"][l], T, d.dim, pl.lin2_fwd, tmp, pl.fuse_ln_partials >= 2,
+                                  bias=self.p["bb2"][l])
+            self._k(nv.add_ln_fwd, ffn, sa, self.p["g2"][l], self.p["b2"][l], self.x[l + 1][:T], self.rstd2[l][:T],
                     eps=d.ln_eps, p_drop=p_h, rng=rng, stream_id=_layer_stream(l, 1))
         return self.x[d.n_layers][:T], S * d.dim
 
@@ -295,10 +318,10 @@ class B200Engine:
         self._k(nv.add_ln_fwd, tmpc, xc, P["g1"][l], P["b1"][l], sac, self.c_rstd1[:Bc], eps=d.ln_eps)
         self._gemm(sac, P["w1"][l], hmidc, bias=P["bb1"][l], aux_out=prec if train else None, epi=nv.EPI_BIAS_GELU,
                    block_n=pl.tail_bn)
-        self._gemm_splitk(hmidc, P["w2"][l], tmpc, pl.tail_long_k, bias=P["bb2"][l], epi=nv.EPI_BIAS)
+        ffn = self._gemm_then(hmidc, P["w2"][l], Bc, d.dim, pl.tail_long_k, tmpc, pl.fuse_ln_partials >= 1, bias=P["bb2"][l])
         # dropout indices differ from the unpruned layout (row = sample instead of token); masks stay consistent
         # between forward and backward because both use the compact indexing
-        self._k(nv.add_ln_fwd, tmpc, sac, P["g2"][l], P["b2"][l], outc, self.c_rstd2[:Bc], eps=d.ln_eps, p_drop=p_h,
+        self._k(nv.add_ln_fwd, ffn, sac, P["g2"][l], P["b2"][l], outc, self.c_rstd2[:Bc], eps=d.ln_eps, p_drop=p_h,
                 rng=rng, stream_id=_layer_stream(l, 1))
         return outc
 
@@ -373,8 +396,8 @@ class B200Engine:
                 self._gemm(da2, P["w2"][l], G.wide, b_major=MN, aux=pre, epi=nv.EPI_DGELU, block_n=pl.lin2_dgrad)
                 # lin1: dW1 = dpre^T sa, db1 = colsum(dpre) (side) ; dsa = dpre W1
                 self._fork(lambda: self._wgrad(G.wide, sa, P["d_w1"][l], pl.wgrad_lin1, G.wide, P["d_bb1"][l]))
-                dsa = G.b
-                self._gemm_splitk(G.wide, P["w1"][l], dsa, pl.lin1_dgrad, b_major=MN)
+                dsa = self._gemm_then(G.wide, P["w1"][l], self.T, D, pl.lin1_dgrad, G.b, pl.fuse_ln_partials >= 2,
+                                      b_major=MN)
                 # sa_layer_norm(attn_out + x): dz1 is the gradient wrt both attn_out and the residual x
                 dz1 = G.a
                 self._k(nv.add_ln_bwd, dsa, dz2, sa, P["g1"][l], P["b1"][l], self.rstd1[l], dz1, None, P["d_g1"][l],
@@ -422,8 +445,7 @@ class B200Engine:
         self._gemm(self.c_gwide, self.c_sa, P["d_w1"][l], a_major=MN, b_major=MN, block_n=pl.tail_wgrad_bn,
                    reduce_add=self.dp is not None)
         self._k(nv.colsum_bf16, self.c_gwide, P["d_bb1"][l])
-        dsa = self.c_gb
-        self._gemm_splitk(self.c_gwide, P["w1"][l], dsa, pl.tail_long_k, b_major=MN)
+        dsa = self._gemm_then(self.c_gwide, P["w1"][l], B, D, pl.tail_long_k, self.c_gb, pl.fuse_ln_partials >= 1, b_major=MN)
         dz1 = self.c_ga
         self._k(nv.add_ln_bwd, dsa, dz2, self.c_sa, P["g1"][l], P["b1"][l], self.c_rstd1, dz1, None, P["d_g1"][l],
                 P["d_b1"][l], P["d_bo"][l])

@@ -94,6 +94,9 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("dcad_gemm_splitk_workspace_bytes", [I, I, I], ctypes.c_size_t)
     sig("dcad_gemm_bf16_splitk", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, I, P, ctypes.c_size_t, P])
     sig("dcad_add_ln_fwd", [P, P, P, P, P, P, I, I, F, F, P, U32, P])
+    sig("dcad_add_ln_fwd_partials", [P, I, L64, P, P, P, P, P, P, I, I, F, F, P, U32, P])
+    sig("dcad_add_ln_bwd_partials", [P, I, L64, P, P, P, P, P, P, P, P, P, P, I, I, F, P, U32, P])
+    sig("dcad_gemm_bf16_splitk_partials", [P, P, I, I, I, I, I, I, I, I, I, I, P, ctypes.c_size_t, P, P, P])
     sig("dcad_add_ln_bwd", [P, P, P, P, P, P, P, P, P, P, P, I, I, F, P, U32, P])
     sig("dcad_embed_ln_fwd", [P, P, P, P, P, P, P, P, I, I, I, F, F, P, U32, P])
     sig("dcad_embed_ln_bwd", [P, P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, F, P, U32, P, P])
@@ -201,7 +204,40 @@ def gemm_bf16_splitk(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, worksp
 # --------------------------------------------------------------------------------------------------------------
 # LayerNorm family
 # --------------------------------------------------------------------------------------------------------------
+class Partials:
+    """fp32 partial tiles a split-K GEMM left in its workspace: ``splits`` slices of ``slice_elems`` floats, row
+    stride = number of columns.  Accepted by add_ln_fwd / add_ln_bwd in place of their first (bf16) operand."""
+
+    def __init__(self, workspace: torch.Tensor, splits: int, slice_elems: int, rows: int, cols: int,
+                 bias: Optional[torch.Tensor] = None):
+        self.workspace, self.splits, self.slice_elems = workspace, splits, slice_elems
+        self.shape = (rows, cols)
+        self.bias = bias
+
+
+def gemm_bf16_splitk_partials(a: torch.Tensor, b: torch.Tensor, M: int, N: int, workspace: torch.Tensor, *,
+                              split_k: int, a_major: int = MAJOR_K, b_major: int = MAJOR_K, block_n: int = 0,
+                              max_ctas: int = 0, bias: Optional[torch.Tensor] = None,
+                              stream: Optional[torch.cuda.Stream] = None) -> Partials:
+    """Pass 1 of the split-K GEMM only; ``bias`` is just carried along for the consumer of the partial sums."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.stride(1) == 1 and b.stride(1) == 1
+    K = a.shape[1] if a_major == MAJOR_K else a.shape[0]
+    splits, slice_elems = c_int(0), c_int64(0)
+    rc = lib().dcad_gemm_bf16_splitk_partials(a.data_ptr(), b.data_ptr(), M, N, K, a_major, b_major, a.stride(0),
+                                              b.stride(0), split_k, block_n, max_ctas, workspace.data_ptr(),
+                                              workspace.numel() * workspace.element_size(), ctypes.byref(splits),
+                                              ctypes.byref(slice_elems), stream_ptr(stream))
+    check(rc, "dcad_gemm_bf16_splitk_partials")
+    return Partials(workspace, splits.value, slice_elems.value, M, N, bias)
+
+
 def add_ln_fwd(a, res, gamma, beta, out, rstd, *, eps=1e-12, p_drop=0.0, rng=None, stream_id=0, stream=None):
+    if isinstance(a, Partials):
+        rows, cols = a.shape
+        check(lib().dcad_add_ln_fwd_partials(a.workspace.data_ptr(), a.splits, a.slice_elems, ptr(a.bias), ptr(res),
+                                             ptr(gamma), ptr(beta), ptr(out), ptr(rstd), rows, cols, eps, p_drop,
+                                             ptr(rng), stream_id, stream_ptr(stream)), "dcad_add_ln_fwd_partials")
+        return out
     rows, cols = a.shape
     check(lib().dcad_add_ln_fwd(ptr(a), ptr(res), ptr(gamma), ptr(beta), ptr(out), ptr(rstd), rows, cols, eps,
                                 p_drop, ptr(rng), stream_id, stream_ptr(stream)), "dcad_add_ln_fwd")
@@ -211,6 +247,12 @@ def add_ln_fwd(a, res, gamma, beta, out, rstd, *, eps=1e-12, p_drop=0.0, rng=Non
 def add_ln_bwd(dy1, dy2, y, gamma, beta, rstd, dz, da, dgamma, dbeta, dbias, *, p_drop=0.0, rng=None, stream_id=0,
                stream=None):
     rows, cols = y.shape
+    if isinstance(dy1, Partials):
+        check(lib().dcad_add_ln_bwd_partials(dy1.workspace.data_ptr(), dy1.splits, dy1.slice_elems, ptr(dy2), ptr(y),
+                                             ptr(gamma), ptr(beta), ptr(rstd), ptr(dz), ptr(da), ptr(dgamma),
+                                             ptr(dbeta), ptr(dbias), rows, cols, p_drop, ptr(rng), stream_id,
+                                             stream_ptr(stream)), "dcad_add_ln_bwd_partials")
+        return
     check(lib().dcad_add_ln_bwd(ptr(dy1), ptr(dy2), ptr(y), ptr(gamma), ptr(beta), ptr(rstd), ptr(dz), ptr(da),
                                 ptr(dgamma), ptr(dbeta), ptr(dbias), rows, cols, p_drop, ptr(rng), stream_id,
                                 stream_ptr(stream)), "dcad_add_ln_bwd")

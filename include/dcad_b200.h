@@ -71,6 +71,11 @@ int dcad_gemm_bf16_splitk(const void* A, const void* B, void* D, int M, int N, i
                           int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
                           int split_k, int block_n, int max_ctas, void* workspace, size_t workspace_bytes,
                           void* stream);
+/* Pass 1 of the split-K GEMM only: the fp32 partial tiles stay in the workspace (slice s at
+ * workspace + s * *slice_elems_out floats, row stride N, *splits_out slices) for a consumer that sums them itself. */
+int dcad_gemm_bf16_splitk_partials(const void* A, const void* B, int M, int N, int K, int a_major, int b_major,
+                                   int lda, int ldb, int split_k, int block_n, int max_ctas, void* workspace,
+                                   size_t workspace_bytes, int* splits_out, int64_t* slice_elems_out, void* stream);
 /* Split-K GEMM without a caller-supplied workspace (no counterpart in the reference, which never touches device
  * memory itself).  Same arguments, kernels and results as dcad_gemm_bf16_splitk, except that the fp32 scratch is a
  * fixed DCAD_SPLITK_STATIC_BYTES (24 MiB) region built into the library, one per GPU that has loaded it, held until
@@ -109,6 +114,16 @@ int dcad_add_ln_fwd(const void* a, const void* res, const float* gamma, const fl
 int dcad_add_ln_bwd(const void* dy1, const void* dy2, const void* y, const float* gamma, const float* beta,
                     const float* rstd, void* dz, void* da, float* dgamma, float* dbeta, float* dbias, int rows,
                     int cols, float p_drop, const uint64_t* rng, uint32_t stream_id, void* stream);
+/* Variants whose first operand is the sum of the fp32 partial tiles a split-K GEMM left in its workspace
+ * (dcad_gemm_bf16_splitk_partials): slice s at partials + s * slice_elems, row stride = cols, plus an optional bias.
+ * They replace "reduce the slices to bf16, then LayerNorm" with one launch and no rounding of the GEMM result. */
+int dcad_add_ln_fwd_partials(const float* a_partials, int splits, int64_t slice_elems, const float* a_bias,
+                             const void* res, const float* gamma, const float* beta, void* out, float* rstd, int rows,
+                             int cols, float eps, float p_drop, const uint64_t* rng, uint32_t stream_id, void* stream);
+int dcad_add_ln_bwd_partials(const float* dy1_partials, int splits, int64_t slice_elems, const void* dy2,
+                             const void* y, const float* gamma, const float* beta, const float* rstd, void* dz,
+                             void* da, float* dgamma, float* dbeta, float* dbias, int rows, int cols, float p_drop,
+                             const uint64_t* rng, uint32_t stream_id, void* stream);
 /* out = dropout_p(LayerNorm(word[ids[r]] + pos[r % seq])).  Replaces HF Embeddings (modeling_distilbert.py:96-122). */
 int dcad_embed_ln_fwd(const int32_t* ids, const float* word, const float* pos, const float* gamma, const float* beta,
                       void* out, float* mean, float* rstd, int rows, int seq, int cols, float eps, float p_drop,

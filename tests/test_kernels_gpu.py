@@ -208,6 +208,40 @@ def test_add_ln_fwd_bwd(nv):
     assert _rel(dbias, z.grad.sum(0)) < 3e-2
 
 
+def test_add_ln_consumes_splitk_partials(nv):
+    """Split-K pass 1 + LayerNorm kernels that sum the fp32 partial tiles themselves (forward and backward)."""
+    torch.manual_seed(21)
+    M, N, K = 300, 768, 1536
+    a = torch.randn(M, K, device="cuda").bfloat16()
+    w = (torch.randn(N, K, device="cuda") * 0.05).bfloat16()
+    bias = torch.randn(N, device="cuda")
+    res = torch.randn(M, N, device="cuda").bfloat16()
+    gamma = torch.rand(N, device="cuda") + 0.5
+    beta = torch.randn(N, device="cuda") * 0.1
+    ws = torch.empty(nv.gemm_splitk_workspace_bytes(M, N, 4) // 4, device="cuda")
+    for split in (2, 3, 4):
+        part = nv.gemm_bf16_splitk_partials(a, w, M, N, ws, split_k=split, block_n=256, bias=bias)
+        assert part.splits == split
+        out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+        rstd = torch.empty(M, device="cuda")
+        nv.add_ln_fwd(part, res, gamma, beta, out, rstd)
+        x = a.float() @ w.float().t() + bias + res.float()
+        ref = F.layer_norm(x, (N,), gamma, beta, 1e-12)
+        assert _rel(out, ref) < 1e-2, split
+    # backward: dy1 = partial sums of a GEMM, compared with the bf16 path fed the same (rounded) sum
+    dy2 = torch.randn(M, N, device="cuda").bfloat16()
+    part = nv.gemm_bf16_splitk_partials(a, w, M, N, ws, split_k=3, block_n=256)
+    dsum = (a.float() @ w.float().t())
+    outs = []
+    for first in (part, dsum.bfloat16()):
+        dz = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+        dg, db, dbias = (torch.zeros(N, device="cuda") for _ in range(3))
+        nv.add_ln_bwd(first, dy2, out, gamma, beta, rstd, dz, None, dg, db, dbias)
+        outs.append((dz, dg, db, dbias))
+    for x, y in zip(*outs):
+        assert _rel(x, y) < 2e-2
+
+
 def test_add_ln_dropout_consistency(nv):
     """Dropout masks are regenerated in backward from (seed, step, stream, index): da must be zero exactly where the
     forward dropped, and the keep rate must match 1-p."""
