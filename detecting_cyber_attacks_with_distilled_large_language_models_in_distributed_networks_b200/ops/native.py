@@ -20,6 +20,8 @@ import torch
 
 _LIB: Optional[ctypes.CDLL] = None
 _LIB_PATH = Path(__file__).resolve().parent.parent / "_native" / "libdcad_b200.so"
+if os.environ.get("DCAD_LIB"):  # A/B runs of two builds of the library inside one benchmark session
+    _LIB_PATH = Path(os.environ["DCAD_LIB"]).resolve()
 
 ERRORS = {
     -1: "bad shape", -2: "bad alignment", -3: "bad argument", -4: "unsupported tile", -5: "no driver entry point",
