@@ -55,6 +55,17 @@ __host__ __device__ constexpr int pow2_ceil(int v) {
 // CG = 1: one CTA per 128 x BN tile.  CG = 2: a CTA pair (cluster of 2, one TPC) per 256 x BN tile with
 // tcgen05.mma.cta_group::2 -- each CTA stages its own 128 A rows and only BN/2 of the B rows, so the operand bytes
 // read from smem per MMA (and fetched from L2 per tile) drop by a third for BN = 256.
+// Up to G independent problems of one tile configuration run in ONE persistent launch (G = 4: the four
+// weight-gradient GEMMs of a transformer block): one prologue and one pipeline fill instead of four, and their work
+// units are spread over the SMs together.  Unit u belongs to the problem i with unit_begin[i] <= u < unit_begin[i+1].
+template <int G>
+struct GemmGroup {
+    CUtensorMap tmA[G], tmB[G], tmD[G], tmAux[G];
+    GemmParams p[G];
+    int unit_begin[G + 1];
+    int n;
+};
+
 template <int BN, int CG = 1>
 struct GemmCfg {
     static constexpr int A_BYTES = BM * BK * 2;
@@ -75,7 +86,7 @@ __device__ __forceinline__ unsigned long long gtimer() {
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     return t;
 }
-#define DCAD_STAMP(i) do { if (p.timing && blockIdx.x == 0 && lane == 0) p.timing[i] = gtimer(); } while (0)
+#define DCAD_STAMP(i) do { if (g.p[0].timing && blockIdx.x == 0 && lane == 0) g.p[0].timing[i] = gtimer(); } while (0)
 
 constexpr int GEMM_THREADS = 640;  // 4 control warps + 16 epilogue warps
 constexpr int EPI_THREADS = 512;
@@ -86,11 +97,22 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t
     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
-template <int BN, int A_MAJOR, int B_MAJOR, int CG>
+// selects the problem a work unit belongs to and rebases the unit index
+#define DCAD_SELECT_PROBLEM(unit)                                                             \
+    int prob = 0;                                                                             \
+    if constexpr (G > 1) {                                                                    \
+        _Pragma("unroll") for (int i = 1; i < G; ++i)                                         \
+            prob += (i < g.n && (unit) >= g.unit_begin[i]) ? 1 : 0;                           \
+    }                                                                                         \
+    const GemmParams& p = g.p[prob];                                                          \
+    const CUtensorMap& tmA = g.tmA[prob]; const CUtensorMap& tmB = g.tmB[prob];               \
+    const CUtensorMap& tmD = g.tmD[prob]; const CUtensorMap& tmAux = g.tmAux[prob];           \
+    (void)tmA; (void)tmB; (void)tmD; (void)tmAux;                                             \
+    const int lu = (unit) - g.unit_begin[prob];
+
+template <int BN, int A_MAJOR, int B_MAJOR, int CG, int G>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
-gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                         const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmAux,
-                         const GemmParams p) {
+gemm_bf16_tcgen05_kernel(const __grid_constant__ GemmGroup<G> g) {
     using Cfg = GemmCfg<BN, CG>;
     constexpr int STAGES = Cfg::STAGES;
     static_assert(BN % 64 == 0 && BN >= 64 && BN <= 256, "BLOCK_N must be a multiple of 64 in [64,256]");
@@ -112,11 +134,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024-B alignment
     const uint32_t staging_base = smem_base + STAGES * Cfg::STAGE_BYTES;
 
-    if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&tmA);
-        tma_prefetch_desc(&tmB);
-        tma_prefetch_desc(&tmD);
-        if (p.has_aux_out) tma_prefetch_desc(&tmAux);
+    if (warp == 0 && lane < static_cast<uint32_t>(g.n)) {
+        tma_prefetch_desc(&g.tmA[lane]);
+        tma_prefetch_desc(&g.tmB[lane]);
+        tma_prefetch_desc(&g.tmD[lane]);
+        if (g.p[lane].has_aux_out) tma_prefetch_desc(&g.tmAux[lane]);
     }
     if (warp == 1 && lane == 0) {
 #pragma unroll
@@ -150,7 +172,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     pdl_wait();  // everything above overlapped the previous kernel's tail; global memory is touched only below
 
     // work unit = (output tile of BM*CG x BN, k-split); units are strided over the persistent CTAs (CTA pairs)
-    const int num_units = p.num_m_blocks * p.num_n_blocks * p.split_k;
+    const int num_units = g.unit_begin[g.n];
     const int unit0 = static_cast<int>(blockIdx.x) / CG, unit_step = static_cast<int>(gridDim.x) / CG;
     if (warp == 0) DCAD_STAMP(0);
 
@@ -158,7 +180,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         // ===================== TMA producer =====================
         uint32_t stage = 0, phase = 0;
         for (int unit = unit0; unit < num_units; unit += unit_step) {
-            const int tile = unit / p.split_k, split = unit % p.split_k;
+            DCAD_SELECT_PROBLEM(unit)
+            const int tile = lu / p.split_k, split = lu % p.split_k;
             const int m_blk = (tile % p.num_m_blocks) * CG + static_cast<int>(cta_rank);
             const int n_blk = tile / p.num_m_blocks;
             const int n_row0 = n_blk * BN + static_cast<int>(cta_rank) * Cfg::B_ROWS;  // this CTA's share of B
@@ -210,7 +233,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         uint32_t stage = 0, phase = 0, acc_stage = 0, acc_phase = 0;
         bool first = true;
         for (int unit = unit0; unit < num_units; unit += unit_step) {
-            const int split = unit % p.split_k;
+            DCAD_SELECT_PROBLEM(unit)
+            const int split = lu % p.split_k;
             const int kb0 = split * p.kb_per_split;
             const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
             mbar_wait(smem_u32(&tmem_empty_bar[acc_stage]), acc_phase ^ 1u);
@@ -253,16 +277,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         const uint32_t q = warp & 3u;
         const int part = static_cast<int>(warp - 4) >> 2;  // 0..3
         const int ep_tid = static_cast<int>(threadIdx.x) - 128;
-        const bool has_bias = (p.epi == DCAD_EPI_BIAS || p.epi == DCAD_EPI_BIAS_GELU);
         const int r_in_tile = q * 32 + lane;
         uint32_t acc_stage = 0, acc_phase = 0, slab_ctr = 0;
         for (int unit = unit0; unit < num_units; unit += unit_step) {
-            const int tile = unit / p.split_k;
+            DCAD_SELECT_PROBLEM(unit)
+            const bool has_bias = (p.epi == DCAD_EPI_BIAS || p.epi == DCAD_EPI_BIAS_GELU);
+            const int tile = lu / p.split_k;
             const int m_blk = (tile % p.num_m_blocks) * CG + static_cast<int>(cta_rank);
             const int n_blk = tile / p.num_m_blocks;
             const int n_base = n_blk * BN;
             const bool tile_ok = m_blk * BM < p.M;  // the peer's half of a pair tile may lie wholly past M
-            const int out_row0 = (unit % p.split_k) * p.ws_row_stride + m_blk * BM;  // ws_row_stride == 0 unless workspace mode
+            const int out_row0 = (lu % p.split_k) * p.ws_row_stride + m_blk * BM;  // ws_row_stride == 0 unless workspace mode
             const int row = m_blk * BM + r_in_tile;
             const bool row_ok = row < p.M;
             if (has_bias) {  // stage this tile's bias while the MMAs are still running
@@ -499,22 +524,20 @@ static int num_sms() {
     return n;
 }
 
-template <int BN, int A_MAJOR, int B_MAJOR, int CG>
-static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmD,
-                       const CUtensorMap& tmAux, const GemmParams& p, int max_ctas, cudaStream_t stream) {
+template <int BN, int A_MAJOR, int B_MAJOR, int CG, int G>
+static int launch_gemm(const GemmGroup<G>& g, int max_ctas, cudaStream_t stream) {
     using Cfg = GemmCfg<BN, CG>;
-    auto kern = gemm_bf16_tcgen05_kernel<BN, A_MAJOR, B_MAJOR, CG>;
+    auto kern = gemm_bf16_tcgen05_kernel<BN, A_MAJOR, B_MAJOR, CG, G>;
     static bool attr_set = false;
     if (!attr_set) {
         DCAD_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
         attr_set = true;
     }
-    int grid = p.num_m_blocks * p.num_n_blocks * p.split_k;  // work units = CTAs (CG 1) or CTA pairs (CG 2)
+    int grid = g.unit_begin[g.n];  // work units = CTAs (CG 1) or CTA pairs (CG 2)
     int cap = (max_ctas > 0 ? max_ctas : num_sms()) / CG;
     if (cap < 1) cap = 1;
     if (grid > cap) grid = cap;
-    return (int)launch_pdl_cluster(kern, dim3(grid * CG), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, CG, tmA, tmB,
-                                   tmD, tmAux, p);
+    return (int)launch_pdl_cluster(kern, dim3(grid * CG), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, CG, g);
 }
 
 }  // namespace dcad
@@ -527,9 +550,11 @@ extern "C" void dcad_gemm_set_timing_buffer(void* dev_ptr) { g_gemm_timing = rei
 
 // ws_row_stride > 0: D is an fp32 workspace of split_k row-slices of ws_row_stride rows each (plain stores);
 // ws_row_stride == 0 with split_k > 1: D is the fp32 result, accumulated with TMA reduce-add.
-static int gemm_dispatch(const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major, int lda,
+// Validates one problem and fills its parameters and tensor maps for tile width bn on cg CTAs per tile.
+static int build_problem(GemmParams& p, CUtensorMap& tmA, CUtensorMap& tmB, CUtensorMap& tmD, CUtensorMap& tmAux,
+                         const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major, int lda,
                          int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
-                         int out_fp32, int split_k, int ws_row_stride, int block_n, int max_ctas, cudaStream_t s) {
+                         int out_fp32, int split_k, int ws_row_stride, int bn, int cg) {
     if (M <= 0 || N <= 0 || K <= 0) return DCAD_ERR_BAD_SHAPE;
     if ((N % 8) || (ldd % 8) || (lda % 8) || (ldb % 8)) return DCAD_ERR_BAD_ALIGNMENT;
     if ((epi == DCAD_EPI_BIAS || epi == DCAD_EPI_BIAS_GELU) && bias == nullptr) return DCAD_ERR_BAD_ARGUMENT;
@@ -538,11 +563,6 @@ static int gemm_dispatch(const void* A, const void* B, void* D, int M, int N, in
     if (split_k > 1 && (!out_fp32 || epi != DCAD_EPI_NONE)) return DCAD_ERR_BAD_ARGUMENT;
     if (out_fp32 && epi != DCAD_EPI_NONE) return DCAD_ERR_BAD_ARGUMENT;
 
-    const int cg = (block_n > 0 && (block_n & DCAD_TILE_PAIR)) ? 2 : 1;
-    int bn = block_n > 0 ? (block_n & ~DCAD_TILE_PAIR) : 0;
-    if (bn <= 0) bn = (N >= 256) ? 256 : (N > 128 ? 192 : (N > 64 ? 128 : 64));
-
-    GemmParams p;
     p.M = M; p.N = N; p.K = K; p.ldaux = ldaux > 0 ? ldaux : ldd;
     p.bias = bias;
     p.aux = reinterpret_cast<const __nv_bfloat16*>(aux);
@@ -558,7 +578,6 @@ static int gemm_dispatch(const void* A, const void* B, void* D, int M, int N, in
     p.ws_row_stride = ws_row_stride;
     p.timing = g_gemm_timing;
 
-    CUtensorMap tmA, tmB, tmD, tmAux;
     int rc;
     if (a_major == kMajorK) rc = make_tensor_map_2d(&tmA, A, M, K, lda, BM, BK, 2);   // A stored [M][lda]
     else                    rc = make_tensor_map_2d(&tmA, A, K, M, lda, BK, 64, 2);   // A stored [K][lda]
@@ -575,13 +594,34 @@ static int gemm_dispatch(const void* A, const void* B, void* D, int M, int N, in
     } else {
         tmAux = tmD;
     }
+    return 0;
+}
+
+static void parse_tile(int block_n, int N, int& bn, int& cg) {
+    cg = (block_n > 0 && (block_n & DCAD_TILE_PAIR)) ? 2 : 1;
+    bn = block_n > 0 ? (block_n & ~DCAD_TILE_PAIR) : 0;
+    if (bn <= 0) bn = (N >= 256) ? 256 : (N > 128 ? 192 : (N > 64 ? 128 : 64));
+}
+
+static int gemm_dispatch(const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major, int lda,
+                         int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
+                         int out_fp32, int split_k, int ws_row_stride, int block_n, int max_ctas, cudaStream_t s) {
+    int bn, cg;
+    parse_tile(block_n, N, bn, cg);
+    GemmGroup<1> g;
+    int rc = build_problem(g.p[0], g.tmA[0], g.tmB[0], g.tmD[0], g.tmAux[0], A, B, D, M, N, K, a_major, b_major, lda,
+                           ldb, ldd, bias, aux, aux_out, ldaux, epi, out_fp32, split_k, ws_row_stride, bn, cg);
+    if (rc) return rc;
+    g.n = 1;
+    g.unit_begin[0] = 0;
+    g.unit_begin[1] = g.p[0].num_m_blocks * g.p[0].num_n_blocks * g.p[0].split_k;
 
 #define DCAD_GEMM_CASE(BN_, AM_, BM_) \
     if (cg == 1 && bn == BN_ && a_major == AM_ && b_major == BM_) \
-        return launch_gemm<BN_, AM_, BM_, 1>(tmA, tmB, tmD, tmAux, p, max_ctas, s);
+        return launch_gemm<BN_, AM_, BM_, 1, 1>(g, max_ctas, s);
 #define DCAD_GEMM_CASE2(BN_, AM_, BM_) \
     if (cg == 2 && bn == BN_ && a_major == AM_ && b_major == BM_) \
-        return launch_gemm<BN_, AM_, BM_, 2>(tmA, tmB, tmD, tmAux, p, max_ctas, s);
+        return launch_gemm<BN_, AM_, BM_, 2, 1>(g, max_ctas, s);
     DCAD_GEMM_CASE2(128, 0, 0)
     DCAD_GEMM_CASE2(192, 0, 0)
     DCAD_GEMM_CASE2(256, 0, 0)
@@ -603,6 +643,40 @@ static int gemm_dispatch(const void* A, const void* B, void* D, int M, int N, in
     DCAD_GEMM_CASE(192, 1, 1)
     DCAD_GEMM_CASE(256, 1, 1)
 #undef DCAD_GEMM_CASE
+    return DCAD_ERR_UNSUPPORTED_TILE;
+}
+
+// Up to DCAD_GEMM_GROUP_MAX independent fp32-output GEMMs (no epilogue) with the same operand layouts and tile width in
+// one persistent launch.  split_k[i] > 1 (or out_fp32 == 2) accumulates problem i with TMA reduce-add.
+extern "C" int dcad_gemm_bf16_group(int n, const void* const* A, const void* const* B, void* const* D, const int* M,
+                                    const int* N, const int* K, const int* lda, const int* ldb, const int* ldd,
+                                    const int* split_k, int a_major, int b_major, int out_fp32, int block_n,
+                                    int max_ctas, void* stream) {
+    if (n < 1 || n > DCAD_GEMM_GROUP_MAX) return DCAD_ERR_BAD_ARGUMENT;
+    if (out_fp32 != 1 && out_fp32 != 2) return DCAD_ERR_BAD_ARGUMENT;
+    if (block_n <= 0 || (block_n & DCAD_TILE_PAIR)) return DCAD_ERR_UNSUPPORTED_TILE;
+    const int bn = block_n;
+    GemmGroup<DCAD_GEMM_GROUP_MAX> g;
+    g.n = n;
+    g.unit_begin[0] = 0;
+    for (int i = 0; i < DCAD_GEMM_GROUP_MAX; ++i) {
+        const int j = i < n ? i : 0;  // unused slots mirror problem 0 (never selected)
+        int rc = build_problem(g.p[i], g.tmA[i], g.tmB[i], g.tmD[i], g.tmAux[i], A[j], B[j], D[j], M[j], N[j], K[j],
+                               a_major, b_major, lda[j], ldb[j], ldd[j], nullptr, nullptr, nullptr, 0, DCAD_EPI_NONE,
+                               out_fp32, split_k[j], 0, bn, 1);
+        if (rc) return rc;
+        g.unit_begin[i + 1] = g.unit_begin[i] +
+                              (i < n ? g.p[i].num_m_blocks * g.p[i].num_n_blocks * g.p[i].split_k : 0);
+    }
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+#define DCAD_GROUP_CASE(BN_, AM_, BM_) \
+    if (bn == BN_ && a_major == AM_ && b_major == BM_) \
+        return launch_gemm<BN_, AM_, BM_, 1, DCAD_GEMM_GROUP_MAX>(g, max_ctas, s);
+    DCAD_GROUP_CASE(128, 1, 1)
+    DCAD_GROUP_CASE(256, 1, 1)
+    DCAD_GROUP_CASE(256, 0, 1)
+    DCAD_GROUP_CASE(256, 0, 0)
+#undef DCAD_GROUP_CASE
     return DCAD_ERR_UNSUPPORTED_TILE;
 }
 

@@ -61,6 +61,9 @@ class GemmPlan:
     tail_bn: int = 64
     tail_long_k: tuple = (64, 8)
     tail_wgrad_bn: int = 128
+    # the four weight-gradient GEMMs of a block go out as ONE grouped persistent launch (BLOCK_N 256, the split_k
+    # values above) at the end of the block's backward instead of four launches spread through it
+    group_wgrad: bool = field(default_factory=lambda: os.environ.get("DCAD_GROUP_WGRAD", "1") != "0")
     # which split-K GEMMs hand their fp32 partial tiles straight to the LayerNorm kernels (see _gemm_then):
     # 0 none, 1 the CLS-row tail only, 2 all
     fuse_ln_partials: int = field(default_factory=lambda: int(os.environ.get("DCAD_FUSE_LN", "2")))
@@ -357,6 +360,18 @@ class B200Engine:
         if dbias is not None:
             self._k(nv.colsum_bf16, dbias_src, dbias)
 
+    def _wgrad_block(self, l: int, da2, G) -> None:
+        """All weight gradients (and the two bias column sums) of block l in one grouped launch; side stream."""
+        P, pl = self.p, self.plan
+        if self._count(1, "gemm_group wgrad x4"):
+            nv.gemm_bf16_group([(da2, self.hmid[l], P["d_w2"][l], pl.wgrad_lin2[1]),
+                                (G.wide, self.sa[l], P["d_w1"][l], pl.wgrad_lin1[1]),
+                                (G.qkv, self.x[l], P["d_wqkv"][l], pl.wgrad_qkv[1]),
+                                (G.a, self.ctx[l], P["d_wo"][l], pl.wgrad_out[1])],
+                               block_n=256, reduce_add=self.dp is not None)
+        self._k(nv.colsum_bf16, G.wide, P["d_bb1"][l])
+        self._k(nv.colsum_bf16, G.qkv, P["d_bqkv"][l])
+
     def _backward(self, early_adam: bool = False) -> None:
         """Backward pass.  With ``early_adam`` (training step, single-GPU client, side stream on) the Adam update of a
         block's GEMM weights is enqueued on the side stream as soon as that block's last data-gradient GEMM has been
@@ -392,10 +407,12 @@ class B200Engine:
                         da2 if d.dropout > 0 else None, P["d_g2"][l], P["d_b2"][l], P["d_bb2"][l], p_drop=d.dropout,
                         rng=self.rng, stream_id=_layer_stream(l, 1))
                 # lin2: dW2 = da2^T hmid (side) ; dpre = (da2 W2) * gelu'(pre)
-                self._fork(lambda: self._wgrad(da2, hmid, P["d_w2"][l], pl.wgrad_lin2))
+                if not pl.group_wgrad:
+                    self._fork(lambda: self._wgrad(da2, hmid, P["d_w2"][l], pl.wgrad_lin2))
                 self._gemm(da2, P["w2"][l], G.wide, b_major=MN, aux=pre, epi=nv.EPI_DGELU, block_n=pl.lin2_dgrad)
                 # lin1: dW1 = dpre^T sa, db1 = colsum(dpre) (side) ; dsa = dpre W1
-                self._fork(lambda: self._wgrad(G.wide, sa, P["d_w1"][l], pl.wgrad_lin1, G.wide, P["d_bb1"][l]))
+                if not pl.group_wgrad:
+                    self._fork(lambda: self._wgrad(G.wide, sa, P["d_w1"][l], pl.wgrad_lin1, G.wide, P["d_bb1"][l]))
                 dsa = self._gemm_then(G.wide, P["w1"][l], self.T, D, pl.lin1_dgrad, G.b, pl.fuse_ln_partials >= 2,
                                       b_major=MN)
                 # sa_layer_norm(attn_out + x): dz1 is the gradient wrt both attn_out and the residual x
@@ -403,14 +420,18 @@ class B200Engine:
                 self._k(nv.add_ln_bwd, dsa, dz2, sa, P["g1"][l], P["b1"][l], self.rstd1[l], dz1, None, P["d_g1"][l],
                         P["d_b1"][l], P["d_bo"][l])
                 # out_lin: dWo = dz1^T ctx (side) ; dctx = dz1 Wo
-                self._fork(lambda: self._wgrad(dz1, ctx, P["d_wo"][l], pl.wgrad_out))
+                if not pl.group_wgrad:
+                    self._fork(lambda: self._wgrad(dz1, ctx, P["d_wo"][l], pl.wgrad_out))
                 dctx = G.e
                 self._gemm(dz1, P["wo"][l], dctx, b_major=MN, block_n=pl.out_dgrad)
             # attention
             self._k(nv.attn_bwd, qkv, ctx, dctx, self.lse2[l], G.qkv, self.lens, B, S, H,
                     p_drop=d.attention_dropout, rng=self.rng, stream_id=_layer_stream(l, 0))
             # QKV: dWqkv = dqkv^T x, dbqkv = colsum(dqkv) (side) ; dx = dqkv Wqkv
-            self._fork(lambda: self._wgrad(G.qkv, x, P["d_wqkv"][l], pl.wgrad_qkv, G.qkv, P["d_bqkv"][l]))
+            if pl.group_wgrad and not (self.prune_last_layer and l == top):
+                self._fork(lambda: self._wgrad_block(l, da2, G))  # dz1 of this block is G.a
+            else:
+                self._fork(lambda: self._wgrad(G.qkv, x, P["d_wqkv"][l], pl.wgrad_qkv, G.qkv, P["d_bqkv"][l]))
             dxq = G.b
             self._gemm(G.qkv, P["wqkv"][l], dxq, b_major=MN, block_n=pl.qkv_dgrad)
             if early_adam:  # nothing reads this block's weights any more, and its weight gradients precede on the side stream

@@ -93,6 +93,7 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("dcad_version", [])
     sig("dcad_set_pdl", [I])
     sig("dcad_gemm_bf16", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, I, I, P])
+    sig("dcad_gemm_bf16_group", [I, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, P])
     sig("dcad_gemm_splitk_workspace_bytes", [I, I, I], ctypes.c_size_t)
     sig("dcad_gemm_bf16_splitk", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, I, P, ctypes.c_size_t, P])
     sig("dcad_add_ln_fwd", [P, P, P, P, P, P, I, I, F, F, P, U32, P])
@@ -178,6 +179,31 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_major: i
 
 def gemm_splitk_workspace_bytes(M: int, N: int, split_k: int) -> int:
     return int(lib().dcad_gemm_splitk_workspace_bytes(M, N, split_k))
+
+
+GEMM_GROUP_MAX = 4
+
+
+def gemm_bf16_group(problems, *, a_major: int = MAJOR_MN, b_major: int = MAJOR_MN, block_n: int = 256,
+                    reduce_add: bool = False, max_ctas: int = 0, stream: Optional[torch.cuda.Stream] = None) -> None:
+    """Up to four independent fp32-output GEMMs ``out_i = A_i . B_i^T`` (same operand layouts and tile width) in ONE
+    persistent launch.  ``problems`` is a list of ``(a, b, out, split_k)``; ``split_k > 1`` (or ``reduce_add``)
+    accumulates into ``out`` with TMA reduce-add, so ``out`` must hold zeros (or the running sum) beforehand."""
+    n = len(problems)
+    assert 1 <= n <= GEMM_GROUP_MAX
+    PA, IA = c_void_p * n, c_int * n
+    A, B, D = PA(), PA(), PA()
+    M, N, K, lda, ldb, ldd, sk = IA(), IA(), IA(), IA(), IA(), IA(), IA()
+    for i, (a, b, out, split_k) in enumerate(problems):
+        assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and out.dtype == torch.float32
+        assert a.stride(1) == 1 and b.stride(1) == 1 and out.stride(1) == 1
+        A[i], B[i], D[i] = a.data_ptr(), b.data_ptr(), out.data_ptr()
+        M[i], N[i] = out.shape
+        K[i] = a.shape[1] if a_major == MAJOR_K else a.shape[0]
+        lda[i], ldb[i], ldd[i], sk[i] = a.stride(0), b.stride(0), out.stride(0), split_k
+    rc = lib().dcad_gemm_bf16_group(n, A, B, D, M, N, K, lda, ldb, ldd, sk, a_major, b_major, 2 if reduce_add else 1,
+                                    block_n, max_ctas, stream_ptr(stream))
+    check(rc, "dcad_gemm_bf16_group")
 
 
 def gemm_bf16_splitk(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, workspace: torch.Tensor, *, split_k: int,

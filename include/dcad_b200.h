@@ -61,6 +61,15 @@ int dcad_set_pdl(int enabled);
 int dcad_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major, int lda,
                    int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
                    int out_fp32, int split_k, int block_n, int max_ctas, void* stream);
+
+/* Up to DCAD_GEMM_GROUP_MAX independent fp32-output GEMMs (no epilogue) that share operand layouts and tile width, in
+ * ONE persistent launch: one prologue and pipeline fill, work units of all problems spread over the SMs together.
+ * The four weight-gradient GEMMs of a transformer block use it.  split_k[i] > 1 accumulates problem i into D[i] with
+ * TMA reduce-add (D[i] zero beforehand); out_fp32 = 2 forces reduce-add for every problem (peer-GPU targets). */
+#define DCAD_GEMM_GROUP_MAX 4
+int dcad_gemm_bf16_group(int n, const void* const* A, const void* const* B, void* const* D, const int* M, const int* N,
+                         const int* K, const int* lda, const int* ldb, const int* ldd, const int* split_k, int a_major,
+                         int b_major, int out_fp32, int block_n, int max_ctas, void* stream);
 /* Split-K for bf16-output GEMMs with a long reduction and few output tiles (FFN lin2 forward / lin1 dgrad).  The
  * reduction is cut into split_k slices; every slice writes its fp32 partial tile to `workspace` (scratch, contents
  * undefined on return), then a second kernel sums the slices in order, applies the epilogue and writes bf16 D.

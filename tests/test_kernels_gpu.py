@@ -88,6 +88,32 @@ def test_gemm_cta_pair_epilogues_and_splitk(nv):
         assert _rel(g, ref) < 1e-3, split
 
 
+def test_gemm_group_matches_separate_launches(nv):
+    """Four weight-gradient shaped problems of different sizes and split-K factors in one persistent launch."""
+    torch.manual_seed(3)
+    T = 640
+    shapes = [(768, 3072, 2), (3072, 768, 2), (768, 768, 4), (2304, 768, 1)]   # dW[M, N] = dY[T, M]^T X[T, N]
+    probs, refs = [], []
+    for M, N, sk in shapes:
+        dy = torch.randn(T, M, device="cuda").bfloat16()
+        x = torch.randn(T, N, device="cuda").bfloat16()
+        out = torch.zeros(M, N, device="cuda")
+        probs.append((dy, x, out, sk))
+        refs.append(dy.float().t() @ x.float())
+    for n in (4, 3, 1):
+        for _, _, out, _ in probs:
+            out.zero_()
+        nv.gemm_bf16_group(probs[:n], block_n=256)
+        for (_, _, out, _), ref in zip(probs[:n], refs[:n]):
+            assert _rel(out, ref) < 1e-3, n
+    # accumulate mode on top of existing contents, few CTAs (several units per CTA across problem boundaries)
+    for _, _, out, _ in probs:
+        out.fill_(1.0)
+    nv.gemm_bf16_group(probs, block_n=128, reduce_add=True, max_ctas=5)
+    for (_, _, out, _), ref in zip(probs, refs):
+        assert _rel(out, ref + 1.0) < 1e-3
+
+
 def test_gemm_split_k_reduce_add(nv):
     torch.manual_seed(11)
     T, Nw, Kw = 2048, 768, 512      # dW[Nw, Kw] = dY[T, Nw]^T X[T, Kw]
