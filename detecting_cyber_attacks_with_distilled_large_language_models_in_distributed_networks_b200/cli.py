@@ -49,8 +49,12 @@ def main(argv=None) -> int:
 
         tr = None
         if cfg.transport == "socket":
+            from .utils.faults import FaultPlan
+
+            plan = FaultPlan.parse(cfg.faults) if cfg.faults else FaultPlan.from_env()
             tr = SocketTransport(cfg.host, cfg.port_recv, cfg.port_send, cfg.timeout, cfg.max_retries, cfg.gzip_level,
-                                 EventLog(f"CLIENT {cfg.client_id}", cfg.event_log, cfg.quiet))
+                                 EventLog(f"CLIENT {cfg.client_id}", cfg.event_log, cfg.quiet), faults=plan,
+                                 client_id=cfg.client_id)
         run_client(cfg, tr)
     elif ns.cmd == "launch":
         from .fed.launcher import launch

@@ -49,11 +49,15 @@ class FedConfig:
     max_retries: int = 5
     gzip_level: int = 0
     min_clients: Optional[int] = None  # quorum for the socket server (default: all)
+    faults: Optional[str] = None       # fault-injection plan, e.g. "drop=2;delay=1:0.5;cut=1:1000000@0" (utils/faults.py)
     # outputs
     out_dir: str = "."
     plots: bool = True
     extra_curves: bool = False         # ROC / PR curves (dead code in the reference, optional here)
     save_val_metrics: bool = False     # the reference computes validation metrics and drops them (Q9)
+    save_state: bool = False           # also write clientN_state.pt after every round: model + Adam moments + RNG +
+                                       # round counter (utils/checkpoint.py); the reference saves the model only
+    resume: bool = False               # continue from clientN_state.pt (skips the rounds it already completed)
     event_log: Optional[str] = None
     quiet: bool = False
 

@@ -74,8 +74,17 @@ def run_client(cfg: FedConfig, transport: Optional[Transport] = None, backend=No
         log.say(f"loading pre-trained model from {model_path}")
         backend.load_state_dict(torch.load(model_path, map_location="cpu"))
 
+    state_path = out(f"client{cid}_state.pt")
+    first_round = 0
+    if cfg.resume and os.path.exists(state_path):
+        from ..utils.checkpoint import load_training_state
+
+        prog = load_training_state(state_path, backend)
+        first_round = int(prog.get("round", 0))
+        log.say(f"resumed full training state from {state_path}: {first_round} round(s) already done")
+
     results: Dict[str, EvalResult] = {}
-    for rnd in range(cfg.rounds):
+    for rnd in range(first_round, cfg.rounds):
         sfx = "" if rnd == 0 else f"_round{rnd + 1}"
         train_model(backend, train, cfg.local_epochs, seed=cfg.resolved_seed() + 1000 * rnd, log=log, name=name)
         sd = backend.state_dict()  # (collective inside a data-parallel client group)
@@ -115,5 +124,9 @@ def run_client(cfg: FedConfig, transport: Optional[Transport] = None, backend=No
         if cfg.plots and reporter:
             with log.phase("plot generation"):
                 plot_evaluation(local, aggregated, out(f"client{cid}_plots{sfx}"), cid, extra_curves=cfg.extra_curves)
+        if cfg.save_state and reporter and getattr(backend, "dp", None) is None:
+            from ..utils.checkpoint import save_training_state
+
+            save_training_state(state_path, backend, round_idx=rnd + 1, epoch=cfg.local_epochs)
     log.say("Client shutdown")
     return results

@@ -30,13 +30,16 @@ class SocketTransport(Transport):
     name = "socket"
 
     def __init__(self, host="localhost", port_recv=st.PORT_RECEIVE, port_send=st.PORT_SEND, timeout=st.TIMEOUT,
-                 max_retries=5, gzip_level=0, log: Optional[EventLog] = None):
+                 max_retries=5, gzip_level=0, log: Optional[EventLog] = None, faults=None, client_id: int = 0):
         self.host, self.port_recv, self.port_send = host, port_recv, port_send
         self.timeout, self.max_retries, self.gzip_level = timeout, max_retries, gzip_level
         self.log = log
+        self.faults, self.client_id, self.round_idx = faults, client_id, 0  # utils.faults.FaultPlan (optional)
 
     def aggregate(self, backend) -> bool:
-        if not st.send_model(backend.state_dict(), self.host, self.port_recv, self.timeout, self.gzip_level, self.log):
+        rnd, self.round_idx = self.round_idx, self.round_idx + 1
+        if not st.send_model(backend.state_dict(), self.host, self.port_recv, self.timeout, self.gzip_level, self.log,
+                             faults=self.faults, client_id=self.client_id, round_idx=rnd):
             return False
         agg = st.receive_aggregated_model(self.host, self.port_send, self.max_retries, self.timeout, self.log)
         if agg is None:
@@ -101,18 +104,31 @@ class LoopbackTransport(Transport):
     all registered state_dicts with the reference's CPU arithmetic and loads the result into each backend."""
     name = "loopback"
 
-    def __init__(self, num_clients: int):
+    def __init__(self, num_clients: int, faults=None, min_clients: Optional[int] = None):
         self.num_clients = num_clients
+        self.min_clients = num_clients if min_clients is None else min_clients
+        self.faults = faults            # utils.faults.FaultPlan: dropped clients never register
         self.pending: List = []
+        self.round_idx = 0
 
-    def aggregate(self, backend) -> bool:
-        from ..parallel.fedavg import fedavg_state_dicts_cpu
-
+    def aggregate(self, backend, client_id: int = 0) -> bool:
+        if self.faults and not self.faults.before_upload(client_id, self.round_idx):
+            return False
         self.pending.append(backend)
         if len(self.pending) < self.num_clients:
             return True
-        agg = fedavg_state_dicts_cpu([b.state_dict() for b in self.pending])
-        for b in self.pending:
+        return self.finish_round()
+
+    def finish_round(self) -> bool:
+        """Close the round with whoever registered (the deadline of a real server): aggregates when the quorum
+        ``min_clients`` is met, otherwise leaves every model untouched and reports failure."""
+        from ..parallel.fedavg import fedavg_state_dicts_cpu
+
+        pending, self.pending = self.pending, []
+        self.round_idx += 1
+        if len(pending) < max(self.min_clients, 1):
+            return False
+        agg = fedavg_state_dicts_cpu([b.state_dict() for b in pending])
+        for b in pending:
             b.load_state_dict(agg)
-        self.pending = []
         return True

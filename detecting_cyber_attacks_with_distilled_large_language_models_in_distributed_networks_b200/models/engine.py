@@ -64,6 +64,8 @@ class GemmPlan:
     # the four weight-gradient GEMMs of a block go out as ONE grouped persistent launch (BLOCK_N 256, the split_k
     # values above) at the end of the block's backward instead of four launches spread through it
     group_wgrad: bool = field(default_factory=lambda: os.environ.get("DCAD_GROUP_WGRAD", "1") != "0")
+    # persistent-grid cap of the grouped weight-gradient launch (0 = one CTA per SM)
+    wgrad_max_ctas: int = field(default_factory=lambda: int(os.environ.get("DCAD_WGRAD_CTAS", "0")))
     # which split-K GEMMs hand their fp32 partial tiles straight to the LayerNorm kernels (see _gemm_then):
     # 0 none, 1 the CLS-row tail only, 2 all
     fuse_ln_partials: int = field(default_factory=lambda: int(os.environ.get("DCAD_FUSE_LN", "2")))
@@ -368,7 +370,7 @@ class B200Engine:
                                 (G.wide, self.sa[l], P["d_w1"][l], pl.wgrad_lin1[1]),
                                 (G.qkv, self.x[l], P["d_wqkv"][l], pl.wgrad_qkv[1]),
                                 (G.a, self.ctx[l], P["d_wo"][l], pl.wgrad_out[1])],
-                               block_n=256, reduce_add=self.dp is not None)
+                               block_n=256, reduce_add=self.dp is not None, max_ctas=pl.wgrad_max_ctas)
         self._k(nv.colsum_bf16, G.wide, P["d_bb1"][l])
         self._k(nv.colsum_bf16, G.qkv, P["d_bqkv"][l])
 

@@ -68,10 +68,15 @@ def decompress_data(data: bytes):
 
 # ---------------------------------------------------------------------------------------------- framing
 def send_chunked_data(sock: socket.socket, data: bytes, chunk_size: int = CHUNK_SEND,
-                      shutdown_write: bool = False) -> bool:
+                      shutdown_write: bool = False, cut_after: Optional[int] = None) -> bool:
+    """``cut_after`` (fault injection, utils/faults.py): tear the connection down after that many payload bytes."""
     sock.sendall(str(len(data)).encode() + b"\n")
     mv = memoryview(data)
     for i in range(0, len(data), chunk_size):
+        if cut_after is not None and i + chunk_size > cut_after:
+            sock.sendall(mv[i:max(i, cut_after)])
+            from ..utils.faults import InjectedFault
+            raise InjectedFault(f"injected: upload cut after {max(i, cut_after)} of {len(data)} bytes")
         sock.sendall(mv[i:i + chunk_size])
     if shutdown_write:
         sock.shutdown(socket.SHUT_WR)
@@ -126,9 +131,18 @@ def _connect_retry(host: str, port: int, timeout: float, interval: float, bufopt
 
 
 def send_model(state_dict, host: str = "localhost", port: int = PORT_RECEIVE, timeout: float = TIMEOUT,
-               gzip_level: int = 0, log: Optional[EventLog] = None, connect_interval: float = 0.2) -> bool:
-    """Upload a state_dict; True only when the server acknowledged (Q2)."""
+               gzip_level: int = 0, log: Optional[EventLog] = None, connect_interval: float = 0.2,
+               faults=None, client_id: int = 0, round_idx: int = 0) -> bool:
+    """Upload a state_dict; True only when the server acknowledged (Q2).  ``faults`` is an optional
+    ``utils.faults.FaultPlan`` consulted for this client and round (drop / delay / cut the upload)."""
     log = log or EventLog("CLIENT", quiet=True)
+    cut = None
+    if faults:
+        if not faults.before_upload(client_id, round_idx):
+            log.say(f"fault injection: client {client_id} drops out of round {round_idx}")
+            return False
+        faults.delay(client_id, round_idx)
+        cut = faults.cut_after(client_id, round_idx)
     try:
         with log.phase("serialise model") as ex:
             payload = compress_data(to_host_state_dict(state_dict), gzip_level)
@@ -136,7 +150,7 @@ def send_model(state_dict, host: str = "localhost", port: int = PORT_RECEIVE, ti
         sock = _connect_retry(host, port, timeout, connect_interval, socket.SO_SNDBUF)
         try:
             with log.phase("upload", bytes=len(payload)):
-                ok = send_chunked_data(sock, payload)
+                ok = send_chunked_data(sock, payload, cut_after=cut)
         finally:
             sock.close()
         return ok

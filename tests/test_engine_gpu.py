@@ -159,3 +159,45 @@ def test_pdl_overlap_does_not_change_gradients():
         assert abs(l_on - l_off) < 1e-5
         err = (g_on - g_off).abs().max().item()
         assert err <= 1e-3 * g_off.abs().max().item() + 1e-6, err
+
+
+def test_training_state_checkpoint_resumes_b200_backend(tmp_path):
+    """Model + Adam moments + touched-row flags + dropout counter restored: the resumed run tracks the uninterrupted
+    one (differences: fp32 atomic / reduce-add order only), while a model-only restore (the reference's .pth) does not."""
+    from importlib import import_module
+    tr = import_module(f"{PKG}.train.trainer")
+    ck = import_module(f"{PKG}.utils.checkpoint")
+    pack = import_module(f"{PKG}.data.pack")
+    eng_mod, arena_mod, db = _mods()
+    dims = _small_dims(arena_mod, dropout=0.1)
+    B, S, n = 8, 128, 32
+    g = torch.Generator().manual_seed(11)
+    split = pack.PackedSplit(torch.randint(1, dims.vocab_size, (n, S), generator=g, dtype=torch.int32),
+                             torch.randint(S // 4, S + 1, (n,), generator=g, dtype=torch.int32),
+                             torch.randint(0, 2, (n,), generator=g, dtype=torch.int32)).to("cuda")
+
+    def backend(seed):
+        return tr.B200Backend(dims, batch=B, seq=S, lr=1e-3, seed=seed, init_seed=seed)
+
+    a = backend(3)
+    gen = torch.Generator().manual_seed(5)
+    a.train_epoch(split, gen)
+    path = ck.save_training_state(str(tmp_path / "s.pt"), a, round_idx=1, epoch=1, shuffle_generator=gen)
+    a.train_epoch(split, gen)
+    want = a.engine.arena.flat.clone()
+
+    b = backend(9)
+    gen_b = torch.Generator()
+    prog = ck.load_training_state(path, b, shuffle_generator=gen_b)
+    assert prog["round"] == 1 and int(b.engine.rng[1].item()) == n // B
+    b.train_epoch(split, gen_b)
+    got = b.engine.arena.flat
+    err_resume = (got - want).abs().max().item()
+
+    c = backend(3)                                        # model only, fresh Adam state and dropout counter
+    c.load_state_dict(torch.load(path, weights_only=False)["model"])
+    gen_c = torch.Generator()
+    gen_c.set_state(torch.load(path, weights_only=False)["progress"]["shuffle_generator"])
+    c.train_epoch(split, gen_c)
+    err_model_only = (c.engine.arena.flat - want).abs().max().item()
+    assert err_resume < 2e-4 and err_model_only > 10 * max(err_resume, 1e-6), (err_resume, err_model_only)
