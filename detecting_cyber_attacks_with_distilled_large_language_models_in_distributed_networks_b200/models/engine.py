@@ -151,7 +151,7 @@ class B200Engine:
         # compact (one row per sample) buffers for the pruned tail of the last block
         self.c_x, self.c_ctx, self.c_tmp, self.c_sa, self.c_out = (torch.empty(batch, D, **bf) for _ in range(5))
         self.c_pre, self.c_hmid, self.c_gwide = (torch.empty(batch, Fh, **bf) for _ in range(3))
-        self.c_ga, self.c_gb, self.c_gc, self.c_gd = (torch.empty(batch, D, **bf) for _ in range(4))
+        self.c_ga, self.c_gb, self.c_gc, self.c_gd, self.c_ge = (torch.empty(batch, D, **bf) for _ in range(5))
         self.c_rstd1, self.c_rstd2 = torch.empty(batch, **f32), torch.empty(batch, **f32)
         self.logits = torch.empty(batch, dims.n_classes, **f32)
         # scratch for the split-K GEMMs (fp32 partial tiles), sized for the larger of the two users
@@ -460,24 +460,27 @@ class B200Engine:
         self._k(nv.add_ln_bwd, self.dcls, None, self.c_out, P["g2"][l], P["b2"][l], self.c_rstd2, dz2,
                 da2 if d.dropout > 0 else None, P["d_g2"][l], P["d_b2"][l], P["d_bb2"][l], p_drop=d.dropout,
                 rng=self.rng, stream_id=_layer_stream(l, 1))
-        # weight gradients of this block come from the CLS rows only: plain stores (reduce-add into the owner GPU's
-        # arena for a data-parallel client)
-        self._gemm(da2, self.c_hmid, P["d_w2"][l], a_major=MN, b_major=MN, block_n=pl.tail_wgrad_bn,
-                   reduce_add=self.dp is not None)
         self._gemm(da2, P["w2"][l], self.c_gwide, b_major=MN, aux=self.c_pre, epi=nv.EPI_DGELU, block_n=pl.tail_bn)
-        self._gemm(self.c_gwide, self.c_sa, P["d_w1"][l], a_major=MN, b_major=MN, block_n=pl.tail_wgrad_bn,
-                   reduce_add=self.dp is not None)
-        self._k(nv.colsum_bf16, self.c_gwide, P["d_bb1"][l])
         dsa = self._gemm_then(self.c_gwide, P["w1"][l], B, D, pl.tail_long_k, self.c_gb, pl.fuse_ln_partials >= 1, b_major=MN)
         dz1 = self.c_ga
         self._k(nv.add_ln_bwd, dsa, dz2, self.c_sa, P["g1"][l], P["b1"][l], self.c_rstd1, dz1, None, P["d_g1"][l],
                 P["d_b1"][l], P["d_bo"][l])
-        self._gemm(dz1, self.c_ctx, P["d_wo"][l], a_major=MN, b_major=MN, block_n=pl.tail_wgrad_bn,
-                   reduce_add=self.dp is not None)
-        dctx_c = self.c_gc  # dz2 is dead by now
+        dctx_c = self.c_ge
         self._gemm(dz1, P["wo"][l], dctx_c, b_major=MN, block_n=pl.tail_bn)
         self._k(nv.scatter_rows_bf16, dctx_c, G.e, B, D, S)
         self._k(nv.scatter_rows_bf16, dz1, G.a, B, D, S)
+
+        # The weight gradients of this block come from the CLS rows only (plain stores; reduce-add into the owner
+        # GPU's arena for a data-parallel client).  Nothing on the chain above needs them: one grouped launch on the
+        # side stream, which is idle at this point of the step.
+        def tail_wgrads():
+            if self._count(1, "gemm_group tail wgrad x3"):
+                nv.gemm_bf16_group([(da2, self.c_hmid, P["d_w2"][l], 1), (self.c_gwide, self.c_sa, P["d_w1"][l], 1),
+                                    (dz1, self.c_ctx, P["d_wo"][l], 1)],
+                                   block_n=pl.tail_wgrad_bn, reduce_add=self.dp is not None)
+            self._k(nv.colsum_bf16, self.c_gwide, P["d_bb1"][l])
+
+        self._fork(tail_wgrads)
         return G.e, G.a
 
     def _adam_range(self, lo: int, hi: int) -> None:

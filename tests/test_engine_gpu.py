@@ -192,12 +192,13 @@ def test_training_state_checkpoint_resumes_b200_backend(tmp_path):
     assert prog["round"] == 1 and int(b.engine.rng[1].item()) == n // B
     b.train_epoch(split, gen_b)
     got = b.engine.arena.flat
-    err_resume = (got - want).abs().max().item()
+    # mean, not max: where a gradient is ~0 the early Adam update is +-lr by the sign of rounding noise
+    err_resume = (got - want).abs().mean().item()
 
     c = backend(3)                                        # model only, fresh Adam state and dropout counter
     c.load_state_dict(torch.load(path, weights_only=False)["model"])
     gen_c = torch.Generator()
     gen_c.set_state(torch.load(path, weights_only=False)["progress"]["shuffle_generator"])
     c.train_epoch(split, gen_c)
-    err_model_only = (c.engine.arena.flat - want).abs().max().item()
-    assert err_resume < 2e-4 and err_model_only > 10 * max(err_resume, 1e-6), (err_resume, err_model_only)
+    err_model_only = (c.engine.arena.flat - want).abs().mean().item()
+    assert err_resume < 2e-5 and err_model_only > 10 * max(err_resume, 1e-7), (err_resume, err_model_only)
