@@ -49,9 +49,15 @@ class GemmPlan:
     lin1_fwd: int = 192
     lin2_fwd: tuple = (256, 3)     # (BLOCK_N, split_k): K = 3072, only 48 output tiles -> workspace split-K
     lin2_dgrad: int = 192   # -> [T, 3072]
-    lin1_dgrad: tuple = (256, 3)   # -> [T, 768], K = 3072
+    # 256 tiles: 128 CTAs x 2 tiles costs the same as 148 CTAs with a ragged second wave (tools/tune_wide.py) and
+    # leaves 20 SMs to the weight-gradient branch
+    lin2_dgrad_ctas: int = field(default_factory=lambda: int(os.environ.get("DCAD_LIN2_DGRAD_CTAS", "128")))
+    lin1_dgrad: tuple = field(default_factory=lambda: (256, int(os.environ.get("DCAD_LIN1_DGRAD_SPLIT", "3"))))  # -> [T, 768], K = 3072
     out_dgrad: int = 128
-    qkv_dgrad: int = 256
+    # -> [T, 768], K = 2304: only 48 tiles.  Cutting the reduction (split-K 2/3/4 -> 96/144/192 units) makes this
+    # GEMM faster in isolation but the STEP slower (1.588 / 1.622 / 1.635 / 1.659 ms, same box): with 48 CTAs it leaves
+    # 100 SMs to the weight-gradient / Adam branch running next to it.
+    qkv_dgrad: tuple = field(default_factory=lambda: (256, int(os.environ.get("DCAD_QKV_DGRAD_SPLIT", "1"))))
     wgrad_lin1: tuple = (256, 2)   # [3072, 768] <- reduce over T
     wgrad_lin2: tuple = (256, 2)   # [768, 3072]
     wgrad_qkv: tuple = (256, 2)    # [2304, 768]
@@ -155,7 +161,7 @@ class B200Engine:
         self.c_rstd1, self.c_rstd2 = torch.empty(batch, **f32), torch.empty(batch, **f32)
         self.logits = torch.empty(batch, dims.n_classes, **f32)
         # scratch for the split-K GEMMs (fp32 partial tiles), sized for the larger of the two users
-        sk = max(self.plan.lin2_fwd[1], self.plan.lin1_dgrad[1], 2)
+        sk = max(self.plan.lin2_fwd[1], self.plan.lin1_dgrad[1], self.plan.qkv_dgrad[1], 2)
         ws_bytes = max(nv.gemm_splitk_workspace_bytes(T, D, sk),
                        nv.gemm_splitk_workspace_bytes(batch, D, self.plan.tail_long_k[1]))
         self.splitk_ws = torch.empty(ws_bytes // 4, **f32)
@@ -411,7 +417,8 @@ class B200Engine:
                 # lin2: dW2 = da2^T hmid (side) ; dpre = (da2 W2) * gelu'(pre)
                 if not pl.group_wgrad:
                     self._fork(lambda: self._wgrad(da2, hmid, P["d_w2"][l], pl.wgrad_lin2))
-                self._gemm(da2, P["w2"][l], G.wide, b_major=MN, aux=pre, epi=nv.EPI_DGELU, block_n=pl.lin2_dgrad)
+                self._gemm(da2, P["w2"][l], G.wide, b_major=MN, aux=pre, epi=nv.EPI_DGELU, block_n=pl.lin2_dgrad,
+                           max_ctas=pl.lin2_dgrad_ctas)
                 # lin1: dW1 = dpre^T sa, db1 = colsum(dpre) (side) ; dsa = dpre W1
                 if not pl.group_wgrad:
                     self._fork(lambda: self._wgrad(G.wide, sa, P["d_w1"][l], pl.wgrad_lin1, G.wide, P["d_bb1"][l]))
@@ -434,8 +441,9 @@ class B200Engine:
                 self._fork(lambda: self._wgrad_block(l, da2, G))  # dz1 of this block is G.a
             else:
                 self._fork(lambda: self._wgrad(G.qkv, x, P["d_wqkv"][l], pl.wgrad_qkv, G.qkv, P["d_bqkv"][l]))
-            dxq = G.b
-            self._gemm(G.qkv, P["wqkv"][l], dxq, b_major=MN, block_n=pl.qkv_dgrad)
+            # block 0 feeds the embedding backward, which wants a materialised bf16 tensor
+            dxq = self._gemm_then(G.qkv, P["wqkv"][l], self.T, D, pl.qkv_dgrad, G.b,
+                                  pl.fuse_ln_partials >= 2 and l > 0, b_major=MN)
             if early_adam:  # nothing reads this block's weights any more, and its weight gradients precede on the side stream
                 lay = self.arena.layout
                 lo = lay.qkv_weight_offset(l)
