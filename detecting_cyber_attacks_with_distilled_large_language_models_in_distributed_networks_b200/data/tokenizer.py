@@ -89,6 +89,36 @@ def _is_cjk(cp: int) -> bool:
             or 0x2F800 <= cp <= 0x2FA1F)
 
 
+_NATIVE_LIB = None
+
+
+def _load_native():
+    """``_native/libdcad_tok.so`` (built by ``utils/build.py::build_host``); None when absent or ``DCAD_NATIVE_TOK=0``."""
+    global _NATIVE_LIB
+    if os.environ.get("DCAD_NATIVE_TOK", "1") == "0":
+        return None
+    if _NATIVE_LIB is None:
+        import ctypes
+
+        path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "_native", "libdcad_tok.so")
+        if not os.path.exists(path):
+            _NATIVE_LIB = False
+            return None
+        lib = ctypes.CDLL(path)
+        lib.dcad_tok_create.restype = ctypes.c_void_p
+        lib.dcad_tok_create.argtypes = [ctypes.c_char_p, ctypes.c_int64, ctypes.c_int, ctypes.c_int]
+        lib.dcad_tok_destroy.argtypes = [ctypes.c_void_p]
+        lib.dcad_tok_destroy.restype = None
+        lib.dcad_tok_vocab_size.argtypes = [ctypes.c_void_p]
+        lib.dcad_tok_vocab_size.restype = ctypes.c_int64
+        lib.dcad_tok_encode_batch.restype = ctypes.c_int64
+        lib.dcad_tok_encode_batch.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_void_p, ctypes.c_int64,
+                                              ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                              ctypes.c_int]
+        _NATIVE_LIB = lib
+    return _NATIVE_LIB or None
+
+
 class WordPieceTokenizer:
     """``encode_batch(texts, max_len)`` -> (ids [N, max_len] int32, lengths [N] int32)."""
 
@@ -192,10 +222,52 @@ class WordPieceTokenizer:
         n = len(ids)
         return ids + [self.pad_id] * (max_len - n), n
 
-    def encode_batch(self, texts: Iterable[str], max_len: int = 128) -> Tuple[np.ndarray, np.ndarray]:
-        texts = list(texts)
+    # ---- native batch path (csrc/host/tokenizer.cpp) ----
+    def _native_handle(self):
+        """ctypes handle of the C++ tokenizer for this vocabulary, or None (library not built / switched off)."""
+        if getattr(self, "_native", None) is None:
+            self._native = False
+            lib = _load_native()
+            if lib is not None:
+                blob = "\n".join(self.vocab).encode("utf-8")
+                h = lib.dcad_tok_create(blob, len(blob), 1 if self.lower else 0, self.max_chars)
+                if h and lib.dcad_tok_vocab_size(h) == len(self.vocab):
+                    self._native = (lib, h)
+        return self._native or None
+
+    def __del__(self):  # pragma: no cover - interpreter shutdown order
+        nat = getattr(self, "_native", None)
+        if nat:
+            try:
+                nat[0].dcad_tok_destroy(nat[1])
+            except Exception:  # noqa: BLE001
+                pass
+
+    def encode_batch(self, texts: Iterable[str], max_len: int = 128, threads: int = 0) -> Tuple[np.ndarray, np.ndarray]:
+        """Whole-batch encoding.  ASCII sentences go through the multi-threaded C++ tokenizer when it is built; rows
+        with non-ASCII characters (and everything, when it is not) take the Python path — identical results."""
+        texts = [str(t) for t in texts]
         ids = np.full((len(texts), max_len), self.pad_id, dtype=np.int32)
         lens = np.zeros(len(texts), dtype=np.int32)
+        nat = self._native_handle() if texts else None
+        if nat is not None:
+            import ctypes
+
+            lib, h = nat
+            enc = [t.encode("utf-8") for t in texts]
+            offsets = np.zeros(len(enc) + 1, dtype=np.int64)
+            np.cumsum([len(e) for e in enc], out=offsets[1:])
+            blob = b"".join(enc)
+            fallback = np.zeros(len(texts), dtype=np.uint8)
+            rc = lib.dcad_tok_encode_batch(h, blob, offsets.ctypes.data_as(ctypes.c_void_p), len(texts), max_len,
+                                           ids.ctypes.data_as(ctypes.c_void_p), lens.ctypes.data_as(ctypes.c_void_p),
+                                           fallback.ctypes.data_as(ctypes.c_void_p), threads)
+            if rc >= 0:
+                for i in np.nonzero(fallback)[0]:
+                    row, n = self.encode(texts[i], max_len)
+                    ids[i] = row
+                    lens[i] = n
+                return ids, lens
         for i, t in enumerate(texts):
             row, n = self.encode(str(t), max_len)
             ids[i] = row

@@ -96,5 +96,32 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     return LIB_PATH
 
 
+HOST_SRC = CSRC / "host"
+TOK_LIB_PATH = NATIVE_DIR / "libdcad_tok.so"
+CXX_FLAGS = ["-O3", "-std=c++17", "-fPIC", "-shared", "-pthread", "-Wall"]
+
+
+def build_host(force: bool = False, verbose: bool = False) -> Path:
+    """Compile the host-side native code (``csrc/host/*.cpp``: the WordPiece tokenizer) with the C++ compiler."""
+    cxx = os.environ.get("CXX") or shutil.which("g++") or shutil.which("c++")
+    if not cxx:
+        raise RuntimeError("no C++ compiler found (set CXX)")
+    srcs = sorted(HOST_SRC.glob("*.cpp"))
+    NATIVE_DIR.mkdir(parents=True, exist_ok=True)
+    OBJ_DIR.mkdir(parents=True, exist_ok=True)
+    key = hashlib.sha256(b"".join(p.read_bytes() for p in srcs) + " ".join(CXX_FLAGS).encode()).hexdigest()
+    stamp = OBJ_DIR / "host.stamp"
+    if not force and TOK_LIB_PATH.exists() and stamp.exists() and stamp.read_text() == key:
+        return TOK_LIB_PATH
+    r = subprocess.run([cxx, *CXX_FLAGS, *map(str, srcs), "-o", str(TOK_LIB_PATH)], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"host build failed:\n{r.stdout}\n{r.stderr}")
+    stamp.write_text(key)
+    if verbose:
+        print(f"[build] built {TOK_LIB_PATH}", file=sys.stderr)
+    return TOK_LIB_PATH
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose=True))
+    print(build_host(force="--force" in sys.argv, verbose=True))
