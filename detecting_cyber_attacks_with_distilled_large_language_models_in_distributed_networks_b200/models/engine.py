@@ -70,6 +70,10 @@ class GemmPlan:
     # the four weight-gradient GEMMs of a block go out as ONE grouped persistent launch (BLOCK_N 256, the split_k
     # values above) at the end of the block's backward instead of four launches spread through it
     group_wgrad: bool = field(default_factory=lambda: os.environ.get("DCAD_GROUP_WGRAD", "1") != "0")
+    # last LayerNorm + classifier + cross-entropy (forward and backward) of the pruned tail as one single-CTA launch
+    # (dcad_tail_head) instead of three.  Correct and tested, but measured neutral (1.584 vs 1.582 ms per step, same
+    # box): one CTA doing three kernels' work serially costs what the two saved launches cost.  Off by default.
+    fuse_tail_head: bool = field(default_factory=lambda: os.environ.get("DCAD_FUSE_TAIL_HEAD", "0") != "0")
     # persistent-grid cap of the grouped weight-gradient launch (0 = one CTA per SM)
     wgrad_max_ctas: int = field(default_factory=lambda: int(os.environ.get("DCAD_WGRAD_CTAS", "0")))
     # which split-K GEMMs hand their fp32 partial tiles straight to the LayerNorm kernels (see _gemm_then):
@@ -287,7 +291,7 @@ class B200Engine:
             return fn(*args, **kw)
 
     # ------------------------------------------------------------------------------------------------ forward
-    def _forward(self, rows_b: int, train: bool):
+    def _forward(self, rows_b: int, train: bool, fuse_head: bool = False):
         """Runs the encoder on the first ``rows_b`` samples of the static input buffers; returns the tensor holding the
         CLS vectors of the last block and the element stride between consecutive samples' CLS rows."""
         d, S, pl = self.dims, self.S, self.plan
@@ -306,7 +310,7 @@ class B200Engine:
             self._k(nv.attn_fwd, qkv, ctx, self.lse2[l], self.lens, rows_b, S, H, p_drop=p_a, rng=rng,
                     stream_id=_layer_stream(l, 0))
             if self.prune_last_layer and l == d.n_layers - 1:
-                return self._forward_tail_pruned(l, rows_b, train, p_h, rng), d.dim
+                return self._forward_tail_pruned(l, rows_b, train, p_h, rng, fuse_head), d.dim
             self._gemm(ctx, self.p["wo"][l], tmp, bias=self.p["bo"][l], epi=nv.EPI_BIAS, block_n=pl.out_fwd)
             self._k(nv.add_ln_fwd, tmp, x, self.p["g1"][l], self.p["b1"][l], sa, self.rstd1[l][:T], eps=d.ln_eps)
             self._gemm(sa, self.p["w1"][l], hmid, bias=self.p["bb1"][l], aux_out=pre if train else None,
@@ -317,8 +321,10 @@ class B200Engine:
                     eps=d.ln_eps, p_drop=p_h, rng=rng, stream_id=_layer_stream(l, 1))
         return self.x[d.n_layers][:T], S * d.dim
 
-    def _forward_tail_pruned(self, l: int, rows_b: int, train: bool, p_h: float, rng) -> torch.Tensor:
-        """out_lin -> LN -> FFN -> LN of the last block on the CLS rows only; returns ``[rows_b, D]``."""
+    def _forward_tail_pruned(self, l: int, rows_b: int, train: bool, p_h: float, rng, fuse_head: bool = False):
+        """out_lin -> LN -> FFN -> LN of the last block on the CLS rows only; returns ``[rows_b, D]``.  With
+        ``fuse_head`` the last LayerNorm is left to ``_tail_head`` (fused with the classifier and their backward) and
+        the not-yet-normalised FFN output is returned instead."""
         d, S, pl, P = self.dims, self.S, self.plan, self.p
         Bc = rows_b
         xc, ctxc, tmpc, sac, outc = (t[:Bc] for t in (self.c_x, self.c_ctx, self.c_tmp, self.c_sa, self.c_out))
@@ -332,9 +338,20 @@ class B200Engine:
         ffn = self._gemm_then(hmidc, P["w2"][l], Bc, d.dim, pl.tail_long_k, tmpc, pl.fuse_ln_partials >= 1, bias=P["bb2"][l])
         # dropout indices differ from the unpruned layout (row = sample instead of token); masks stay consistent
         # between forward and backward because both use the compact indexing
+        if fuse_head:
+            return ffn
         self._k(nv.add_ln_fwd, ffn, sac, P["g2"][l], P["b2"][l], outc, self.c_rstd2[:Bc], eps=d.ln_eps, p_drop=p_h,
                 rng=rng, stream_id=_layer_stream(l, 1))
         return outc
+
+    def _tail_head(self, ffn) -> None:
+        """Output LayerNorm of the last block + classifier head + cross-entropy, forward and backward, in one launch
+        on the CLS rows (replaces add_ln_fwd -> cls_head_train -> add_ln_bwd)."""
+        d, P, l = self.dims, self.p, self.dims.n_layers - 1
+        self._k(nv.tail_head, ffn, self.c_sa, P["g2"][l], P["b2"][l], self.cw, self.cb, self.labels, self.B,
+                self.loss_accum, self.logits, self.d_cw, self.d_cb, self.c_gc, self.c_gd if d.dropout > 0 else None,
+                P["d_g2"][l], P["d_b2"][l], P["d_bb2"][l], cols=d.dim, eps=d.ln_eps, p_ln=d.dropout,
+                ln_stream=_layer_stream(l, 1), p_head=d.head_dropout, head_stream=_STREAM_HEAD, rng=self.rng)
 
     # ------------------------------------------------------------------------------------------------ backward
     def _fork(self, fn) -> None:
@@ -380,7 +397,7 @@ class B200Engine:
         self._k(nv.colsum_bf16, G.wide, P["d_bb1"][l])
         self._k(nv.colsum_bf16, G.qkv, P["d_bqkv"][l])
 
-    def _backward(self, early_adam: bool = False) -> None:
+    def _backward(self, early_adam: bool = False, head_fused: bool = False) -> None:
         """Backward pass.  With ``early_adam`` (training step, single-GPU client, side stream on) the Adam update of a
         block's GEMM weights is enqueued on the side stream as soon as that block's last data-gradient GEMM has been
         issued: the HBM-bound optimizer pass then runs underneath the tensor-bound backward of the earlier blocks, and
@@ -394,7 +411,7 @@ class B200Engine:
         P = self.p
         side_done = {}  # layer -> event marking the end of its side-stream work
         if self.prune_last_layer:
-            dy1, dy2 = self._backward_tail_pruned(top)
+            dy1, dy2 = self._backward_tail_pruned(top, head_fused)
         else:
             # gradient wrt the last hidden states: only the CLS rows are non-zero
             dy1, dy2 = self.gset[(top + 1) % 2].a, None
@@ -457,7 +474,7 @@ class B200Engine:
         for ev in side_done.values():  # every weight gradient is complete before the optimizer reads it
             self._join(ev)
 
-    def _backward_tail_pruned(self, l: int):
+    def _backward_tail_pruned(self, l: int, head_fused: bool = False):
         """Backward of the pruned tail (LN2, FFN, LN1, out_lin of the last block) on the B CLS rows.  Returns
         (d ctx scattered to [T, D], residual gradient wrt x scattered to [T, D])."""
         d, S, B, pl, P = self.dims, self.S, self.B, self.plan, self.p
@@ -465,9 +482,10 @@ class B200Engine:
         MN = nv.MAJOR_MN
         G = self.gset[l % 2]
         dz2, da2 = self.c_gc, (self.c_gd if d.dropout > 0 else self.c_gc)
-        self._k(nv.add_ln_bwd, self.dcls, None, self.c_out, P["g2"][l], P["b2"][l], self.c_rstd2, dz2,
-                da2 if d.dropout > 0 else None, P["d_g2"][l], P["d_b2"][l], P["d_bb2"][l], p_drop=d.dropout,
-                rng=self.rng, stream_id=_layer_stream(l, 1))
+        if not head_fused:  # otherwise _tail_head already produced dz2 / da2 and the LayerNorm parameter gradients
+            self._k(nv.add_ln_bwd, self.dcls, None, self.c_out, P["g2"][l], P["b2"][l], self.c_rstd2, dz2,
+                    da2 if d.dropout > 0 else None, P["d_g2"][l], P["d_b2"][l], P["d_bb2"][l], p_drop=d.dropout,
+                    rng=self.rng, stream_id=_layer_stream(l, 1))
         self._gemm(da2, P["w2"][l], self.c_gwide, b_major=MN, aux=self.c_pre, epi=nv.EPI_DGELU, block_n=pl.tail_bn)
         dsa = self._gemm_then(self.c_gwide, P["w1"][l], B, D, pl.tail_long_k, self.c_gb, pl.fuse_ln_partials >= 1, b_major=MN)
         dz1 = self.c_ga
@@ -542,11 +560,15 @@ class B200Engine:
     # ------------------------------------------------------------------------------------------------ public API
     def _train_step_kernels(self) -> None:
         self._n_launch = 0
-        h, stride = self._forward(self.B, train=True)
-        self._k(nv.cls_head_train, h, stride, self.cw, self.cb, self.labels, self.B, self.loss_accum,
-                self.logits, self.d_cw, self.d_cb, self.dcls, cols=self.dims.dim, p_drop=self.dims.head_dropout,
-                rng=self.rng, stream_id=_STREAM_HEAD)
-        self._backward(early_adam=True)
+        fuse_head = self.prune_last_layer and self.plan.fuse_tail_head and self.B <= 64
+        h, stride = self._forward(self.B, train=True, fuse_head=fuse_head)
+        if fuse_head:
+            self._tail_head(h)
+        else:
+            self._k(nv.cls_head_train, h, stride, self.cw, self.cb, self.labels, self.B, self.loss_accum,
+                    self.logits, self.d_cw, self.d_cb, self.dcls, cols=self.dims.dim, p_drop=self.dims.head_dropout,
+                    rng=self.rng, stream_id=_STREAM_HEAD)
+        self._backward(early_adam=True, head_fused=fuse_head)
         self._optimizer()
         self.launches_per_train_step = self._n_launch
 

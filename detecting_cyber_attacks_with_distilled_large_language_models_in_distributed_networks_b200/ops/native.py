@@ -105,6 +105,7 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("dcad_embed_ln_bwd", [P, P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, F, P, U32, P, P])
     sig("dcad_colsum_bf16", [P, P, I, I, I, P])
     sig("dcad_cls_head_train", [P, I, P, P, P, I, F, P, U32, P, P, P, P, P, I, P])
+    sig("dcad_tail_head", [P, I, L64, P, P, P, P, P, F, F, U32, P, P, P, F, U32, P, I, I, P, P, P, P, P, P, P, P, P, P])
     sig("dcad_cls_head_eval", [P, I, P, P, P, I, I, P, P, P, P, P])
     sig("dcad_adam_step", [P, P, P, P, P, L64, L64, L64, L64, L64, F, F, F, F, P, P])
     sig("dcad_adam_step_rows", [P, P, P, P, P, L64, L64, L64, L64, L64, F, F, F, F, P, P, L64, L64, I, P])
@@ -322,6 +323,21 @@ def cls_head_train(h, sample_stride, W, bias, labels, batch, loss_accum, logits,
     check(lib().dcad_cls_head_train(ptr(h), sample_stride, ptr(W), ptr(bias), ptr(labels), batch, p_drop, ptr(rng),
                                     stream_id, ptr(loss_accum), ptr(logits), ptr(dW), ptr(db), ptr(dcls), cols,
                                     stream_ptr(stream)), "dcad_cls_head_train")
+
+
+def tail_head(a, res, gamma, beta, W, cls_bias, labels, batch, loss_accum, logits, dW, db, dz, da, dgamma, dbeta,
+              dbias, *, cols=768, eps=1e-12, p_ln=0.0, ln_stream=0, p_head=0.0, head_stream=0, rng=None, stream=None):
+    """Fused LayerNorm + classifier + cross-entropy forward and backward on ``batch`` CLS rows; ``a`` is a bf16
+    ``[batch, cols]`` tensor or a ``Partials`` object (split-K pass-1 output + bias)."""
+    assert labels.dtype == torch.int32
+    if isinstance(a, Partials):
+        part, splits, slice_elems, bias, a_ptr = a.workspace.data_ptr(), a.splits, a.slice_elems, ptr(a.bias), None
+    else:
+        part, splits, slice_elems, bias, a_ptr = None, 0, 0, None, ptr(a)
+    check(lib().dcad_tail_head(part, splits, slice_elems, bias, a_ptr, ptr(res), ptr(gamma), ptr(beta), eps, p_ln,
+                               ln_stream, ptr(W), ptr(cls_bias), ptr(labels), p_head, head_stream, ptr(rng), batch,
+                               cols, ptr(loss_accum), ptr(logits), ptr(dW), ptr(db), ptr(dz), ptr(da), ptr(dgamma),
+                               ptr(dbeta), ptr(dbias), stream_ptr(stream)), "dcad_tail_head")
 
 
 def cls_head_eval(h, sample_stride, W, bias, labels, batch, loss_accum, confusion, probs=None, preds=None, *,

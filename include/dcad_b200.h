@@ -159,6 +159,18 @@ int dcad_cls_head_eval(const void* h, int sample_stride, const float* W, const f
                        int batch, int cols, float* loss_accum, int32_t* confusion, float* probs, int32_t* preds,
                        void* stream);
 
+/* Fused output LayerNorm + classifier head + cross-entropy, forward AND backward, for the CLS rows of the last block
+ * (one launch instead of add_ln_fwd -> cls_head_train -> add_ln_bwd; fp32 between the stages).
+ * LayerNorm input: split-K partial tiles (a_partials != NULL, plus a_bias) or the bf16 tensor a, with dropout p_ln, plus
+ * the residual res.  Outputs: loss_accum {sum of batch-mean losses, batches}, logits [batch,2] (may be NULL), dW / db
+ * of the classifier, dz = grad wrt the LayerNorm input sum, da = grad wrt a (only when p_ln > 0), dgamma / dbeta /
+ * dbias accumulated with atomics.  batch <= 64, batch * cols * 4 bytes <= 200 KB. */
+int dcad_tail_head(const float* a_partials, int splits, int64_t slice_elems, const float* a_bias, const void* a,
+                   const void* res, const float* gamma, const float* beta, float eps, float p_ln, uint32_t ln_stream,
+                   const float* W, const float* cls_bias, const int32_t* labels, float p_head, uint32_t head_stream,
+                   const uint64_t* rng, int batch, int cols, float* loss_accum, float* logits, float* dW, float* db,
+                   void* dz, void* da, float* dgamma, float* dbeta, float* dbias, void* stream);
+
 /* ---- optimizer (reference client1.py:106,110,380: Adam(lr=2e-5) + zero_grad) ----
  * One launch over the flat arena.  Elements in [bf16_begin, bf16_end) are also written as bf16 to
  * p_bf16[i - bf16_begin]; gradients in [zero_begin, zero_end) are cleared after use.  The step number is

@@ -526,3 +526,57 @@ def test_raw_buffer_views_and_cast(nv):
     assert torch.all(b.float() == 1.5)
     del t
     buf.free()
+
+
+@pytest.mark.parametrize("p_ln,p_head", [(0.0, 0.0), (0.1, 0.3)])
+def test_tail_head_matches_the_three_kernel_sequence(nv, p_ln, p_head):
+    """Fused LayerNorm + classifier + CE (+ backward) vs add_ln_fwd -> cls_head_train -> add_ln_bwd, and vs autograd
+    when dropout is off."""
+    torch.manual_seed(31)
+    B, C = 16, 768
+    a = torch.randn(B, C, device="cuda").bfloat16()
+    res = torch.randn(B, C, device="cuda").bfloat16()
+    gamma = torch.rand(C, device="cuda") + 0.5
+    beta = torch.randn(C, device="cuda") * 0.1
+    W = torch.randn(2, C, device="cuda") * 0.05
+    cb = torch.randn(2, device="cuda") * 0.1
+    labels = torch.randint(0, 2, (B,), device="cuda", dtype=torch.int32)
+    rng = _rng_state(step=3)
+
+    def outs():
+        return dict(loss=torch.zeros(2, device="cuda"), logits=torch.zeros(B, 2, device="cuda"),
+                    dW=torch.zeros(2, C, device="cuda"), db=torch.zeros(2, device="cuda"),
+                    dz=torch.zeros(B, C, device="cuda", dtype=torch.bfloat16),
+                    da=torch.zeros(B, C, device="cuda", dtype=torch.bfloat16),
+                    dg=torch.zeros(C, device="cuda"), dbt=torch.zeros(C, device="cuda"), dbias=torch.zeros(C, device="cuda"))
+
+    f = outs()
+    nv.tail_head(a, res, gamma, beta, W, cb, labels, B, f["loss"], f["logits"], f["dW"], f["db"], f["dz"],
+                 f["da"] if p_ln > 0 else None, f["dg"], f["dbt"], f["dbias"], cols=C, p_ln=p_ln, ln_stream=7,
+                 p_head=p_head, head_stream=9, rng=rng)
+    u = outs()
+    y = torch.empty(B, C, device="cuda", dtype=torch.bfloat16)
+    rstd = torch.empty(B, device="cuda")
+    dcls = torch.empty(B, C, device="cuda", dtype=torch.bfloat16)
+    nv.add_ln_fwd(a, res, gamma, beta, y, rstd, p_drop=p_ln, rng=rng, stream_id=7)
+    nv.cls_head_train(y, C, W, cb, labels, B, u["loss"], u["logits"], u["dW"], u["db"], dcls, cols=C, p_drop=p_head,
+                      rng=rng, stream_id=9)
+    nv.add_ln_bwd(dcls, None, y, gamma, beta, rstd, u["dz"], u["da"] if p_ln > 0 else None, u["dg"], u["dbt"],
+                  u["dbias"], p_drop=p_ln, rng=rng, stream_id=7)
+    torch.cuda.synchronize()
+    assert abs(f["loss"][0].item() - u["loss"][0].item()) < 5e-3 and f["loss"][1].item() == 1.0
+    # the unfused path rounds y and d(cls) to bf16 in between: compare with bf16-level tolerances
+    for k, tol in (("logits", 2e-2), ("dW", 3e-2), ("db", 1e-2), ("dz", 5e-2), ("dg", 5e-2), ("dbt", 5e-2), ("dbias", 5e-2)):
+        assert _rel(f[k], u[k]) < tol, (k, _rel(f[k], u[k]))
+    if p_ln > 0:
+        assert _rel(f["da"], u["da"]) < 5e-2
+        assert ((f["da"].float() == 0) == (u["da"].float() == 0)).float().mean() > 0.999   # same dropout mask
+    else:
+        x = (a.float() + res.float()).requires_grad_(True)
+        g_, b_, W_, cb_ = (t.clone().requires_grad_(True) for t in (gamma, beta, W, cb))
+        loss = F.cross_entropy(F.layer_norm(x, (C,), g_, b_, 1e-12) @ W_.t() + cb_, labels.long())
+        loss.backward()
+        assert abs(f["loss"][0].item() - loss.item()) < 1e-4
+        for got, want in ((f["dW"], W_.grad), (f["db"], cb_.grad), (f["dg"], g_.grad), (f["dbt"], b_.grad),
+                          (f["dz"], x.grad), (f["dbias"], x.grad.sum(0))):
+            assert _rel(got, want) < 1e-2
