@@ -58,10 +58,13 @@ class GemmPlan:
     # GEMM faster in isolation but the STEP slower (1.588 / 1.622 / 1.635 / 1.659 ms, same box): with 48 CTAs it leaves
     # 100 SMs to the weight-gradient / Adam branch running next to it.
     qkv_dgrad: tuple = field(default_factory=lambda: (256, int(os.environ.get("DCAD_QKV_DGRAD_SPLIT", "1"))))
-    wgrad_lin1: tuple = (256, 2)   # [3072, 768] <- reduce over T
-    wgrad_lin2: tuple = (256, 2)   # [768, 3072]
-    wgrad_qkv: tuple = (256, 2)    # [2304, 768]
-    wgrad_out: tuple = (128, 4)    # [768, 768]
+    # Weight gradients (reduction over the T tokens).  Launched one by one they need split-K (36-54 tiles each); in
+    # the grouped launch the four problems of a block have 144 tiles together = one wave of 148 SMs, so they run
+    # unsplit: plain TMA stores instead of reduce-add (no read-modify-write), and Adam need not clear those gradients.
+    wgrad_lin1: tuple = field(default_factory=lambda: (256, int(os.environ.get("DCAD_WGRAD_SPLIT", "1"))))   # [3072, 768]
+    wgrad_lin2: tuple = field(default_factory=lambda: (256, int(os.environ.get("DCAD_WGRAD_SPLIT", "1"))))   # [768, 3072]
+    wgrad_qkv: tuple = field(default_factory=lambda: (256, int(os.environ.get("DCAD_WGRAD_SPLIT", "1"))))    # [2304, 768]
+    wgrad_out: tuple = field(default_factory=lambda: (256, int(os.environ.get("DCAD_WGRAD_SPLIT", "1"))))    # [768, 768]
     # CLS-row tail of the last block (M = batch rows): latency-bound, so narrow tiles spread the weight matrix over
     # many SMs and the K = 3072 reductions are cut eight ways (TOKENS=16 tools/tune_gemm.py)
     tail_bn: int = 64
@@ -515,9 +518,14 @@ class B200Engine:
         bf_hi = min(hi, a.layout.gemm_end)
         w0 = a.layout.offsets[_WORD_EMB]
         w1 = w0 + a.layout.numel(_WORD_EMB)
+        # GEMM-weight gradients that are written with plain stores every step need no clearing (4 of 34 bytes per
+        # parameter); everything accumulated with atomics / reduce-add does
+        pl = self.plan
+        stored = (self.dp is None and hi <= a.layout.gemm_end and os.environ.get("DCAD_ADAM_SKIP_ZERO", "1") != "0"
+                  and max(pl.wgrad_lin1[1], pl.wgrad_lin2[1], pl.wgrad_qkv[1], pl.wgrad_out[1]) == 1)
         args = (a.flat[lo:hi], a.grad[lo:hi], a.exp_avg[lo:hi], a.exp_avg_sq[lo:hi],
-                a.bf16[lo:bf_hi] if bf_hi > lo else None, hi - lo, 0, max(bf_hi - lo, 0), 0, hi - lo, self.lr,
-                self.betas[0], self.betas[1], self.eps, self.rng)
+                a.bf16[lo:bf_hi] if bf_hi > lo else None, hi - lo, 0, max(bf_hi - lo, 0), 0, 0 if stored else hi - lo,
+                self.lr, self.betas[0], self.betas[1], self.eps, self.rng)
         if lo <= w0 and w1 <= hi:  # the range holds the word-embedding table: skip rows without optimizer state
             self._k(nv.adam_step_rows, *args, self.touched_rows, w0 - lo, w1 - lo, self.dims.dim)
         else:
