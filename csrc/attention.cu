@@ -189,7 +189,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
                 const __nv_bfloat16* __restrict__ ctx, const __nv_bfloat16* __restrict__ dctx,
                 const float* __restrict__ lse2, __nv_bfloat16* __restrict__ dqkv, const int32_t* __restrict__ lens,
                 int S, int H, float scale, uint32_t thresh, float keep_scale, const uint64_t* __restrict__ rng,
-                uint32_t stream_id) {
+                uint32_t stream_id, float* __restrict__ dbias) {
     uint8_t* smem = smem_attn_bwd;
     if ((smem_u32(smem) & 1023u) != 0u) __trap();  // the swizzled tiles need the declared alignment
     const int bh = blockIdx.x, b = bh / H, h = bh % H;
@@ -340,6 +340,16 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
                 *reinterpret_cast<uint4*>(dst + j) = o;
             }
         }
+        if (dbias) {
+            // gradient of the fused QKV bias = column sums of dqkv: this warp's 32 tokens x 32 columns are reduced
+            // with a shuffle butterfly and leave as one fp32 atomic per column (no separate pass over dqkv)
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = row < S ? __uint_as_float(r[j]) : 0.f;
+            const uint32_t lane = static_cast<uint32_t>(tid) & 31u;
+            warp_colsum<32>(v, lane);
+            atomicAdd(dbias + which * HD + h * AT_D + hsel * 32 + lane, v[0]);
+        }
     }
     tc_fence_before();
     __syncthreads();
@@ -382,7 +392,7 @@ extern "C" int dcad_attn_fwd(const void* qkv, void* ctx, float* lse2, const int3
 // dctx: [B*S, H*64] bf16 gradient of ctx; dqkv: [B*S, 3*H*64] bf16 output
 extern "C" int dcad_attn_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse2, void* dqkv,
                              const int32_t* lens, int B, int S, int H, float p_drop, const uint64_t* rng,
-                             uint32_t stream_id, void* stream) {
+                             uint32_t stream_id, float* dbias, void* stream) {
     if (B <= 0) return 0;
     if (S <= 0 || S > AT_S || H <= 0) return DCAD_ERR_BAD_SHAPE;
     if (p_drop > 0.f && rng == nullptr) return DCAD_ERR_BAD_ARGUMENT;
@@ -404,5 +414,5 @@ extern "C" int dcad_attn_bwd(const void* qkv, const void* ctx, const void* dctx,
     return (int)launch_pdl(attn_bwd_kernel, dim3(B * H), dim3(AT_THREADS), SMEM, reinterpret_cast<cudaStream_t>(stream),
                            tq, td, reinterpret_cast<const __nv_bfloat16*>(ctx),
                            reinterpret_cast<const __nv_bfloat16*>(dctx), lse2, reinterpret_cast<__nv_bfloat16*>(dqkv),
-                           lens, S, H, 0.125f, drop_thresh_attn(p_drop), ks, rng, stream_id);
+                           lens, S, H, 0.125f, drop_thresh_attn(p_drop), ks, rng, stream_id, dbias);
 }

@@ -85,6 +85,28 @@ __device__ __forceinline__ float warp_max(float v) {
     return v;
 }
 
+// Column sums across the 32 lanes of a warp: every lane holds N values v[0..N) (one row of an [32][N] block); on return
+// lane l (l < N) holds sum over lanes of v[l] in v[0].  Reduce-scatter butterfly: N - 1 (+ N for N = 16) shuffles
+// instead of 5 N.  N is 16 or 32.
+template <int N>
+__device__ __forceinline__ void warp_colsum(float (&v)[N], uint32_t lane) {
+    static_assert(N == 16 || N == 32, "16 or 32 columns");
+    if constexpr (N == 16) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] += __shfl_xor_sync(0xffffffffu, v[j], 16);
+    }
+#pragma unroll
+    for (int off = (N == 32 ? 16 : 8); off >= 1; off >>= 1) {
+        const bool upper = (lane & off) != 0;
+#pragma unroll
+        for (int j = 0; j < off; ++j) {
+            const float send = upper ? v[j] : v[j + off];
+            const float keep = upper ? v[j + off] : v[j];
+            v[j] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+    }
+}
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&v);

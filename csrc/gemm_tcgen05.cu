@@ -36,6 +36,7 @@ struct GemmParams {
     int M, N, K;
     int ldaux;
     const float* bias;
+    float* colsum;             // optional [N] fp32: += column sums of the bf16 output (bias gradient of the consumer)
     const __nv_bfloat16* aux;  // EPI_DGELU: pre-activation (same shape as D)
     int has_aux_out;           // EPI_BIAS_GELU: also store the pre-activation through tmAux
     int epi;
@@ -356,6 +357,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ GemmGroup<G> g) {
                         st_shared_v4(sD + sw128_offset(r_in_tile, part * 2 + j),
                                      pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
                                      pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+                    if (p.colsum) {
+                        // bias gradient of the layer that consumes this output: the warp's 32 rows x 16 columns are
+                        // reduced with a shuffle butterfly, one fp32 atomic per column and warp
+                        if (!row_ok) {
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) v[j] = 0.f;
+                        }
+                        warp_colsum<16>(v, lane);
+                        const int col = n_base + c0 + static_cast<int>(lane);
+                        if (lane < 16 && col < p.N) atomicAdd(p.colsum + col, v[0]);
+                    }
                     fence_proxy_async_smem();
                     epi_bar_sync();
                     if (ep_tid == 0) {
@@ -554,8 +566,9 @@ extern "C" void dcad_gemm_set_timing_buffer(void* dev_ptr) { g_gemm_timing = rei
 static int build_problem(GemmParams& p, CUtensorMap& tmA, CUtensorMap& tmB, CUtensorMap& tmD, CUtensorMap& tmAux,
                          const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major, int lda,
                          int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
-                         int out_fp32, int split_k, int ws_row_stride, int bn, int cg) {
+                         int out_fp32, int split_k, int ws_row_stride, int bn, int cg, float* colsum = nullptr) {
     if (M <= 0 || N <= 0 || K <= 0) return DCAD_ERR_BAD_SHAPE;
+    if (colsum && out_fp32) return DCAD_ERR_BAD_ARGUMENT;
     if ((N % 8) || (ldd % 8) || (lda % 8) || (ldb % 8)) return DCAD_ERR_BAD_ALIGNMENT;
     if ((epi == DCAD_EPI_BIAS || epi == DCAD_EPI_BIAS_GELU) && bias == nullptr) return DCAD_ERR_BAD_ARGUMENT;
     if (epi == DCAD_EPI_DGELU && aux == nullptr) return DCAD_ERR_BAD_ARGUMENT;
@@ -565,6 +578,7 @@ static int build_problem(GemmParams& p, CUtensorMap& tmA, CUtensorMap& tmB, CUte
 
     p.M = M; p.N = N; p.K = K; p.ldaux = ldaux > 0 ? ldaux : ldd;
     p.bias = bias;
+    p.colsum = colsum;
     p.aux = reinterpret_cast<const __nv_bfloat16*>(aux);
     p.has_aux_out = (epi == DCAD_EPI_BIAS_GELU && aux_out != nullptr) ? 1 : 0;
     p.epi = epi; p.out_fp32 = out_fp32;
@@ -605,12 +619,13 @@ static void parse_tile(int block_n, int N, int& bn, int& cg) {
 
 static int gemm_dispatch(const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major, int lda,
                          int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
-                         int out_fp32, int split_k, int ws_row_stride, int block_n, int max_ctas, cudaStream_t s) {
+                         int out_fp32, int split_k, int ws_row_stride, int block_n, int max_ctas, cudaStream_t s,
+                         float* colsum = nullptr) {
     int bn, cg;
     parse_tile(block_n, N, bn, cg);
     GemmGroup<1> g;
     int rc = build_problem(g.p[0], g.tmA[0], g.tmB[0], g.tmD[0], g.tmAux[0], A, B, D, M, N, K, a_major, b_major, lda,
-                           ldb, ldd, bias, aux, aux_out, ldaux, epi, out_fp32, split_k, ws_row_stride, bn, cg);
+                           ldb, ldd, bias, aux, aux_out, ldaux, epi, out_fp32, split_k, ws_row_stride, bn, cg, colsum);
     if (rc) return rc;
     g.n = 1;
     g.unit_begin[0] = 0;
@@ -685,6 +700,16 @@ extern "C" int dcad_gemm_bf16(const void* A, const void* B, void* D, int M, int 
                               int epi, int out_fp32, int split_k, int block_n, int max_ctas, void* stream) {
     return gemm_dispatch(A, B, D, M, N, K, a_major, b_major, lda, ldb, ldd, bias, aux, aux_out, ldaux, epi, out_fp32,
                          split_k, 0, block_n, max_ctas, reinterpret_cast<cudaStream_t>(stream));
+}
+
+// Same, plus colsum (fp32 [N], may be NULL): the epilogue also accumulates the column sums of the bf16 output D into
+// it with atomics -- the bias gradient of the Linear layer whose output gradient D is (no separate pass over D).
+extern "C" int dcad_gemm_bf16_colsum(const void* A, const void* B, void* D, int M, int N, int K, int a_major,
+                                     int b_major, int lda, int ldb, int ldd, const float* bias, const void* aux,
+                                     void* aux_out, int ldaux, int epi, int block_n, int max_ctas, float* colsum,
+                                     void* stream) {
+    return gemm_dispatch(A, B, D, M, N, K, a_major, b_major, lda, ldb, ldd, bias, aux, aux_out, ldaux, epi, 0, 1, 0,
+                         block_n, max_ctas, reinterpret_cast<cudaStream_t>(stream), colsum);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -77,6 +77,9 @@ class GemmPlan:
     # (dcad_tail_head) instead of three.  Correct and tested, but measured neutral (1.584 vs 1.582 ms per step, same
     # box): one CTA doing three kernels' work serially costs what the two saved launches cost.  Off by default.
     fuse_tail_head: bool = field(default_factory=lambda: os.environ.get("DCAD_FUSE_TAIL_HEAD", "0") != "0")
+    # bias gradients of lin1 and of the fused QKV projection are accumulated by the kernels that PRODUCE dpre / dqkv
+    # (dGELU GEMM epilogue, attention backward epilogue) instead of two column-sum passes over those tensors per block
+    fuse_colsum: bool = field(default_factory=lambda: os.environ.get("DCAD_FUSE_COLSUM", "1") != "0")
     # persistent-grid cap of the grouped weight-gradient launch (0 = one CTA per SM)
     wgrad_max_ctas: int = field(default_factory=lambda: int(os.environ.get("DCAD_WGRAD_CTAS", "0")))
     # which split-K GEMMs hand their fp32 partial tiles straight to the LayerNorm kernels (see _gemm_then):
@@ -397,8 +400,9 @@ class B200Engine:
                                 (G.qkv, self.x[l], P["d_wqkv"][l], pl.wgrad_qkv[1]),
                                 (G.a, self.ctx[l], P["d_wo"][l], pl.wgrad_out[1])],
                                block_n=256, reduce_add=self.dp is not None, max_ctas=pl.wgrad_max_ctas)
-        self._k(nv.colsum_bf16, G.wide, P["d_bb1"][l])
-        self._k(nv.colsum_bf16, G.qkv, P["d_bqkv"][l])
+        if not pl.fuse_colsum:
+            self._k(nv.colsum_bf16, G.wide, P["d_bb1"][l])
+            self._k(nv.colsum_bf16, G.qkv, P["d_bqkv"][l])
 
     def _backward(self, early_adam: bool = False, head_fused: bool = False) -> None:
         """Backward pass.  With ``early_adam`` (training step, single-GPU client, side stream on) the Adam update of a
@@ -438,10 +442,11 @@ class B200Engine:
                 if not pl.group_wgrad:
                     self._fork(lambda: self._wgrad(da2, hmid, P["d_w2"][l], pl.wgrad_lin2))
                 self._gemm(da2, P["w2"][l], G.wide, b_major=MN, aux=pre, epi=nv.EPI_DGELU, block_n=pl.lin2_dgrad,
-                           max_ctas=pl.lin2_dgrad_ctas)
+                           max_ctas=pl.lin2_dgrad_ctas, colsum=P["d_bb1"][l] if pl.fuse_colsum else None)
                 # lin1: dW1 = dpre^T sa, db1 = colsum(dpre) (side) ; dsa = dpre W1
                 if not pl.group_wgrad:
-                    self._fork(lambda: self._wgrad(G.wide, sa, P["d_w1"][l], pl.wgrad_lin1, G.wide, P["d_bb1"][l]))
+                    self._fork(lambda: self._wgrad(G.wide, sa, P["d_w1"][l], pl.wgrad_lin1, G.wide,
+                                                   None if pl.fuse_colsum else P["d_bb1"][l]))
                 dsa = self._gemm_then(G.wide, P["w1"][l], self.T, D, pl.lin1_dgrad, G.b, pl.fuse_ln_partials >= 2,
                                       b_major=MN)
                 # sa_layer_norm(attn_out + x): dz1 is the gradient wrt both attn_out and the residual x
@@ -455,12 +460,14 @@ class B200Engine:
                 self._gemm(dz1, P["wo"][l], dctx, b_major=MN, block_n=pl.out_dgrad)
             # attention
             self._k(nv.attn_bwd, qkv, ctx, dctx, self.lse2[l], G.qkv, self.lens, B, S, H,
-                    p_drop=d.attention_dropout, rng=self.rng, stream_id=_layer_stream(l, 0))
+                    p_drop=d.attention_dropout, rng=self.rng, stream_id=_layer_stream(l, 0),
+                    dbias=P["d_bqkv"][l] if pl.fuse_colsum else None)
             # QKV: dWqkv = dqkv^T x, dbqkv = colsum(dqkv) (side) ; dx = dqkv Wqkv
             if pl.group_wgrad and not (self.prune_last_layer and l == top):
                 self._fork(lambda: self._wgrad_block(l, da2, G))  # dz1 of this block is G.a
             else:
-                self._fork(lambda: self._wgrad(G.qkv, x, P["d_wqkv"][l], pl.wgrad_qkv, G.qkv, P["d_bqkv"][l]))
+                self._fork(lambda: self._wgrad(G.qkv, x, P["d_wqkv"][l], pl.wgrad_qkv, G.qkv,
+                                               None if pl.fuse_colsum else P["d_bqkv"][l]))
             # block 0 feeds the embedding backward, which wants a materialised bf16 tensor
             dxq = self._gemm_then(G.qkv, P["wqkv"][l], self.T, D, pl.qkv_dgrad, G.b,
                                   pl.fuse_ln_partials >= 2 and l > 0, b_major=MN)
@@ -489,7 +496,8 @@ class B200Engine:
             self._k(nv.add_ln_bwd, self.dcls, None, self.c_out, P["g2"][l], P["b2"][l], self.c_rstd2, dz2,
                     da2 if d.dropout > 0 else None, P["d_g2"][l], P["d_b2"][l], P["d_bb2"][l], p_drop=d.dropout,
                     rng=self.rng, stream_id=_layer_stream(l, 1))
-        self._gemm(da2, P["w2"][l], self.c_gwide, b_major=MN, aux=self.c_pre, epi=nv.EPI_DGELU, block_n=pl.tail_bn)
+        self._gemm(da2, P["w2"][l], self.c_gwide, b_major=MN, aux=self.c_pre, epi=nv.EPI_DGELU, block_n=pl.tail_bn,
+                   colsum=P["d_bb1"][l] if pl.fuse_colsum else None)
         dsa = self._gemm_then(self.c_gwide, P["w1"][l], B, D, pl.tail_long_k, self.c_gb, pl.fuse_ln_partials >= 1, b_major=MN)
         dz1 = self.c_ga
         self._k(nv.add_ln_bwd, dsa, dz2, self.c_sa, P["g1"][l], P["b1"][l], self.c_rstd1, dz1, None, P["d_g1"][l],
@@ -507,7 +515,8 @@ class B200Engine:
                 nv.gemm_bf16_group([(da2, self.c_hmid, P["d_w2"][l], 1), (self.c_gwide, self.c_sa, P["d_w1"][l], 1),
                                     (dz1, self.c_ctx, P["d_wo"][l], 1)],
                                    block_n=pl.tail_wgrad_bn, reduce_add=self.dp is not None)
-            self._k(nv.colsum_bf16, self.c_gwide, P["d_bb1"][l])
+            if not pl.fuse_colsum:
+                self._k(nv.colsum_bf16, self.c_gwide, P["d_bb1"][l])
 
         self._fork(tail_wgrads)
         return G.e, G.a

@@ -93,6 +93,7 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("dcad_version", [])
     sig("dcad_set_pdl", [I])
     sig("dcad_gemm_bf16", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, I, I, P])
+    sig("dcad_gemm_bf16_colsum", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, P, P])
     sig("dcad_gemm_bf16_group", [I, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, P])
     sig("dcad_gemm_splitk_workspace_bytes", [I, I, I], ctypes.c_size_t)
     sig("dcad_gemm_bf16_splitk", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, I, P, ctypes.c_size_t, P])
@@ -113,7 +114,7 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("dcad_adam_step_dp", [P, P, P, P, L64, L64, L64, L64, L64, L64, F, F, F, F, F, P, P, P, I, I, P])
     sig("dcad_xgpu_barrier", [P, I, I, P, U32, P])
     sig("dcad_attn_fwd", [P, P, P, P, I, I, I, F, P, U32, P])
-    sig("dcad_attn_bwd", [P, P, P, P, P, P, I, I, I, F, P, U32, P])
+    sig("dcad_attn_bwd", [P, P, P, P, P, P, I, I, I, F, P, U32, P, P])
     sig("dcad_fedavg_local", [P, P, P, I, L64, I, P, L64, L64, I, P])
     sig("dcad_fedavg_p2p", [P, P, P, P, P, I, I, L64, I, I, L64, L64, U32, I, P])
     sig("dcad_fedavg_p2p_grouped", [P, I, P, P, P, I, P, I, L64, I, L64, L64, U32, I, P])
@@ -136,12 +137,14 @@ def _declare(L: ctypes.CDLL) -> None:
 def gemm_bf16(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_major: int = MAJOR_K, b_major: int = MAJOR_K,
               bias: Optional[torch.Tensor] = None, aux: Optional[torch.Tensor] = None,
               aux_out: Optional[torch.Tensor] = None, epi: int = EPI_NONE, split_k: int = 1,
-              reduce_add: bool = False, block_n: int = 0, max_ctas: int = 0, stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
+              reduce_add: bool = False, block_n: int = 0, max_ctas: int = 0, colsum: Optional[torch.Tensor] = None,
+              stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
     """``out[M,N] = epilogue(A·Bᵀ)`` on the tcgen05 kernel.  ``a``/``b`` are 2-D bf16 with unit inner stride.
 
     ``a`` is ``[M,K]`` (MAJOR_K) or ``[K,M]`` (MAJOR_MN); ``b`` is ``[N,K]`` (MAJOR_K) or ``[K,N]`` (MAJOR_MN).
     ``split_k > 1`` (fp32 ``out`` only, no epilogue) splits the reduction over several CTAs that accumulate into
-    ``out`` with TMA reduce-add: ``out`` must be zero beforehand.
+    ``out`` with TMA reduce-add: ``out`` must be zero beforehand.  ``colsum`` (fp32 ``[N]``, bf16 ``out`` only): the
+    epilogue also accumulates the column sums of ``out`` into it (the bias gradient when ``out`` is an output gradient).
     """
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
     assert a.dim() == 2 and b.dim() == 2 and out.dim() == 2
@@ -171,6 +174,13 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_major: i
         ldaux = aux_out.stride(0)
     if bias is not None:
         assert bias.dtype == torch.float32 and bias.numel() == N
+    if colsum is not None:
+        assert not out_fp32 and split_k == 1 and colsum.dtype == torch.float32 and colsum.numel() == N
+        rc = lib().dcad_gemm_bf16_colsum(a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K, a_major, b_major,
+                                         a.stride(0), b.stride(0), out.stride(0), ptr(bias), ptr(aux), ptr(aux_out),
+                                         ldaux, epi, block_n, max_ctas, ptr(colsum), stream_ptr(stream))
+        check(rc, "dcad_gemm_bf16_colsum")
+        return out
     rc = lib().dcad_gemm_bf16(a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K, a_major, b_major, a.stride(0),
                               b.stride(0), out.stride(0), ptr(bias), ptr(aux), ptr(aux_out), ldaux, epi, out_fp32,
                               split_k, block_n, max_ctas, stream_ptr(stream))
@@ -393,9 +403,10 @@ def attn_fwd(qkv, ctx, lse2, lens, B, S, H, *, p_drop=0.0, rng=None, stream_id=0
     return ctx
 
 
-def attn_bwd(qkv, ctx, dctx, lse2, dqkv, lens, B, S, H, *, p_drop=0.0, rng=None, stream_id=0, stream=None):
+def attn_bwd(qkv, ctx, dctx, lse2, dqkv, lens, B, S, H, *, p_drop=0.0, rng=None, stream_id=0, dbias=None, stream=None):
+    """``dbias`` (fp32 [3*H*64], optional): accumulates the column sums of ``dqkv`` (fused QKV bias gradient)."""
     check(lib().dcad_attn_bwd(ptr(qkv), ptr(ctx), ptr(dctx), ptr(lse2), ptr(dqkv), ptr(lens), B, S, H, p_drop,
-                              ptr(rng), stream_id, stream_ptr(stream)), "dcad_attn_bwd")
+                              ptr(rng), stream_id, ptr(dbias), stream_ptr(stream)), "dcad_attn_bwd")
     return dqkv
 
 

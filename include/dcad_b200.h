@@ -62,6 +62,12 @@ int dcad_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, i
                    int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
                    int out_fp32, int split_k, int block_n, int max_ctas, void* stream);
 
+/* dcad_gemm_bf16 with a bf16 output whose epilogue ALSO accumulates the column sums of D into colsum [N] (fp32,
+ * atomics): the bias gradient of the Linear layer whose output gradient D is, without a second pass over D. */
+int dcad_gemm_bf16_colsum(const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major, int lda,
+                          int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
+                          int block_n, int max_ctas, float* colsum, void* stream);
+
 /* Up to DCAD_GEMM_GROUP_MAX independent fp32-output GEMMs (no epilogue) that share operand layouts and tile width, in
  * ONE persistent launch: one prologue and pipeline fill, work units of all problems spread over the SMs together.
  * The four weight-gradient GEMMs of a transformer block use it.  split_k[i] > 1 accumulates problem i into D[i] with
@@ -202,9 +208,10 @@ int dcad_xgpu_barrier(const void* const* pads, int rank, int n, const uint64_t* 
  * qkv [B*S, 3*H*64] bf16 (Q | K | V), ctx [B*S, H*64] bf16, lse2 [B*H*128] fp32, lens [B] valid key counts or NULL. */
 int dcad_attn_fwd(const void* qkv, void* ctx, float* lse2, const int32_t* lens, int B, int S, int H, float p_drop,
                   const uint64_t* rng, uint32_t stream_id, void* stream);
+/* dbias (may be NULL): [3*H*64] fp32, += column sums of dqkv = gradient of the fused QKV bias (atomics). */
 int dcad_attn_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse2, void* dqkv,
                   const int32_t* lens, int B, int S, int H, float p_drop, const uint64_t* rng, uint32_t stream_id,
-                  void* stream);
+                  float* dbias, void* stream);
 
 /* ---- FedAvg (reference server.py:67-79) ---- */
 #define DCAD_FED_MAX_CLIENTS 16

@@ -114,6 +114,27 @@ def test_gemm_group_matches_separate_launches(nv):
         assert _rel(out, ref + 1.0) < 1e-3
 
 
+@pytest.mark.parametrize("bn", [64, 192, 256])
+def test_gemm_epilogue_column_sums(nv, bn):
+    """dGELU GEMM whose epilogue also accumulates the column sums of its output (bias gradient of the consumer)."""
+    torch.manual_seed(4)
+    M, N, K = 300, 776, 320          # ragged rows and columns
+    a = torch.randn(M, K, device="cuda").bfloat16()
+    w = (torch.randn(K, N, device="cuda") * 0.05).bfloat16()     # MN-major B, like a dgrad
+    aux = torch.randn(M, N, device="cuda").bfloat16()
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    cs = torch.full((N,), 2.0, device="cuda")
+    nv.gemm_bf16(a, w, out, b_major=nv.MAJOR_MN, aux=aux, epi=nv.EPI_DGELU, block_n=bn, colsum=cs)
+    x = aux.float().requires_grad_(True)
+    F.gelu(x).backward(torch.ones_like(x))
+    ref = (a.float() @ w.float()) * x.grad
+    assert _rel(out, ref) < 1e-2
+    assert _rel(cs - 2.0, ref.sum(0)) < 1e-2
+    plain = torch.empty_like(out)
+    nv.gemm_bf16(a, w, plain, b_major=nv.MAJOR_MN, aux=aux, epi=nv.EPI_DGELU, block_n=bn)
+    assert torch.equal(plain, out)
+
+
 def test_gemm_split_k_reduce_add(nv):
     torch.manual_seed(11)
     T, Nw, Kw = 2048, 768, 512      # dW[Nw, Kw] = dY[T, Nw]^T X[T, Kw]
@@ -464,8 +485,11 @@ def test_attention_fwd_bwd(nv, S):
     dctx = torch.randn(B * S, H * 64, device="cuda").bfloat16()
     ref.backward(dctx.float())
     dqkv = torch.empty_like(qkv)
-    nv.attn_bwd(qkv, ctx, dctx, lse2, dqkv, lens, B, S, H)
+    dbias = torch.full((3 * H * 64,), 0.5, device="cuda")
+    nv.attn_bwd(qkv, ctx, dctx, lse2, dqkv, lens, B, S, H, dbias=dbias)
     assert _rel(dqkv, q32.grad) < 3e-2
+    # fused bias gradient = column sums of dqkv (accumulated on top of what was there)
+    assert _rel(dbias - 0.5, q32.grad.sum(0)) < 2e-2
     # padded keys receive exactly zero dK/dV
     g = dqkv.view(B, S, 3, H * 64)
     assert torch.all(g[1, 57:, 1:] == 0) and torch.all(g[2, 5:, 1:] == 0)
