@@ -15,7 +15,7 @@ adam_flat_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict
                  __nv_bfloat16* __restrict__ p_bf16, int64_t n, int64_t bf16_begin, int64_t bf16_end,
                  int64_t zero_begin, int64_t zero_end, float lr, float beta1, float beta2, float eps,
                  const uint64_t* __restrict__ state, const uint8_t* __restrict__ row_flags, int64_t rows_begin,
-                 int64_t rows_end, int row_len) {
+                 int64_t rows_end, int row_len, unsigned int* __restrict__ advance_ticket) {
     __shared__ float s_c[2];
     pdl_trigger();
     pdl_wait();
@@ -52,6 +52,18 @@ adam_flat_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict
             o.x = pack_bf16x2(pp.x, pp.y);
             o.y = pack_bf16x2(pp.z, pp.w);
             *reinterpret_cast<uint2*>(p_bf16 + (i - bf16_begin)) = o;
+        }
+    }
+    if (advance_ticket) {
+        // Last launch of the step: the block that finishes last advances the step counter (every block read it at its
+        // start, and none can read it after this point), which saves the separate one-thread launch.
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            if (atomicAdd(advance_ticket, 1u) == gridDim.x - 1) {
+                *advance_ticket = 0u;
+                const_cast<uint64_t*>(state)[1] += 1;
+            }
         }
     }
 }
@@ -151,8 +163,9 @@ extern "C" int dcad_adam_step_rows(float* p, float* g, float* m, float* v, void*
                                    int64_t bf16_begin, int64_t bf16_end, int64_t zero_begin, int64_t zero_end,
                                    float lr, float beta1, float beta2, float eps, const uint64_t* state,
                                    const uint8_t* row_flags, int64_t rows_begin, int64_t rows_end, int row_len,
-                                   void* stream) {
+                                   unsigned int* advance_ticket, void* stream) {
     if (n <= 0) return 0;
+    if (advance_ticket && state == nullptr) return DCAD_ERR_BAD_ARGUMENT;
     if (row_flags && (row_len <= 0 || (row_len & 3) || (rows_begin & 3))) return DCAD_ERR_BAD_ALIGNMENT;
     if ((n | bf16_begin | bf16_end | zero_begin | zero_end) & 3) return DCAD_ERR_BAD_ALIGNMENT;
     if ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) |
@@ -164,14 +177,14 @@ extern "C" int dcad_adam_step_rows(float* p, float* g, float* m, float* v, void*
     return (int)launch_pdl(adam_flat_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0,
                            reinterpret_cast<cudaStream_t>(stream), p, g, m, v, reinterpret_cast<__nv_bfloat16*>(p_bf16),
                            n, bf16_begin, bf16_end, zero_begin, zero_end, lr, beta1, beta2, eps, state, row_flags,
-                           rows_begin, rows_end, row_len);
+                           rows_begin, rows_end, row_len, advance_ticket);
 }
 
 extern "C" int dcad_adam_step(float* p, float* g, float* m, float* v, void* p_bf16, int64_t n, int64_t bf16_begin,
                               int64_t bf16_end, int64_t zero_begin, int64_t zero_end, float lr, float beta1,
                               float beta2, float eps, const uint64_t* state, void* stream) {
     return dcad_adam_step_rows(p, g, m, v, p_bf16, n, bf16_begin, bf16_end, zero_begin, zero_end, lr, beta1, beta2,
-                               eps, state, nullptr, 0, 0, 1, stream);
+                               eps, state, nullptr, 0, 0, 1, nullptr, stream);
 }
 
 extern "C" int dcad_step_advance(uint64_t* state, void* stream) {

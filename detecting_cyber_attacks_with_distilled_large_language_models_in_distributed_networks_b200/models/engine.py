@@ -180,6 +180,7 @@ class B200Engine:
         # others (their g, m and v are exactly zero, so the update is the identity) -- flow sentences use a small
         # part of the 30522-row table, which is more than a third of all parameters
         self.touched_rows = torch.zeros(dims.vocab_size, device=dev, dtype=torch.uint8)
+        self._step_ticket = torch.zeros(1, device=dev, dtype=torch.int32)
         self.loss_accum = torch.zeros(2, **f32)                       # {sum of batch-mean losses, #batches}
         self.eval_loss_accum = torch.zeros(2, **f32)
         self.confusion = torch.zeros(4, device=dev, dtype=torch.int32)  # [true*2 + pred]
@@ -521,7 +522,7 @@ class B200Engine:
         self._fork(tail_wgrads)
         return G.e, G.a
 
-    def _adam_range(self, lo: int, hi: int) -> None:
+    def _adam_range(self, lo: int, hi: int, advance: bool = False) -> None:
         """Adam + zero_grad (+ bf16 mirror refresh for the GEMM-weight part) on arena elements [lo, hi)."""
         a = self.arena
         bf_hi = min(hi, a.layout.gemm_end)
@@ -535,8 +536,11 @@ class B200Engine:
         args = (a.flat[lo:hi], a.grad[lo:hi], a.exp_avg[lo:hi], a.exp_avg_sq[lo:hi],
                 a.bf16[lo:bf_hi] if bf_hi > lo else None, hi - lo, 0, max(bf_hi - lo, 0), 0, 0 if stored else hi - lo,
                 self.lr, self.betas[0], self.betas[1], self.eps, self.rng)
+        ticket = self._step_ticket if advance else None  # last launch of the step also advances the step counter
         if lo <= w0 and w1 <= hi:  # the range holds the word-embedding table: skip rows without optimizer state
-            self._k(nv.adam_step_rows, *args, self.touched_rows, w0 - lo, w1 - lo, self.dims.dim)
+            self._k(nv.adam_step_rows, *args, self.touched_rows, w0 - lo, w1 - lo, self.dims.dim, ticket)
+        elif advance:
+            self._k(nv.adam_step_rows, *args, None, 0, 0, 4, ticket)
         else:
             self._k(nv.adam_step, *args)
 
@@ -545,9 +549,8 @@ class B200Engine:
         lay = a.layout
         if self.dp is None:
             # GEMM weights were already updated block by block under the backward pass when early_adam was on
-            self._adam_range(lay.gemm_end if getattr(self, "_adam_early_done", False) else 0, lay.total)
+            self._adam_range(lay.gemm_end if getattr(self, "_adam_early_done", False) else 0, lay.total, advance=True)
             self._adam_early_done = False
-            self._k(nv.step_advance, self.rng)
             return
         # ---- data-parallel client: reduce-scatter (already done tile by tile for the GEMM weights by the wgrad
         # epilogues) -> sharded Adam with the parameter all-gather fused in -> barrier ----

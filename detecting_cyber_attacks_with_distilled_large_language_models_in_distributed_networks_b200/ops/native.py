@@ -109,7 +109,7 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("dcad_tail_head", [P, I, L64, P, P, P, P, P, F, F, U32, P, P, P, F, U32, P, I, I, P, P, P, P, P, P, P, P, P, P])
     sig("dcad_cls_head_eval", [P, I, P, P, P, I, I, P, P, P, P, P])
     sig("dcad_adam_step", [P, P, P, P, P, L64, L64, L64, L64, L64, F, F, F, F, P, P])
-    sig("dcad_adam_step_rows", [P, P, P, P, P, L64, L64, L64, L64, L64, F, F, F, F, P, P, L64, L64, I, P])
+    sig("dcad_adam_step_rows", [P, P, P, P, P, L64, L64, L64, L64, L64, F, F, F, F, P, P, L64, L64, I, P, P])
     sig("dcad_step_advance", [P, P])
     sig("dcad_adam_step_dp", [P, P, P, P, L64, L64, L64, L64, L64, L64, F, F, F, F, F, P, P, P, I, I, P])
     sig("dcad_xgpu_barrier", [P, I, I, P, U32, P])
@@ -368,13 +368,14 @@ def adam_step(p, g, m, v, p_bf16, n, bf16_begin, bf16_end, zero_begin, zero_end,
 
 
 def adam_step_rows(p, g, m, v, p_bf16, n, bf16_begin, bf16_end, zero_begin, zero_end, lr, beta1, beta2, eps, state,
-                   row_flags, rows_begin, rows_end, row_len, stream=None):
+                   row_flags, rows_begin, rows_end, row_len, advance_ticket=None, stream=None):
     """Adam over ``n`` elements where [rows_begin, rows_end) is a table of ``row_len``-element rows and rows whose
-    byte in ``row_flags`` is 0 (never received a gradient: g = m = v = 0) are skipped -- an exact no-op for them."""
-    assert row_flags.dtype == torch.uint8
+    byte in ``row_flags`` is 0 (never received a gradient: g = m = v = 0) are skipped -- an exact no-op for them.
+    ``advance_ticket`` (zeroed int32 device word): the last block to finish also advances the step counter."""
+    assert row_flags is None or row_flags.dtype == torch.uint8
     check(lib().dcad_adam_step_rows(ptr(p), ptr(g), ptr(m), ptr(v), ptr(p_bf16), n, bf16_begin, bf16_end, zero_begin,
                                     zero_end, lr, beta1, beta2, eps, ptr(state), ptr(row_flags), rows_begin, rows_end,
-                                    row_len, stream_ptr(stream)), "dcad_adam_step_rows")
+                                    row_len, ptr(advance_ticket), stream_ptr(stream)), "dcad_adam_step_rows")
 
 
 def adam_step_dp(p, g, m, v, begin, end, bf16_begin, bf16_end, push32_begin, push32_end, lr, beta1, beta2, eps,

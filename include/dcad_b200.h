@@ -186,11 +186,13 @@ int dcad_adam_step(float* p, float* g, float* m, float* v, void* p_bf16, int64_t
                    float eps, const uint64_t* state, void* stream);
 /* Same update, but elements [rows_begin, rows_end) form a table of rows of row_len elements (the word embeddings) and
  * a row is skipped while row_flags[row] == 0.  Exact, not an approximation: a row that never received a gradient has
- * g = m = v = 0, so Adam leaves it unchanged (no weight decay in the reference, client1.py:380). */
+ * g = m = v = 0, so Adam leaves it unchanged (no weight decay in the reference, client1.py:380).
+ * advance_ticket (may be NULL): a zero-initialised device word; when given, the block that finishes last also does
+ * state[1] += 1 (what dcad_step_advance does), for the last Adam launch of a step. */
 int dcad_adam_step_rows(float* p, float* g, float* m, float* v, void* p_bf16, int64_t n, int64_t bf16_begin,
                         int64_t bf16_end, int64_t zero_begin, int64_t zero_end, float lr, float beta1, float beta2,
                         float eps, const uint64_t* state, const uint8_t* row_flags, int64_t rows_begin,
-                        int64_t rows_end, int row_len, void* stream);
+                        int64_t rows_end, int row_len, unsigned int* advance_ticket, void* stream);
 int dcad_step_advance(uint64_t* state, void* stream);
 /* Intra-client data parallelism (no counterpart in the reference, which has no DP): sharded Adam over the arena
  * elements [begin, end) this rank owns, gradients scaled by grad_scale (1/G after a sum over the group), with the

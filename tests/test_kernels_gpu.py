@@ -447,9 +447,16 @@ def test_adam_row_skipping_is_exact(nv):
         ref_p.grad = g.clone()
         opt.step()
         gk = g.clone()
-        nv.adam_step_rows(p, gk, m, v, None, n, 0, 0, 0, n, 1e-3, 0.9, 0.999, 1e-8, state, flags, head,
-                          head + rows * cols, cols)
-        nv.step_advance(state)
+        ticket = torch.zeros(1, device="cuda", dtype=torch.int32)
+        if step % 2:   # the kernel's last block advances the step counter itself ...
+            nv.adam_step_rows(p, gk, m, v, None, n, 0, 0, 0, n, 1e-3, 0.9, 0.999, 1e-8, state, flags, head,
+                              head + rows * cols, cols, ticket)
+            assert int(ticket.item()) == 0
+        else:          # ... or a separate launch does
+            nv.adam_step_rows(p, gk, m, v, None, n, 0, 0, 0, n, 1e-3, 0.9, 0.999, 1e-8, state, flags, head,
+                              head + rows * cols, cols)
+            nv.step_advance(state)
+        assert int(state[1].item()) == step + 1
         assert torch.all(gk == 0)
     assert torch.allclose(p, ref_p.detach(), rtol=1e-5, atol=1e-7)
     untouched = flags == 0
