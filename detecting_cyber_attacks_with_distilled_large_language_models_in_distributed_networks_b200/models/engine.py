@@ -117,6 +117,10 @@ class B200Engine:
         # (partial waves, prologue/epilogue tails of its small dependent kernels).
         self.overlap_wgrad = overlap_wgrad = overlap_wgrad and os.environ.get("DCAD_OVERLAP_WGRAD", "1") != "0"
         self._side = torch.cuda.Stream(device=dev) if overlap_wgrad else None
+        # Programmatic dependent launch pays on a single chain (1.918 -> 1.878 ms when it was introduced) but not
+        # next to the second branch: early-launched CTAs of the chain park in griddepcontrol.wait on SMs the branch
+        # could be using (same box: PDL everywhere 1.533 ms, main chain only 1.523 ms, nowhere 1.517 ms per step).
+        self.use_pdl = os.environ.get("DCAD_PDL", "0" if overlap_wgrad else "1") != "0"
         if dp is not None:
             flat_params, bf16_params = dp.param_tensor(), dp.mirror_tensor()
         self.arena = ParamArena(dims, dev, flat=flat_params, with_optimizer_state=True, with_bf16=bf16_params is None)
@@ -370,8 +374,16 @@ class B200Engine:
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream())
         self._side.wait_event(ev)
-        with torch.cuda.stream(self._side):
-            fn()
+        # Side-branch kernels are always launched WITHOUT programmatic dependent launch: an early-launched
+        # persistent GEMM would sit in griddepcontrol.wait holding a whole SM's shared memory that the chain needs.
+        side_pdl = os.environ.get("DCAD_SIDE_PDL", "0") != "0"
+        prev = None if side_pdl else nv.set_pdl(False)
+        try:
+            with torch.cuda.stream(self._side):
+                fn()
+        finally:
+            if prev is not None:
+                nv.set_pdl(prev)
 
     def _side_mark(self):
         if self._side is None:
@@ -579,6 +591,13 @@ class B200Engine:
 
     # ------------------------------------------------------------------------------------------------ public API
     def _train_step_kernels(self) -> None:
+        prev_pdl = nv.set_pdl(self.use_pdl)
+        try:
+            self._train_step_kernels_inner()
+        finally:
+            nv.set_pdl(prev_pdl)
+
+    def _train_step_kernels_inner(self) -> None:
         self._n_launch = 0
         fuse_head = self.prune_last_layer and self.plan.fuse_tail_head and self.B <= 64
         h, stride = self._forward(self.B, train=True, fuse_head=fuse_head)
