@@ -158,6 +158,15 @@ __global__ void step_advance_kernel(uint64_t* state) {
 
 using namespace dcad;
 
+// Resident 256-thread blocks per SM of the flat Adam kernel.  8 fill an SM's 2048 thread slots, which keeps every
+// other kernel off the SM while Adam streams; fewer leave room for a GEMM CTA of the other graph branch to co-reside.
+static int g_adam_blocks_per_sm = 16;
+extern "C" int dcad_set_adam_blocks_per_sm(int blocks) {
+    const int prev = g_adam_blocks_per_sm;
+    if (blocks >= 1 && blocks <= 64) g_adam_blocks_per_sm = blocks;
+    return prev;
+}
+
 // n, bf16_begin/end, zero_begin/end are element offsets into the arena and must be multiples of 4.
 extern "C" int dcad_adam_step_rows(float* p, float* g, float* m, float* v, void* p_bf16, int64_t n,
                                    int64_t bf16_begin, int64_t bf16_end, int64_t zero_begin, int64_t zero_end,
@@ -172,7 +181,7 @@ extern "C" int dcad_adam_step_rows(float* p, float* g, float* m, float* v, void*
          reinterpret_cast<uintptr_t>(v)) & 15u)
         return DCAD_ERR_BAD_ALIGNMENT;
     int64_t blocks = (n / 4 + 255) / 256;
-    const int64_t cap = 148 * 16;
+    const int64_t cap = 148 * static_cast<int64_t>(g_adam_blocks_per_sm);
     if (blocks > cap) blocks = cap;
     return (int)launch_pdl(adam_flat_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0,
                            reinterpret_cast<cudaStream_t>(stream), p, g, m, v, reinterpret_cast<__nv_bfloat16*>(p_bf16),

@@ -116,7 +116,8 @@ class B200Engine:
         # graph they become a parallel branch whose CTAs fill the SMs that the data-gradient chain leaves idle
         # (partial waves, prologue/epilogue tails of its small dependent kernels).
         self.overlap_wgrad = overlap_wgrad = overlap_wgrad and os.environ.get("DCAD_OVERLAP_WGRAD", "1") != "0"
-        self._side = torch.cuda.Stream(device=dev) if overlap_wgrad else None
+        self._side = (torch.cuda.Stream(device=dev, priority=int(os.environ.get("DCAD_SIDE_PRIO", "0")))
+                      if overlap_wgrad else None)
         # Programmatic dependent launch pays on a single chain (1.918 -> 1.878 ms when it was introduced) but not
         # next to the second branch: early-launched CTAs of the chain park in griddepcontrol.wait on SMs the branch
         # could be using (same box: PDL everywhere 1.533 ms, main chain only 1.523 ms, nowhere 1.517 ms per step).
@@ -625,7 +626,8 @@ class B200Engine:
 
     def capture(self) -> None:
         """Warm up eagerly, then capture the training step (and its end-to-end variant) into CUDA graphs."""
-        s = torch.cuda.Stream(device=self.device, priority=-1)  # the critical chain outranks the weight-gradient branch
+        # the critical chain outranks the weight-gradient branch
+        s = torch.cuda.Stream(device=self.device, priority=int(os.environ.get("DCAD_MAIN_PRIO", "-1")))
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
             saved = (self.arena.flat.clone(), self.rng.clone())

@@ -57,6 +57,8 @@ def lib() -> ctypes.CDLL:
         _declare(_LIB)
         if os.environ.get("DCAD_PDL", "1") == "0":
             _LIB.dcad_set_pdl(0)
+        if os.environ.get("DCAD_ADAM_BLOCKS"):
+            _LIB.dcad_set_adam_blocks_per_sm(int(os.environ["DCAD_ADAM_BLOCKS"]))
     return _LIB
 
 
@@ -92,6 +94,7 @@ def _declare(L: ctypes.CDLL) -> None:
     P, I, F, L64, U32 = c_void_p, c_int, c_float, c_int64, c_uint32
     sig("dcad_version", [])
     sig("dcad_set_pdl", [I])
+    sig("dcad_set_adam_blocks_per_sm", [I])
     sig("dcad_gemm_bf16", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, I, I, P])
     sig("dcad_gemm_bf16_colsum", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, P, P])
     sig("dcad_gemm_bf16_group", [I, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, P])

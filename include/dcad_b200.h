@@ -177,6 +177,9 @@ int dcad_tail_head(const float* a_partials, int splits, int64_t slice_elems, con
                    const uint64_t* rng, int batch, int cols, float* loss_accum, float* logits, float* dW, float* db,
                    void* dz, void* da, float* dgamma, float* dbeta, float* dbias, void* stream);
 
+/* Grid size of the flat Adam kernels: 148 * blocks 256-thread blocks (default 16).  Returns the previous value. */
+int dcad_set_adam_blocks_per_sm(int blocks);
+
 /* ---- optimizer (reference client1.py:106,110,380: Adam(lr=2e-5) + zero_grad) ----
  * One launch over the flat arena.  Elements in [bf16_begin, bf16_end) are also written as bf16 to
  * p_bf16[i - bf16_begin]; gradients in [zero_begin, zero_end) are cleared after use.  The step number is
