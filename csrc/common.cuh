@@ -107,6 +107,12 @@ __device__ __forceinline__ void warp_colsum(float (&v)[N], uint32_t lane) {
     }
 }
 
+// 16-byte vector reduction: four fp32 atomic adds in ONE instruction (sm_90+).  The embedding backward issues
+// 1536 adds per token row; as scalar REDs they saturate the load/store queue (ncu: lg_throttle is its top stall).
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&v);

@@ -318,14 +318,18 @@ embed_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy1, const __nv_bfloat16* 
 #pragma unroll
         for (int v = 0; v < NV; ++v) {
             const int col = (v * 32 + lane) * 8;
-            float pg[8];
+            float pg[8], dx[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-                const float dx = rs * (g[v][j] - c1 - xh[v][j] * c2);
-                atomicAdd(dword + static_cast<size_t>(id) * COLS + col + j, dx);
-                atomicAdd(dpos + static_cast<size_t>(ps) * COLS + col + j, dx);
+                dx[j] = rs * (g[v][j] - c1 - xh[v][j] * c2);
                 pg[j] = d[v][j] * xh[v][j];
             }
+            float* dw = dword + static_cast<size_t>(id) * COLS + col;
+            float* dp = dpos + static_cast<size_t>(ps) * COLS + col;
+            red_add_v4(dw, dx[0], dx[1], dx[2], dx[3]);
+            red_add_v4(dw + 4, dx[4], dx[5], dx[6], dx[7]);
+            red_add_v4(dp, dx[0], dx[1], dx[2], dx[3]);
+            red_add_v4(dp + 4, dx[4], dx[5], dx[6], dx[7]);
             *reinterpret_cast<float4*>(slot + col) = make_float4(pg[0], pg[1], pg[2], pg[3]);
             *reinterpret_cast<float4*>(slot + col + 4) = make_float4(pg[4], pg[5], pg[6], pg[7]);
             *reinterpret_cast<float4*>(slot + COLS + col) = make_float4(d[v][0], d[v][1], d[v][2], d[v][3]);
