@@ -193,12 +193,15 @@ add_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy1, const PartialIn dy1_par
         for (int c = lane; c < 3 * COLS; c += 32) slot[c] = 0.f;
     }
     __syncthreads();
-    for (int c = threadIdx.x; c < 3 * COLS; c += blockDim.x) {
-        float t = 0.f;
+    for (int c = threadIdx.x * 4; c < 3 * COLS; c += blockDim.x * 4) {  // four columns per thread, one vector RED
+        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-        for (int w = 0; w < LN_WARPS; ++w) t += s_part[w * 3 * COLS + c];
+        for (int w = 0; w < LN_WARPS; ++w) {
+            const float4 a = *reinterpret_cast<const float4*>(s_part + w * 3 * COLS + c);
+            t.x += a.x; t.y += a.y; t.z += a.z; t.w += a.w;
+        }
         float* dst = c < COLS ? dgamma : (c < 2 * COLS ? dbeta : dbias);
-        if (dst) atomicAdd(dst + (c % COLS), t);
+        if (dst) red_add_v4(dst + (c % COLS), t.x, t.y, t.z, t.w);
     }
 }
 
@@ -339,11 +342,15 @@ embed_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy1, const __nv_bfloat16* 
         for (int c = lane; c < 2 * COLS; c += 32) slot[c] = 0.f;
     }
     __syncthreads();
-    for (int c = threadIdx.x; c < 2 * COLS; c += blockDim.x) {
-        float t = 0.f;
+    for (int c = threadIdx.x * 4; c < 2 * COLS; c += blockDim.x * 4) {
+        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-        for (int w = 0; w < LN_WARPS; ++w) t += s_part[w * 2 * COLS + c];
-        if (t != 0.f) atomicAdd((c < COLS ? dgamma : dbeta) + (c % COLS), t);
+        for (int w = 0; w < LN_WARPS; ++w) {
+            const float4 a = *reinterpret_cast<const float4*>(s_part + w * 2 * COLS + c);
+            t.x += a.x; t.y += a.y; t.z += a.z; t.w += a.w;
+        }
+        if (t.x != 0.f || t.y != 0.f || t.z != 0.f || t.w != 0.f)
+            red_add_v4((c < COLS ? dgamma : dbeta) + (c % COLS), t.x, t.y, t.z, t.w);
     }
 }
 
