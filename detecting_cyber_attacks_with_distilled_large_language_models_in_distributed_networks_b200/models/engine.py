@@ -139,13 +139,16 @@ class B200Engine:
         bf = dict(device=dev, dtype=torch.bfloat16)
         f32 = dict(device=dev, dtype=torch.float32)
         # static inputs
-        self.ids = torch.zeros(T, device=dev, dtype=torch.int32)
-        self.lens = torch.full((batch,), seq, device=dev, dtype=torch.int32)
-        self.labels = torch.zeros(batch, device=dev, dtype=torch.int32)
         # pinned staging for the end-to-end path: ids | lens | labels in one buffer -> one H2D copy per step
         self.h_in = torch.zeros(T + 2 * batch, dtype=torch.int32).pin_memory()
+        self._h_in_np = self.h_in.numpy()
         self.d_in = torch.zeros(T + 2 * batch, device=dev, dtype=torch.int32)
+        # the kernels read ids | lens | labels straight out of the staging buffer: the one H2D copy of the end-to-end
+        # path is all the input handling there is (no unpack kernels)
+        self.ids, self.lens, self.labels = self.d_in[:T], self.d_in[T: T + batch], self.d_in[T + batch:]
+        self.lens.fill_(seq)
         self.h_loss = torch.zeros(2, dtype=torch.float32).pin_memory()
+        self._h_loss_np = self.h_loss.numpy()
         # saved activations
         self.x = [torch.empty(T, D, **bf) for _ in range(L + 1)]
         self.qkv = [torch.empty(T, 3 * D, **bf) for _ in range(L)]
@@ -614,9 +617,7 @@ class B200Engine:
 
     def _unpack_inputs(self) -> None:
         T, B = self.T, self.B
-        self.ids.copy_(self.d_in[:T])
-        self.lens.copy_(self.d_in[T: T + B])
-        self.labels.copy_(self.d_in[T + B:])
+        pass  # ids / lens / labels are views of d_in
 
     def set_batch(self, input_ids: torch.Tensor, lens: torch.Tensor, labels: torch.Tensor) -> None:
         """Device-side batch set-up (inputs already on the GPU, e.g. from the device-resident dataset)."""
@@ -668,9 +669,10 @@ class B200Engine:
         """End-to-end step as a user calls it: host tensors in, running mean loss out.  Copies the batch through
         pinned memory (one H2D), runs the step, reads back the loss accumulators (one D2H, one sync)."""
         T, B = self.T, self.B
-        self.h_in[:T].copy_(ids.reshape(-1))
-        self.h_in[T: T + B].copy_(lens)
-        self.h_in[T + B:].copy_(labels)
+        hn = self._h_in_np  # numpy views of the pinned staging buffers: three memcpys, no tensor-op dispatch
+        hn[:T] = ids.numpy().reshape(-1)
+        hn[T: T + B] = lens.numpy()
+        hn[T + B:] = labels.numpy()
         if self._graph_train_e2e is not None:
             self._graph_train_e2e.replay()
         else:
@@ -679,7 +681,8 @@ class B200Engine:
             self._train_step_kernels()
             self.h_loss.copy_(self.loss_accum, non_blocking=True)
         torch.cuda.current_stream().synchronize()
-        return float(self.h_loss[0] / max(float(self.h_loss[1]), 1.0))
+        hl = self._h_loss_np
+        return float(hl[0]) / max(float(hl[1]), 1.0)
 
     @property
     def h2d_bytes_per_step(self) -> int:
