@@ -122,6 +122,9 @@ class B200Engine:
         # next to the second branch: early-launched CTAs of the chain park in griddepcontrol.wait on SMs the branch
         # could be using (same box: PDL everywhere 1.533 ms, main chain only 1.523 ms, nowhere 1.517 ms per step).
         self.use_pdl = os.environ.get("DCAD_PDL", "0" if overlap_wgrad else "1") != "0"
+        # ... but the branch is idle during the forward pass and the CLS-row tail, where the chain is alone again:
+        # there PDL is on ("auto"); DCAD_PDL_FWD=0/1 forces it
+        self.use_pdl_fwd = os.environ.get("DCAD_PDL_FWD", os.environ.get("DCAD_PDL", "1")) != "0"
         if dp is not None:
             flat_params, bf16_params = dp.param_tensor(), dp.mirror_tensor()
         self.arena = ParamArena(dims, dev, flat=flat_params, with_optimizer_state=True, with_bf16=bf16_params is None)
@@ -436,6 +439,8 @@ class B200Engine:
         side_done = {}  # layer -> event marking the end of its side-stream work
         if self.prune_last_layer:
             dy1, dy2 = self._backward_tail_pruned(top, head_fused)
+            if early_adam:  # training step: from here on the second branch has work (see use_pdl)
+                nv.set_pdl(self.use_pdl)
         else:
             # gradient wrt the last hidden states: only the CLS rows are non-zero
             dy1, dy2 = self.gset[(top + 1) % 2].a, None
@@ -595,7 +600,7 @@ class B200Engine:
 
     # ------------------------------------------------------------------------------------------------ public API
     def _train_step_kernels(self) -> None:
-        prev_pdl = nv.set_pdl(self.use_pdl)
+        prev_pdl = nv.set_pdl(self.use_pdl_fwd)
         try:
             self._train_step_kernels_inner()
         finally:
