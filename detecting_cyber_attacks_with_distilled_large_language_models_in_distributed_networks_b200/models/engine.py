@@ -430,6 +430,7 @@ class B200Engine:
         issued: the HBM-bound optimizer pass then runs underneath the tensor-bound backward of the earlier blocks, and
         ``_optimizer`` only has the embeddings / biases / LayerNorm / classifier region left."""
         d, S, B, pl = self.dims, self.S, self.B, self.plan
+        in_step = early_adam  # called from the training step (as opposed to a bare backward in tests / tools)
         early_adam = early_adam and self._side is not None and self.dp is None
         self._adam_early_done = early_adam
         H, D = d.n_heads, d.dim
@@ -439,7 +440,7 @@ class B200Engine:
         side_done = {}  # layer -> event marking the end of its side-stream work
         if self.prune_last_layer:
             dy1, dy2 = self._backward_tail_pruned(top, head_fused)
-            if early_adam:  # training step: from here on the second branch has work (see use_pdl)
+            if in_step:  # training step: from here on the second branch has work (see use_pdl)
                 nv.set_pdl(self.use_pdl)
         else:
             # gradient wrt the last hidden states: only the CLS rows are non-zero
