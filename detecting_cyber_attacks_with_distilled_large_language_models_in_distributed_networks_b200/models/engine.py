@@ -652,6 +652,15 @@ class B200Engine:
                 self._train_step_kernels()
                 self.h_loss.copy_(self.loss_accum, non_blocking=True)
             self._graph_train_e2e = g2
+            # evaluation forward (dropout off) on a full batch; partial last batches run eagerly
+            self._eval_kernels(self.B, True)
+            s.synchronize()
+            g3 = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g3, stream=s):
+                self._eval_kernels(self.B, True)
+            self._graph_eval = g3
+            self.eval_loss_accum.zero_()
+            self.confusion.zero_()
             # undo the warm-up steps
             self.arena.flat.copy_(saved[0])
             self.rng.copy_(saved[1])
@@ -714,6 +723,13 @@ class B200Engine:
     def eval_batch(self, rows_b: Optional[int] = None, want_probs: bool = False) -> None:
         """Forward (dropout off) + classifier metrics on the first ``rows_b`` samples of the static inputs."""
         rows_b = self.B if rows_b is None else rows_b
+        g = getattr(self, "_graph_eval", None)
+        if g is not None and rows_b == self.B:   # full batches replay a captured graph (probs / preds always written)
+            g.replay()
+            return
+        self._eval_kernels(rows_b, want_probs)
+
+    def _eval_kernels(self, rows_b: int, want_probs: bool) -> None:
         h, stride = self._forward(rows_b, train=False)
         self._k(nv.cls_head_eval, h, stride, self.cw, self.cb, self.labels, rows_b,
                 self.eval_loss_accum, self.confusion, self.probs if want_probs else None,
