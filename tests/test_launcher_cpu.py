@@ -32,3 +32,14 @@ def test_two_rank_gloo_launch(tmp_path):
     for cid in (1, 2):
         for kind in ("local", "aggregated"):
             assert len(pd.read_csv(os.path.join(tmp, f"client{cid}_{kind}_metrics.csv"))) == 1
+
+
+def test_clock_sampler_degrades_gracefully_without_a_gpu():
+    """bench.py samples clocks through NVML (or nvidia-smi); on a machine with neither it must still return the
+    dictionary shape the JSON line expects."""
+    from detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200.utils.clocks import (
+        ClockSampler)
+
+    out = ClockSampler(0).start().stop()
+    assert set(out) >= {"sm_mhz", "sm_max_mhz", "reasons", "samples"}
+    assert isinstance(out["reasons"], list)
