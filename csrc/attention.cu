@@ -25,6 +25,85 @@ constexpr int AT_D = 64;         // head dim
 constexpr int TILE_BYTES = AT_S * AT_D * 2;  // 16 KB: [128][64] bf16, 128-byte rows, SW128
 constexpr float LOG2E = 1.4426950408889634f;
 
+// Attention-probability dropout draws ONE 32-bit hash per PAIR of adjacent keys and compares its two 16-bit halves
+// with the top 16 bits of the threshold (drop probability quantised to 1/65536: 0.1 -> 0.09999): the softmax loops
+// are ALU-bound and the hash was a fifth of their instructions.  Forward and backward use the same pairing.
+// j = position inside the (even-aligned) run of keys starting at first_idx; h carries the pair's hash from the even
+// element to the odd one (the loops are fully unrolled, so this is straight-line code)
+__device__ __forceinline__ bool attn_keep(uint64_t seed, uint32_t stream, uint32_t first_idx, int j, uint32_t th16,
+                                          uint32_t& h) {
+    if ((j & 1) == 0) h = rng_u32(seed, stream, (first_idx >> 1) + (j >> 1));
+    return ((h >> ((j & 1) * 16)) & 0xFFFFu) >= th16;
+}
+
+// A 32-key chunk of a row is FULL (all keys valid), PARTIAL or EMPTY with respect to the sample's length.  The class is
+// the same for a whole warp (the length is per sample, the chunk per warp), so the softmax loops are specialised on it:
+// no per-element length compare for full chunks, no exp / hash / multiply at all for empty ones.  A typical flow
+// sentence (84 tokens of 128) has 2 full, 1 partial and 1 empty chunk per row.
+enum { CHUNK_FULL = 0, CHUNK_PARTIAL = 1, CHUNK_EMPTY = 2 };
+__device__ __forceinline__ int chunk_mode(int first_key, int len) {
+    return first_key + 32 <= len ? CHUNK_FULL : (first_key >= len ? CHUNK_EMPTY : CHUNK_PARTIAL);
+}
+
+template <int MODE>
+__device__ __forceinline__ float fwd_chunk_max(const uint32_t (&r)[32], int first_key, int len, float mx) {
+    if constexpr (MODE == CHUNK_EMPTY) return mx;
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+        if (MODE == CHUNK_FULL || first_key + j < len) mx = fmaxf(mx, __uint_as_float(r[j]));
+    return mx;
+}
+
+// probabilities (dropped, not yet normalised) of one chunk into pv; returns the chunk's contribution to the row sum
+template <int MODE>
+__device__ __forceinline__ float fwd_chunk_exp(const uint32_t (&r)[32], int first_key, int len, float sc2, float m2,
+                                               uint64_t seed, uint32_t stream_id, uint32_t drop_first, uint32_t thresh,
+                                               uint32_t th16, float keep_scale, float (&pv)[32]) {
+    float sum = 0.f;
+    if constexpr (MODE == CHUNK_EMPTY) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) pv[j] = 0.f;
+        return 0.f;
+    }
+    uint32_t hpair = 0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        float e = (MODE == CHUNK_FULL || first_key + j < len) ? fast_exp2(__uint_as_float(r[j]) * sc2 - m2) : 0.f;
+        sum += e;
+        if (thresh) e = attn_keep(seed, stream_id, drop_first, j, th16, hpair) ? e * keep_scale : 0.f;
+        pv[j] = e;
+    }
+    return sum;
+}
+
+// backward: recomputed probabilities (dropped) into pd and dS = P o (dP_dropped - delta) * scale into ds
+template <int MODE>
+__device__ __forceinline__ void bwd_chunk(const uint32_t (&rs)[32], const uint32_t (&rp)[32], int first_key, int len,
+                                          bool row_ok, float sc2, float l2, float delta, float scale, uint64_t seed,
+                                          uint32_t stream_id, uint32_t drop_first, uint32_t thresh, uint32_t th16,
+                                          float keep_scale, float (&pd)[32], float (&ds)[32]) {
+    if constexpr (MODE == CHUNK_EMPTY) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) { pd[j] = 0.f; ds[j] = 0.f; }
+        return;
+    }
+    uint32_t hpair = 0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        const bool valid = (MODE == CHUNK_FULL || first_key + j < len) && row_ok;
+        const float pr = valid ? fast_exp2(__uint_as_float(rs[j]) * sc2 - l2) : 0.f;
+        float dp = __uint_as_float(rp[j]);
+        float pk = pr;
+        if (thresh) {
+            const bool keep = attn_keep(seed, stream_id, drop_first, j, th16, hpair);
+            pk = keep ? pr * keep_scale : 0.f;
+            dp = keep ? dp * keep_scale : 0.f;
+        }
+        pd[j] = pk;
+        ds[j] = valid ? pr * (dp - delta) * scale : 0.f;
+    }
+}
+
 __device__ __forceinline__ uint64_t attn_seed(const uint64_t* rng) {
     return rng ? rng[0] + rng[1] * 0xD1B54A32D192ED03ULL : 0ULL;
 }
@@ -98,6 +177,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
     }
     const int len = min(lens ? lens[b] : S, S);
     const uint64_t seed = attn_seed(rng);
+    const uint32_t th16 = thresh >> 16;
     const float sc2 = scale * LOG2E;
     mbar_wait(smem_u32(&bar_mma1), 0);
     tc_fence_after();
@@ -109,12 +189,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
     tmem_ld_32x32b_x32(tS + t_lane + key0, r0);
     tmem_ld_32x32b_x32(tS + t_lane + key0 + 32, r1);
     tmem_ld_wait();
+    const int mode0 = chunk_mode(key0, len), mode1 = chunk_mode(key0 + 32, len);  // warp-uniform
     float mx = -INFINITY;
-#pragma unroll
-    for (int j = 0; j < 32; ++j) {
-        if (key0 + j < len) mx = fmaxf(mx, __uint_as_float(r0[j]));
-        if (key0 + 32 + j < len) mx = fmaxf(mx, __uint_as_float(r1[j]));
-    }
+    if (mode0 == CHUNK_FULL) mx = fwd_chunk_max<CHUNK_FULL>(r0, key0, len, mx);
+    else if (mode0 == CHUNK_PARTIAL) mx = fwd_chunk_max<CHUNK_PARTIAL>(r0, key0, len, mx);
+    if (mode1 == CHUNK_FULL) mx = fwd_chunk_max<CHUNK_FULL>(r1, key0 + 32, len, mx);
+    else if (mode1 == CHUNK_PARTIAL) mx = fwd_chunk_max<CHUNK_PARTIAL>(r1, key0 + 32, len, mx);
     s_max[hsel][row] = mx;
     __syncthreads();
     const float m2 = fmaxf(s_max[0][row], s_max[1][row]) * sc2;  // key 0 is always valid -> finite
@@ -123,17 +203,16 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
 #pragma unroll
     for (int c = 0; c < 2; ++c) {
         float pv[32];
+        const int fk = key0 + c * 32, mode = c == 0 ? mode0 : mode1;
+        const uint32_t (&r)[32] = c == 0 ? r0 : r1;
+        if (mode == CHUNK_FULL)
+            sum += fwd_chunk_exp<CHUNK_FULL>(r, fk, len, sc2, m2, seed, stream_id, drop_base + fk, thresh, th16, keep_scale, pv);
+        else if (mode == CHUNK_PARTIAL)
+            sum += fwd_chunk_exp<CHUNK_PARTIAL>(r, fk, len, sc2, m2, seed, stream_id, drop_base + fk, thresh, th16, keep_scale, pv);
+        else
+            sum += fwd_chunk_exp<CHUNK_EMPTY>(r, fk, len, sc2, m2, seed, stream_id, drop_base + fk, thresh, th16, keep_scale, pv);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            const int key = key0 + c * 32 + j;
-            const float sv = __uint_as_float(c == 0 ? r0[j] : r1[j]);
-            float e = key < len ? exp2f(sv * sc2 - m2) : 0.f;
-            sum += e;
-            if (thresh) e = dropout_keep(seed, stream_id, drop_base + key, thresh) ? e * keep_scale : 0.f;
-            pv[j] = e;
-        }
-#pragma unroll
-        for (int j = 0; j < 32; j += 8) st_tile8(sP, row, key0 + c * 32 + j, pv + j);
+        for (int j = 0; j < 32; j += 8) st_tile8(sP, row, fk + j, pv + j);
     }
     s_sum[hsel][row] = sum;
     fence_proxy_async_smem();
@@ -262,6 +341,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     }
     const int len = min(lens ? lens[b] : S, S);
     const uint64_t seed = attn_seed(rng);
+    const uint32_t th16 = thresh >> 16;
     const float sc2 = scale * LOG2E;
     const float l2 = (row < S) ? lse2[static_cast<size_t>(bh) * AT_S + row] : 0.f;
     const uint32_t t_lane = (static_cast<uint32_t>(warp & 3) * 32u) << 16;
@@ -271,25 +351,22 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     tc_fence_after();
 #pragma unroll 1
     for (int c = 0; c < 2; ++c) {
-        uint32_t rs[32], rp[32];
-        tmem_ld_32x32b_x32(tS + t_lane + key0 + c * 32, rs);
-        tmem_ld_32x32b_x32(tdP + t_lane + key0 + c * 32, rp);
-        tmem_ld_wait();
+        const int fk = key0 + c * 32, mode = chunk_mode(fk, len);  // warp-uniform
         float pd[32], ds[32];
+        if (mode == CHUNK_EMPTY) {  // nothing to read or compute: P and dS of padded keys are zero
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            const int key = key0 + c * 32 + j;
-            const bool valid = key < len && row < S;
-            const float pr = valid ? exp2f(__uint_as_float(rs[j]) * sc2 - l2) : 0.f;
-            float dp = __uint_as_float(rp[j]);
-            float pk = pr;
-            if (thresh) {
-                const bool keep = dropout_keep(seed, stream_id, drop_base + key, thresh);
-                pk = keep ? pr * keep_scale : 0.f;
-                dp = keep ? dp * keep_scale : 0.f;
-            }
-            pd[j] = pk;
-            ds[j] = valid ? pr * (dp - delta) * scale : 0.f;
+            for (int j = 0; j < 32; ++j) { pd[j] = 0.f; ds[j] = 0.f; }
+        } else {
+            uint32_t rs[32], rp[32];
+            tmem_ld_32x32b_x32(tS + t_lane + fk, rs);
+            tmem_ld_32x32b_x32(tdP + t_lane + fk, rp);
+            tmem_ld_wait();
+            if (mode == CHUNK_FULL)
+                bwd_chunk<CHUNK_FULL>(rs, rp, fk, len, row < S, sc2, l2, delta, scale, seed, stream_id, drop_base + fk,
+                                      thresh, th16, keep_scale, pd, ds);
+            else
+                bwd_chunk<CHUNK_PARTIAL>(rs, rp, fk, len, row < S, sc2, l2, delta, scale, seed, stream_id,
+                                         drop_base + fk, thresh, th16, keep_scale, pd, ds);
         }
 #pragma unroll
         for (int j = 0; j < 32; j += 8) {
