@@ -189,7 +189,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
     tmem_ld_32x32b_x32(tS + t_lane + key0, r0);
     tmem_ld_32x32b_x32(tS + t_lane + key0 + 32, r1);
     tmem_ld_wait();
-    const int mode0 = chunk_mode(key0, len), mode1 = chunk_mode(key0 + 32, len);  // warp-uniform
+    // Query rows at or past the sample's length are padding: nothing downstream reads their context vector (they are
+    // masked as keys and only the CLS row reaches the head), so a warp whose 32 rows are all padding skips the softmax
+    // and writes zeros.
+    const bool dead_rows = (warp & 3) * 32 >= len;                                 // warp-uniform
+    const int mode0 = dead_rows ? CHUNK_EMPTY : chunk_mode(key0, len);
+    const int mode1 = dead_rows ? CHUNK_EMPTY : chunk_mode(key0 + 32, len);
     float mx = -INFINITY;
     if (mode0 == CHUNK_FULL) mx = fwd_chunk_max<CHUNK_FULL>(r0, key0, len, mx);
     else if (mode0 == CHUNK_PARTIAL) mx = fwd_chunk_max<CHUNK_PARTIAL>(r0, key0, len, mx);
@@ -229,7 +234,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
     }
     const float total = s_sum[0][row] + s_sum[1][row];
     if (hsel == 0 && lse2_out && row < S) lse2_out[static_cast<size_t>(bh) * AT_S + row] = m2 + log2f(total);
-    const float inv = 1.0f / total;
+    const float inv = dead_rows ? 0.f : 1.0f / total;
     mbar_wait(smem_u32(&bar_mma2), 0);
     tc_fence_after();
     {
@@ -351,7 +356,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     tc_fence_after();
 #pragma unroll 1
     for (int c = 0; c < 2; ++c) {
-        const int fk = key0 + c * 32, mode = chunk_mode(fk, len);  // warp-uniform
+        // padded query rows have dO = 0 and receive dQ = 0: their P / dS rows are simply zero (see the forward kernel)
+        const int fk = key0 + c * 32;
+        const int mode = (warp & 3) * 32 >= len ? CHUNK_EMPTY : chunk_mode(fk, len);  // warp-uniform
         float pd[32], ds[32];
         if (mode == CHUNK_EMPTY) {  // nothing to read or compute: P and dS of padded keys are zero
 #pragma unroll
