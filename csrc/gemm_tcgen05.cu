@@ -36,6 +36,7 @@ struct GemmParams {
     int M, N, K;
     int ldaux;
     const float* bias;
+    const int* row_lens;       // optional, rows come in sequences of BM: row r of tile m is padding when r >= row_lens[m]
     float* colsum;             // optional [N] fp32: += column sums of the bf16 output (bias gradient of the consumer)
     const __nv_bfloat16* aux;  // EPI_DGELU: pre-activation (same shape as D)
     int has_aux_out;           // EPI_BIAS_GELU: also store the pre-activation through tmAux
@@ -291,6 +292,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ GemmGroup<G> g) {
             const int out_row0 = (lu % p.split_k) * p.ws_row_stride + m_blk * BM;  // ws_row_stride == 0 unless workspace mode
             const int row = m_blk * BM + r_in_tile;
             const bool row_ok = row < p.M;
+            // Padded token rows (tile = one 128-token sequence): the GELU / dGELU arithmetic is skipped for them and
+            // zeros are written -- nothing downstream reads them and their gradients are exactly zero.  The epilogue
+            // is ALU-bound (two MUFU per element), and a third of the rows of a flow-sentence batch are padding.
+            const bool row_live = row_ok && (p.row_lens == nullptr || r_in_tile < __ldg(p.row_lens + m_blk));
             if (has_bias) {  // stage this tile's bias while the MMAs are still running
                 if (ep_tid < BN)
                     s_bias[acc_stage][ep_tid] = (n_base + ep_tid < p.N) ? __ldg(p.bias + n_base + ep_tid) : 0.f;
@@ -339,8 +344,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ GemmGroup<G> g) {
                                              pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
                                              pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
                         }
+                        if (row_live) {
 #pragma unroll
-                        for (int j = 0; j < 16; ++j) v[j] = gelu_erf(v[j]);
+                            for (int j = 0; j < 16; ++j) v[j] = gelu_erf(v[j]);
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) v[j] = 0.f;
+                        }
+                    } else if (p.epi == DCAD_EPI_DGELU && !row_live) {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) v[j] = 0.f;
                     } else if (p.epi == DCAD_EPI_DGELU) {
 #pragma unroll
                         for (int j = 0; j < 2; ++j) {
@@ -566,7 +579,8 @@ extern "C" void dcad_gemm_set_timing_buffer(void* dev_ptr) { g_gemm_timing = rei
 static int build_problem(GemmParams& p, CUtensorMap& tmA, CUtensorMap& tmB, CUtensorMap& tmD, CUtensorMap& tmAux,
                          const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major, int lda,
                          int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
-                         int out_fp32, int split_k, int ws_row_stride, int bn, int cg, float* colsum = nullptr) {
+                         int out_fp32, int split_k, int ws_row_stride, int bn, int cg, float* colsum = nullptr,
+                         const int* row_lens = nullptr) {
     if (M <= 0 || N <= 0 || K <= 0) return DCAD_ERR_BAD_SHAPE;
     if (colsum && out_fp32) return DCAD_ERR_BAD_ARGUMENT;
     if ((N % 8) || (ldd % 8) || (lda % 8) || (ldb % 8)) return DCAD_ERR_BAD_ALIGNMENT;
@@ -579,6 +593,7 @@ static int build_problem(GemmParams& p, CUtensorMap& tmA, CUtensorMap& tmB, CUte
     p.M = M; p.N = N; p.K = K; p.ldaux = ldaux > 0 ? ldaux : ldd;
     p.bias = bias;
     p.colsum = colsum;
+    p.row_lens = (cg == 1) ? row_lens : nullptr;  // (a CTA-pair tile spans two sequences: not supported there)
     p.aux = reinterpret_cast<const __nv_bfloat16*>(aux);
     p.has_aux_out = (epi == DCAD_EPI_BIAS_GELU && aux_out != nullptr) ? 1 : 0;
     p.epi = epi; p.out_fp32 = out_fp32;
@@ -620,12 +635,12 @@ static void parse_tile(int block_n, int N, int& bn, int& cg) {
 static int gemm_dispatch(const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major, int lda,
                          int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
                          int out_fp32, int split_k, int ws_row_stride, int block_n, int max_ctas, cudaStream_t s,
-                         float* colsum = nullptr) {
+                         float* colsum = nullptr, const int* row_lens = nullptr) {
     int bn, cg;
     parse_tile(block_n, N, bn, cg);
     GemmGroup<1> g;
     int rc = build_problem(g.p[0], g.tmA[0], g.tmB[0], g.tmD[0], g.tmAux[0], A, B, D, M, N, K, a_major, b_major, lda,
-                           ldb, ldd, bias, aux, aux_out, ldaux, epi, out_fp32, split_k, ws_row_stride, bn, cg, colsum);
+                           ldb, ldd, bias, aux, aux_out, ldaux, epi, out_fp32, split_k, ws_row_stride, bn, cg, colsum, row_lens);
     if (rc) return rc;
     g.n = 1;
     g.unit_begin[0] = 0;
@@ -707,9 +722,9 @@ extern "C" int dcad_gemm_bf16(const void* A, const void* B, void* D, int M, int 
 extern "C" int dcad_gemm_bf16_colsum(const void* A, const void* B, void* D, int M, int N, int K, int a_major,
                                      int b_major, int lda, int ldb, int ldd, const float* bias, const void* aux,
                                      void* aux_out, int ldaux, int epi, int block_n, int max_ctas, float* colsum,
-                                     void* stream) {
+                                     const int32_t* row_lens, void* stream) {
     return gemm_dispatch(A, B, D, M, N, K, a_major, b_major, lda, ldb, ldd, bias, aux, aux_out, ldaux, epi, 0, 1, 0,
-                         block_n, max_ctas, reinterpret_cast<cudaStream_t>(stream), colsum);
+                         block_n, max_ctas, reinterpret_cast<cudaStream_t>(stream), colsum, row_lens);
 }
 
 // ------------------------------------------------------------------------------------------------

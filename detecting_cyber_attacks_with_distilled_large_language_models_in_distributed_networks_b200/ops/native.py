@@ -96,7 +96,7 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("dcad_set_pdl", [I])
     sig("dcad_set_adam_blocks_per_sm", [I])
     sig("dcad_gemm_bf16", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, I, I, P])
-    sig("dcad_gemm_bf16_colsum", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, P, P])
+    sig("dcad_gemm_bf16_colsum", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, P, P, P])
     sig("dcad_gemm_bf16_group", [I, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, P])
     sig("dcad_gemm_splitk_workspace_bytes", [I, I, I], ctypes.c_size_t)
     sig("dcad_gemm_bf16_splitk", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, I, P, ctypes.c_size_t, P])
@@ -141,7 +141,7 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_major: i
               bias: Optional[torch.Tensor] = None, aux: Optional[torch.Tensor] = None,
               aux_out: Optional[torch.Tensor] = None, epi: int = EPI_NONE, split_k: int = 1,
               reduce_add: bool = False, block_n: int = 0, max_ctas: int = 0, colsum: Optional[torch.Tensor] = None,
-              stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
+              row_lens: Optional[torch.Tensor] = None, stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
     """``out[M,N] = epilogue(A·Bᵀ)`` on the tcgen05 kernel.  ``a``/``b`` are 2-D bf16 with unit inner stride.
 
     ``a`` is ``[M,K]`` (MAJOR_K) or ``[K,M]`` (MAJOR_MN); ``b`` is ``[N,K]`` (MAJOR_K) or ``[K,N]`` (MAJOR_MN).
@@ -177,11 +177,14 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_major: i
         ldaux = aux_out.stride(0)
     if bias is not None:
         assert bias.dtype == torch.float32 and bias.numel() == N
-    if colsum is not None:
-        assert not out_fp32 and split_k == 1 and colsum.dtype == torch.float32 and colsum.numel() == N
+    if colsum is not None or row_lens is not None:
+        assert not out_fp32 and split_k == 1
+        assert colsum is None or (colsum.dtype == torch.float32 and colsum.numel() == N)
+        assert row_lens is None or (row_lens.dtype == torch.int32 and row_lens.numel() * 128 >= M)
         rc = lib().dcad_gemm_bf16_colsum(a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K, a_major, b_major,
                                          a.stride(0), b.stride(0), out.stride(0), ptr(bias), ptr(aux), ptr(aux_out),
-                                         ldaux, epi, block_n, max_ctas, ptr(colsum), stream_ptr(stream))
+                                         ldaux, epi, block_n, max_ctas, ptr(colsum), ptr(row_lens),
+                                         stream_ptr(stream))
         check(rc, "dcad_gemm_bf16_colsum")
         return out
     rc = lib().dcad_gemm_bf16(a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K, a_major, b_major, a.stride(0),

@@ -63,10 +63,12 @@ int dcad_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, i
                    int out_fp32, int split_k, int block_n, int max_ctas, void* stream);
 
 /* dcad_gemm_bf16 with a bf16 output whose epilogue ALSO accumulates the column sums of D into colsum [N] (fp32,
- * atomics): the bias gradient of the Linear layer whose output gradient D is, without a second pass over D. */
+ * atomics): the bias gradient of the Linear layer whose output gradient D is, without a second pass over D.
+ * row_lens (may be NULL; rows must come in sequences of 128 = one tile): rows at or past row_lens[sequence] are
+ * padding -- the GELU / dGELU epilogues skip their arithmetic and store zeros. */
 int dcad_gemm_bf16_colsum(const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major, int lda,
                           int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
-                          int block_n, int max_ctas, float* colsum, void* stream);
+                          int block_n, int max_ctas, float* colsum, const int32_t* row_lens, void* stream);
 
 /* Up to DCAD_GEMM_GROUP_MAX independent fp32-output GEMMs (no epilogue) that share operand layouts and tile width, in
  * ONE persistent launch: one prologue and pipeline fill, work units of all problems spread over the SMs together.

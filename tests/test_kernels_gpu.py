@@ -135,6 +135,32 @@ def test_gemm_epilogue_column_sums(nv, bn):
     assert torch.equal(plain, out)
 
 
+def test_gemm_activation_epilogues_skip_padded_rows(nv):
+    """row_lens: rows past a sequence's length (tile = one 128-token sequence) get zeros instead of GELU / dGELU."""
+    torch.manual_seed(6)
+    B, N, K = 3, 512, 256
+    M = B * 128
+    lens = torch.tensor([128, 70, 5], device="cuda", dtype=torch.int32)
+    live = (torch.arange(128, device="cuda")[None, :] < lens[:, None]).reshape(M, 1)
+    a = torch.randn(M, K, device="cuda").bfloat16()
+    w = (torch.randn(N, K, device="cuda") * 0.05).bfloat16()
+    bias = torch.randn(N, device="cuda")
+    for bn in (192, 256):
+        out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+        pre = torch.empty_like(out)
+        ref_o, ref_p = torch.empty_like(out), torch.empty_like(out)
+        nv.gemm_bf16(a, w, out, bias=bias, aux_out=pre, epi=nv.EPI_BIAS_GELU, block_n=bn, row_lens=lens)
+        nv.gemm_bf16(a, w, ref_o, bias=bias, aux_out=ref_p, epi=nv.EPI_BIAS_GELU, block_n=bn)
+        assert torch.equal(out[live.expand_as(out)], ref_o[live.expand_as(out)])
+        assert torch.all(out[~live.expand_as(out)] == 0) and torch.equal(pre, ref_p)
+        d = torch.empty_like(out)
+        cs, cs_ref = torch.zeros(N, device="cuda"), torch.zeros(N, device="cuda")
+        nv.gemm_bf16(a, w, d, aux=pre, epi=nv.EPI_DGELU, block_n=bn, row_lens=lens, colsum=cs)
+        nv.gemm_bf16(a, w, ref_o, aux=pre, epi=nv.EPI_DGELU, block_n=bn, colsum=cs_ref)
+        assert torch.equal(d[live.expand_as(d)], ref_o[live.expand_as(d)]) and torch.all(d[~live.expand_as(d)] == 0)
+        assert _rel(cs, (ref_o.float() * live).sum(0)) < 1e-2
+
+
 def test_gemm_split_k_reduce_add(nv):
     torch.manual_seed(11)
     T, Nw, Kw = 2048, 768, 512      # dW[Nw, Kw] = dY[T, Nw]^T X[T, Kw]
