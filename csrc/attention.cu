@@ -462,11 +462,8 @@ extern "C" int dcad_attn_fwd(const void* qkv, void* ctx, float* lse2, const int3
     int rc = make_tensor_map_bf16_3d(&tm, qkv, 3 * HD, S, B, 3 * HD, static_cast<uint64_t>(S) * 3 * HD, AT_D, AT_S);
     if (rc) return rc;
     constexpr int SMEM = 5 * TILE_BYTES + 1024;
-    static bool attr = false;
-    if (!attr) {
-        DCAD_CUDA_TRY(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-        attr = true;
-    }
+    static DeviceOnce once;
+    DCAD_CUDA_TRY(ensure_dynamic_smem(attn_fwd_kernel, SMEM, once));
     const float ks = p_drop > 0.f ? 1.0f / (1.0f - p_drop) : 1.0f;
     return (int)launch_pdl(attn_fwd_kernel, dim3(B * H), dim3(AT_THREADS), SMEM, reinterpret_cast<cudaStream_t>(stream),
                            tm, reinterpret_cast<__nv_bfloat16*>(ctx), lse2, lens, S, H, 0.125f,
@@ -487,13 +484,8 @@ extern "C" int dcad_attn_bwd(const void* qkv, const void* ctx, const void* dctx,
     rc = make_tensor_map_bf16_3d(&td, dctx, HD, S, B, HD, static_cast<uint64_t>(S) * HD, AT_D, AT_S);
     if (rc) return rc;
     constexpr int SMEM = 7 * TILE_BYTES + 64;  // tiles + 3 mbarriers + the TMEM base word
-    static bool attr = false;
-    if (!attr) {
-        DCAD_CUDA_TRY(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-        DCAD_CUDA_TRY(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                           cudaSharedmemCarveoutMaxShared));
-        attr = true;
-    }
+    static DeviceOnce once;
+    DCAD_CUDA_TRY(ensure_dynamic_smem(attn_bwd_kernel, SMEM, once, /*max_carveout=*/true));
     const float ks = p_drop > 0.f ? 1.0f / (1.0f - p_drop) : 1.0f;
     return (int)launch_pdl(attn_bwd_kernel, dim3(B * H), dim3(AT_THREADS), SMEM, reinterpret_cast<cudaStream_t>(stream),
                            tq, td, reinterpret_cast<const __nv_bfloat16*>(ctx),

@@ -182,11 +182,8 @@ static int launch_cls_train(const void* h, int sample_stride, const float* W, co
                             uint32_t stream_id, float* loss_accum, float* logits, float* dW, float* db, void* dcls,
                             cudaStream_t s) {
     constexpr int SMEM = (CLS_TRAIN_THREADS / 32) * 2 * NV * 256 * (int)sizeof(float);
-    static bool attr = false;
-    if (!attr) {
-        DCAD_CUDA_TRY(cudaFuncSetAttribute(cls_head_train_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-        attr = true;
-    }
+    static DeviceOnce once;
+    DCAD_CUDA_TRY(ensure_dynamic_smem(cls_head_train_kernel<NV>, SMEM, once));
     return (int)launch_pdl(cls_head_train_kernel<NV>, dim3(1), dim3(CLS_TRAIN_THREADS), SMEM, s,
                            reinterpret_cast<const __nv_bfloat16*>(h), sample_stride, W, bias, labels, batch, th, ks, rng,
                            stream_id, loss_accum, logits, dW, db, reinterpret_cast<__nv_bfloat16*>(dcls));

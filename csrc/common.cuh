@@ -9,6 +9,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 #ifndef DCAD_WATCHDOG
 #define DCAD_WATCHDOG 1
 #endif
@@ -23,6 +25,30 @@ namespace dcad {
         cudaError_t _e = (expr);                             \
         if (_e != cudaSuccess) return (int)_e;               \
     } while (0)
+
+// cudaFuncSetAttribute (and the SM count) belong to ONE device: a process that drives several GPUs through the C ABI
+// must opt every kernel in on each of them.  DeviceOnce remembers, per call site, which device ordinals are done.
+struct DeviceOnce {
+    std::atomic<unsigned long long> mask[2] = {};  // 128 device ordinals
+    bool test(int dev) const { return (mask[(dev >> 6) & 1].load(std::memory_order_acquire) >> (dev & 63)) & 1ull; }
+    void set(int dev) { mask[(dev >> 6) & 1].fetch_or(1ull << (dev & 63), std::memory_order_release); }
+};
+// Raises the dynamic shared-memory limit of `kern` on the current device the first time it is launched there.
+template <typename Kern>
+inline cudaError_t ensure_dynamic_smem(Kern kern, int bytes, DeviceOnce& once, bool max_carveout = false) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev >= 0 && dev < 128 && once.test(dev)) return cudaSuccess;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) return e;
+    if (max_carveout) {
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        if (e != cudaSuccess) return e;
+    }
+    if (dev >= 0 && dev < 128) once.set(dev);
+    return cudaSuccess;
+}
 
 // ----------------------------------------------------------------------------------------------
 // programmatic dependent launch (PDL): every kernel of the training step is launched with

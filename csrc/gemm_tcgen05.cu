@@ -539,12 +539,16 @@ int make_tensor_map_bf16_3d(CUtensorMap* out, const void* ptr, uint64_t d0, uint
     return r == CUDA_SUCCESS ? 0 : DCAD_ERR_TENSOR_MAP;
 }
 
+// SM count of the CURRENT device (cached per device ordinal: one process may drive several GPUs)
 static int num_sms() {
-    static int n = 0;
+    static std::atomic<int> cache[128] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const bool cacheable = dev >= 0 && dev < 128;
+    int n = cacheable ? cache[dev].load(std::memory_order_relaxed) : 0;
     if (n == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (cacheable) cache[dev].store(n, std::memory_order_relaxed);
     }
     return n;
 }
@@ -553,11 +557,8 @@ template <int BN, int A_MAJOR, int B_MAJOR, int CG, int G>
 static int launch_gemm(const GemmGroup<G>& g, int max_ctas, cudaStream_t stream) {
     using Cfg = GemmCfg<BN, CG>;
     auto kern = gemm_bf16_tcgen05_kernel<BN, A_MAJOR, B_MAJOR, CG, G>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        DCAD_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-        attr_set = true;
-    }
+    static DeviceOnce once;
+    DCAD_CUDA_TRY(ensure_dynamic_smem(kern, Cfg::SMEM_BYTES, once));
     int grid = g.unit_begin[g.n];  // work units = CTAs (CG 1) or CTA pairs (CG 2)
     int cap = (max_ctas > 0 ? max_ctas : num_sms()) / CG;
     if (cap < 1) cap = 1;

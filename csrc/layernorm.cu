@@ -453,12 +453,8 @@ static int add_ln_bwd_run(const void* dy1, PartialIn dy1_part, const void* dy2, 
     const int grid = (rows + LN_WARPS - 1) / LN_WARPS;
     const int smem = LN_WARPS * 3 * cols * (int)sizeof(float);
     DCAD_NV_DISPATCH(cols, {
-        static bool attr = false;
-        if (!attr) {
-            DCAD_CUDA_TRY(cudaFuncSetAttribute(add_ln_bwd_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                               LN_WARPS * 3 * NV * 256 * (int)sizeof(float)));
-            attr = true;
-        }
+        static DeviceOnce once;
+        DCAD_CUDA_TRY(ensure_dynamic_smem(add_ln_bwd_kernel<NV>, LN_WARPS * 3 * NV * 256 * (int)sizeof(float), once));
         return (int)launch_pdl(
             add_ln_bwd_kernel<NV>, dim3(grid), dim3(LN_WARPS * 32), smem, s,
             reinterpret_cast<const __nv_bfloat16*>(dy1), dy1_part, reinterpret_cast<const __nv_bfloat16*>(dy2),
@@ -519,12 +515,8 @@ extern "C" int dcad_embed_ln_bwd(const void* dy1, const void* dy2, const int32_t
     const int grid = (rows + LN_WARPS - 1) / LN_WARPS;
     const int smem = LN_WARPS * 2 * cols * (int)sizeof(float);
     DCAD_NV_DISPATCH(cols, {
-        static bool attr = false;
-        if (!attr) {
-            DCAD_CUDA_TRY(cudaFuncSetAttribute(embed_ln_bwd_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                               LN_WARPS * 2 * NV * 256 * (int)sizeof(float)));
-            attr = true;
-        }
+        static DeviceOnce once;
+        DCAD_CUDA_TRY(ensure_dynamic_smem(embed_ln_bwd_kernel<NV>, LN_WARPS * 2 * NV * 256 * (int)sizeof(float), once));
         return (int)launch_pdl(
             embed_ln_bwd_kernel<NV>, dim3(grid), dim3(LN_WARPS * 32), smem, s,
             reinterpret_cast<const __nv_bfloat16*>(dy1), reinterpret_cast<const __nv_bfloat16*>(dy2), ids, word, pos,

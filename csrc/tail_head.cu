@@ -267,12 +267,8 @@ extern "C" int dcad_tail_head(const float* a_partials, int splits, int64_t slice
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
 #define DCAD_TH_CASE(NV_)                                                                                          \
     case NV_: {                                                                                                    \
-        static bool attr = false;                                                                                  \
-        if (!attr) {                                                                                               \
-            DCAD_CUDA_TRY(cudaFuncSetAttribute(tail_head_kernel<NV_>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                               200 * 1024));                                                       \
-            attr = true;                                                                                           \
-        }                                                                                                          \
+        static DeviceOnce once;                                                                                    \
+        DCAD_CUDA_TRY(ensure_dynamic_smem(tail_head_kernel<NV_>, 200 * 1024, once));                               \
         return (int)launch_pdl(tail_head_kernel<NV_>, dim3(1), dim3(TH_THREADS), smem, s, p);                      \
     }
     switch (cols / 256) {
