@@ -14,7 +14,8 @@
 //                       single-process tests)
 //
 // Cross-GPU handshake: per-rank signal pad in peer memory, flags written with st.release.sys and polled with
-// ld.acquire.sys; bounded spins set an error flag instead of hanging.
+// ld.acquire.sys; bounded spins set an error flag instead of hanging, and a rank whose start handshake timed out
+// leaves every arena untouched.  The host reads the flag after the round and clears it (dcad users: pad word 33).
 #include <string.h>
 
 #include "common.cuh"
@@ -53,6 +54,45 @@ __device__ __forceinline__ bool spin_until_ge(const uint32_t* p, uint32_t target
         __nanosleep(64);
     }
     return false;
+}
+
+// Start handshake of a round (all threads of every block call it).  Block 0 publishes this rank's ready flag to every
+// peer; every block waits until every peer's flag has reached `epoch`.  Returns false -- for the whole block, after
+// raising the error word -- when a peer did not show up within the bounded spin.
+__device__ __forceinline__ bool start_barrier(const FedArgs& a, uint32_t* my_pad, int rank, int nr, uint32_t epoch) {
+    __shared__ int s_timed_out;
+    if (threadIdx.x == 0) s_timed_out = 0;
+    __syncthreads();
+    if (blockIdx.x == 0 && threadIdx.x < nr) st_release_sys(a.pad[threadIdx.x] + PAD_READY + rank, epoch);
+    if (threadIdx.x < nr) {
+        if (!spin_until_ge(my_pad + PAD_READY + threadIdx.x, epoch)) {
+            atomicExch(my_pad + PAD_ERROR, 1u);
+            s_timed_out = 1;
+        }
+    }
+    __syncthreads();
+    return s_timed_out == 0;
+}
+
+// End handshake: the last block of this rank to finish tells every peer that this rank's stores are visible, then
+// waits for theirs.  Every block takes part in the block counter (also one that skipped its work after a time-out, so
+// the counter is back at zero for the next round), but a rank whose error word is set does not signal completion:
+// its peers then time out too and every client of the round reports the failure instead of trusting a partial result.
+__device__ __forceinline__ void end_barrier(const FedArgs& a, uint32_t* my_pad, int rank, int nr, uint32_t epoch) {
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const uint32_t prev = atomicAdd(my_pad + PAD_COUNTER, 1u);
+        if (prev == gridDim.x - 1) {
+            my_pad[PAD_COUNTER] = 0;
+            __threadfence_system();
+            if (atomicAdd(my_pad + PAD_ERROR, 0u) == 0u) {
+                for (int k = 0; k < nr; ++k) st_release_sys(a.pad[k] + PAD_DONE + rank, epoch);
+                for (int k = 0; k < nr; ++k)
+                    if (!spin_until_ge(my_pad + PAD_DONE + k, epoch)) atomicExch(my_pad + PAD_ERROR, 1u);
+            }
+        }
+    }
 }
 
 template <bool IN_BF16>
@@ -180,12 +220,10 @@ fedavg_p2p_kernel(const FedArgs a, int rank, int n, int64_t num_vecs, int mode, 
     constexpr int E = VecIO<IN_BF16>::ELEMS;
     const int nr = a.n_dst;
     uint32_t* my_pad = a.pad[rank];
-    // start barrier: every peer's arena is final (their launch is stream-ordered after their local training)
-    if (blockIdx.x == 0 && threadIdx.x < nr) st_release_sys(a.pad[threadIdx.x] + PAD_READY + rank, epoch);
-    if (threadIdx.x < nr) {
-        if (!spin_until_ge(my_pad + PAD_READY + threadIdx.x, epoch)) my_pad[PAD_ERROR] = 1;
-    }
-    __syncthreads();
+    // start barrier: every peer's arena is final (their launch is stream-ordered after their local training).  A peer
+    // that never arrives (dead client, hung process) must not cost the others their models: the block that times out
+    // raises the error word and NO block of this rank that saw the time-out reads or writes a single parameter.
+    if (!start_barrier(a, my_pad, rank, nr, epoch)) num_vecs = 0;
 
     int64_t lo = 0, hi = num_vecs;
     if (mode == DCAD_FED_TWO_SHOT) {
@@ -217,16 +255,7 @@ fedavg_p2p_kernel(const FedArgs a, int rank, int n, int64_t num_vecs, int mode, 
     // end barrier: the last block of this rank tells every peer its pushes are visible, then waits for theirs
     __threadfence_system();
     __syncthreads();
-    if (threadIdx.x == 0) {
-        const uint32_t prev = atomicAdd(my_pad + PAD_COUNTER, 1u);
-        if (prev == gridDim.x - 1) {
-            my_pad[PAD_COUNTER] = 0;
-            __threadfence_system();
-            for (int k = 0; k < nr; ++k) st_release_sys(a.pad[k] + PAD_DONE + rank, epoch);
-            for (int k = 0; k < nr; ++k)
-                if (!spin_until_ge(my_pad + PAD_DONE + k, epoch)) my_pad[PAD_ERROR] = 1;
-        }
-    }
+    end_barrier(a, my_pad, rank, nr, epoch);
 }
 
 // ---- NVLS: in-switch reduction over a multicast mapping of all clients' arenas ----
@@ -253,11 +282,7 @@ __global__ void __launch_bounds__(512)
 fedavg_nvls_kernel(const FedArgs a, float* mc_arena, __nv_bfloat16* mc_mirror, int rank, int n, int64_t num_vecs,
                    int64_t bf16_begin, int64_t bf16_end, uint32_t epoch) {
     uint32_t* my_pad = a.pad[rank];
-    if (blockIdx.x == 0 && threadIdx.x < n) st_release_sys(a.pad[threadIdx.x] + PAD_READY + rank, epoch);
-    if (threadIdx.x < n) {
-        if (!spin_until_ge(my_pad + PAD_READY + threadIdx.x, epoch)) my_pad[PAD_ERROR] = 1;
-    }
-    __syncthreads();
+    if (!start_barrier(a, my_pad, rank, n, epoch)) num_vecs = 0;  // (see fedavg_p2p_kernel)
     const int64_t lo = num_vecs * rank / n, hi = num_vecs * (rank + 1) / n;
     const float inv_n = 1.0f / static_cast<float>(n);
     const float nf = static_cast<float>(n);
@@ -282,16 +307,7 @@ fedavg_nvls_kernel(const FedArgs a, float* mc_arena, __nv_bfloat16* mc_mirror, i
     (void)inv_n;
     __threadfence_system();
     __syncthreads();
-    if (threadIdx.x == 0) {
-        const uint32_t prev = atomicAdd(my_pad + PAD_COUNTER, 1u);
-        if (prev == gridDim.x - 1) {
-            my_pad[PAD_COUNTER] = 0;
-            __threadfence_system();
-            for (int k = 0; k < n; ++k) st_release_sys(a.pad[k] + PAD_DONE + rank, epoch);
-            for (int k = 0; k < n; ++k)
-                if (!spin_until_ge(my_pad + PAD_DONE + k, epoch)) my_pad[PAD_ERROR] = 1;
-        }
-    }
+    end_barrier(a, my_pad, rank, n, epoch);
 }
 
 static int fill_args(FedArgs& fa, const void* const* arenas, const void* const* outs, const void* const* mirrors,

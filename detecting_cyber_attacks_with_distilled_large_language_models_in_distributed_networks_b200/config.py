@@ -46,6 +46,8 @@ class FedConfig:
     port_send: int = 12346
     timeout: float = 300.0
     accept_timeout: Optional[float] = None
+    round_timeout: Optional[float] = None  # deadline of a server round's collect / distribute phase (default 5 x timeout)
+    allow_remote: bool = False         # socket server: bind a non-loopback --host (the wire protocol is unauthenticated)
     max_retries: int = 5
     gzip_level: int = 0
     min_clients: Optional[int] = None  # quorum for the socket server (default: all)

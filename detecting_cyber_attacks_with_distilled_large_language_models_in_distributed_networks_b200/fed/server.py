@@ -14,5 +14,5 @@ def run_server(cfg: FedConfig) -> None:
     srv = FedServer(num_clients=cfg.num_clients, host=cfg.host, port_recv=cfg.port_recv, port_send=cfg.port_send,
                     timeout=cfg.timeout, accept_timeout=cfg.accept_timeout, gzip_level=cfg.gzip_level,
                     save_path=os.path.join(cfg.out_dir, "ddos_distilbert_model.pth"), min_clients=cfg.min_clients,
-                    log=log)
+                    log=log, round_timeout=cfg.round_timeout, allow_remote=cfg.allow_remote)
     srv.serve(cfg.rounds)

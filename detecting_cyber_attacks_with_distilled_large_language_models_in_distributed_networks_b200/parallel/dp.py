@@ -200,8 +200,14 @@ class DPGroup:
         torch.cuda.synchronize()
         dist.barrier(group=self._dist_group)
 
-    def error_flag(self) -> int:
-        return int(self.pad_tensor()[33].item())
+    def error_flag(self, clear: bool = True) -> int:
+        """1 when a bounded handshake wait of a kernel on this rank expired since the flag was last cleared.  Reading
+        it reports the failure ONCE: the word is reset so that later rounds are judged on their own."""
+        pad = self.pad_tensor()
+        v = int(pad[33].item())
+        if v and clear:
+            pad[33] = 0
+        return v
 
     def close(self) -> None:
         for b in self._opened:

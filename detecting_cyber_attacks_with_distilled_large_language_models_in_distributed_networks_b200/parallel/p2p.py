@@ -89,8 +89,14 @@ class PeerGroup:
                       weights=weights, in_bf16=self.arena_dtype == torch.bfloat16, mode=mode, bf16_begin=0,
                       bf16_end=self.mirror_elems if with_mirror else 0, max_ctas=max_ctas, stream=stream)
 
-    def error_flag(self) -> int:
-        return int(self.pad_tensor()[33].item())
+    def error_flag(self, clear: bool = True) -> int:
+        """1 when a bounded handshake wait of a kernel on this rank expired since the flag was last cleared.  Reading
+        it reports the failure ONCE: the word is reset so that later rounds are judged on their own."""
+        pad = self.pad_tensor()
+        v = int(pad[33].item())
+        if v and clear:
+            pad[33] = 0
+        return v
 
     def close(self) -> None:
         for b in self._opened:
@@ -162,8 +168,14 @@ class SymmPeerGroup:
                           weights=weights, mode=TWO_SHOT, bf16_begin=0,
                           bf16_end=self.mirror_elems if with_mirror else 0, max_ctas=max_ctas, stream=stream)
 
-    def error_flag(self) -> int:
-        return int(self.pad_tensor()[33].item())
+    def error_flag(self, clear: bool = True) -> int:
+        """1 when a bounded handshake wait of a kernel on this rank expired since the flag was last cleared.  Reading
+        it reports the failure ONCE: the word is reset so that later rounds are judged on their own."""
+        pad = self.pad_tensor()
+        v = int(pad[33].item())
+        if v and clear:
+            pad[33] = 0
+        return v
 
     def close(self) -> None:
         self._hdl = None

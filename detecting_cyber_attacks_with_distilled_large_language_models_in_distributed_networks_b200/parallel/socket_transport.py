@@ -14,7 +14,11 @@ kernel (``parallel/p2p.py``); sockets remain for clients on other hosts.
 Deliberate fixes relative to the reference: Q1 no connect-then-close readiness probes (the real
 connection is retried instead) and the server tolerates such probes from reference clients without burning a global
 retry budget; Q2 ``send_model`` returns the ACK result; Q5 the accept timeout is configurable (default: none);
-Q13 tensors are always staged through host memory before pickling; the receive buffer is a pre-sized ``bytearray``
+Q13 tensors are always staged through host memory before pickling; payloads are decoded with an allow-list unpickler
+(``OrderedDict`` + torch's tensor rebuild functions only: the reference's bare ``pickle.loads`` lets any peer that can
+reach the port run code on the server and, through the download, on every client), are refused beyond
+``MAX_PAYLOAD_BYTES``, and binding a non-loopback address has to be asked for (``allow_remote``); every round has a
+deadline (``round_timeout``) so a client that never shows up cannot stall a multi-round server; the receive buffer is a pre-sized ``bytearray``
 filled with ``recv_into`` instead of quadratic ``bytes +=``; the gzip level is configurable and defaults to 0 (stored:
 still a valid gzip stream for the reference's decoder) because fp32 weights compress by only 7.5 % while level 9
 costs ~11 s per 265 MB hop on the published machine and ~30 s on this one.
@@ -41,6 +45,10 @@ CHUNK_SEND = 1024 * 1024
 CHUNK_RECV = 4 * 1024 * 1024
 SOCK_BUF = 8 * 1024 * 1024
 ACK = b"RECEIVED"
+# DistilBERT-base DDoSClassifier pickles to 265.5 MB; 2 GiB leaves room for larger encoders while an
+# unauthenticated peer can no longer make the receiver allocate the reference framing's full 16 GiB
+MAX_PAYLOAD_BYTES = 2 << 30
+LOOPBACK_HOSTS = ("localhost", "127.0.0.1", "::1")
 
 
 # ---------------------------------------------------------------------------------------------- serialisation
@@ -61,9 +69,39 @@ def compress_data(obj, level: int = 0) -> bytes:
     return buf.getvalue()
 
 
-def decompress_data(data: bytes):
+def _safe_storage_from_bytes(b: bytes):
+    """Stand-in for ``torch.storage._load_from_bytes`` (which is ``torch.load(..., weights_only=False)``, i.e. a second,
+    unrestricted pickle inside the first): the nested storage archive is decoded by torch's own weights-only loader."""
+    return torch.load(io.BytesIO(b), weights_only=True)
+
+
+class _StateDictUnpickler(pickle.Unpickler):
+    """Decodes exactly what ``pickle.dumps(model.state_dict())`` emits (reference client1.py:232, server.py:25) and
+    nothing else: an ``OrderedDict`` (with its ``_metadata``) of tensors / parameters."""
+
+    _ALLOWED = {
+        ("collections", "OrderedDict"): OrderedDict,
+        ("torch._utils", "_rebuild_tensor_v2"): torch._utils._rebuild_tensor_v2,
+        ("torch._utils", "_rebuild_tensor"): torch._utils._rebuild_tensor,
+        ("torch._utils", "_rebuild_parameter"): torch._utils._rebuild_parameter,
+        ("torch.storage", "_load_from_bytes"): _safe_storage_from_bytes,
+        ("torch", "Size"): torch.Size,
+    }
+
+    def find_class(self, module: str, name: str):
+        try:
+            return self._ALLOWED[(module, name)]
+        except KeyError:
+            raise pickle.UnpicklingError(f"refusing to unpickle {module}.{name}: not part of a state_dict") from None
+
+
+def decompress_data(data: bytes, trusted: bool = False):
+    """gunzip + unpickle a state_dict.  ``trusted=True`` is the reference's bare ``pickle.loads`` (local files only)."""
     with gzip.GzipFile(fileobj=io.BytesIO(data), mode="rb") as f:
-        return pickle.loads(f.read())
+        raw = f.read()
+    if trusted:
+        return pickle.loads(raw)
+    return _StateDictUnpickler(io.BytesIO(raw)).load()
 
 
 # ---------------------------------------------------------------------------------------------- framing
@@ -87,7 +125,7 @@ def send_chunked_data(sock: socket.socket, data: bytes, chunk_size: int = CHUNK_
     return ack == ACK
 
 
-def receive_chunked_data(sock: socket.socket, max_bytes: int = 1 << 34) -> bytes:
+def receive_chunked_data(sock: socket.socket, max_bytes: int = MAX_PAYLOAD_BYTES) -> bytes:
     header = bytearray()
     while not header.endswith(b"\n"):
         b = sock.recv(1)
@@ -193,7 +231,16 @@ class FedServer:
                  port_send: int = PORT_SEND, timeout: float = TIMEOUT, accept_timeout: Optional[float] = None,
                  gzip_level: int = 0, aggregate: Optional[Callable[[List[dict]], dict]] = None,
                  save_path: Optional[str] = "ddos_distilbert_model.pth", send_failure_budget: int = 5,
-                 min_clients: Optional[int] = None, log: Optional[EventLog] = None):
+                 min_clients: Optional[int] = None, log: Optional[EventLog] = None,
+                 round_timeout: Optional[float] = None, allow_remote: bool = False,
+                 max_payload_bytes: int = MAX_PAYLOAD_BYTES):
+        if host not in LOOPBACK_HOSTS and not allow_remote:
+            raise ValueError(f"refusing to bind {host!r}: the wire protocol is unauthenticated; pass allow_remote=True "
+                             f"(--allow-remote) to serve other hosts on a network you trust")
+        # Deadline of each phase of a round (collect, distribute).  Default: the reference's bound -- its 300 s socket
+        # timeout times its five attempts (server.py:10,93) -- instead of waiting for ever.
+        self.round_timeout = timeout * 5 if round_timeout is None else round_timeout
+        self.max_payload_bytes = max_payload_bytes
         self.num_clients, self.host = num_clients, host
         self.port_recv, self.port_send = port_recv, port_send
         self.timeout, self.accept_timeout = timeout, accept_timeout
@@ -215,7 +262,7 @@ class FedServer:
     def _listen(self, port: int) -> socket.socket:
         s = socket.socket(socket.AF_INET, socket.SOCK_STREAM)
         s.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1)
-        s.settimeout(self.accept_timeout)
+        s.settimeout(self.accept_timeout if self.accept_timeout is not None else 1.0)
         s.bind((self.host, port))
         s.listen(max(self.num_clients, 8))
         return s
@@ -238,7 +285,7 @@ class FedServer:
     def _handle_upload(self, conn: socket.socket, addr, slot: int, slots: List[Optional[dict]]) -> None:
         try:
             conn.settimeout(self.timeout)
-            data = receive_chunked_data(conn)
+            data = receive_chunked_data(conn, self.max_payload_bytes)
             model = decompress_data(data)
             with self._lock:
                 slots[slot] = model
@@ -252,8 +299,10 @@ class FedServer:
         assert self._recv_sock is not None
         slots: List[Optional[dict]] = []
         threads = []
-        # keep accepting until num_clients uploads SUCCEEDED (a probe / broken upload does not consume a slot)
-        deadline = None if self.accept_timeout is None else time.time() + self.accept_timeout
+        # keep accepting until num_clients uploads SUCCEEDED (a probe / broken upload does not consume a slot) or the
+        # round's deadline passes; the quorum (min_clients) is then applied to whoever arrived
+        limit = self.round_timeout if self.accept_timeout is None else min(self.accept_timeout, self.round_timeout)
+        deadline = time.time() + limit
         while True:
             with self._lock:
                 done = sum(1 for m in slots if m is not None)
@@ -263,20 +312,24 @@ class FedServer:
             if done + pending >= self.num_clients:
                 for t in threads:
                     t.join(timeout=0.05)
+                if time.time() > deadline + self.timeout:  # an accepted upload that never completes
+                    break
                 continue
+            if time.time() > deadline:
+                self.log.say(f"collect deadline ({limit:.0f} s) passed with {done} of {self.num_clients} uploads")
+                break
             try:
                 conn, addr = self._recv_sock.accept()
             except socket.timeout:
-                if deadline is not None and time.time() > deadline:
-                    break
                 continue
             slots.append(None)
             t = threading.Thread(target=self._handle_upload, args=(conn, addr, len(slots) - 1, slots), daemon=True)
             t.start()
             threads.append(t)
         for t in threads:
-            t.join()
-        self.received = [m for m in slots if m is not None]
+            t.join(timeout=self.timeout)
+        with self._lock:
+            self.received = [m for m in slots if m is not None]
         return self.received
 
     def aggregate_models(self) -> Optional[dict]:
@@ -311,6 +364,8 @@ class FedServer:
             with self._lock:
                 results.append(ok)
 
+        limit = self.round_timeout if self.accept_timeout is None else min(self.accept_timeout, self.round_timeout)
+        deadline = time.time() + limit
         while True:
             with self._lock:
                 served = sum(1 for r in results if r)
@@ -321,12 +376,13 @@ class FedServer:
             if served + alive >= n_targets:
                 time.sleep(0.01)
                 continue
+            if time.time() > deadline:  # a client that uploaded but never came back for the result
+                self.log.say(f"distribute deadline ({limit:.0f} s) passed with {served} of {n_targets} downloads")
+                break
             try:
-                self._send_sock.settimeout(1.0 if self.accept_timeout is None else self.accept_timeout)
+                self._send_sock.settimeout(min(1.0, limit))
                 conn, _ = self._send_sock.accept()
             except socket.timeout:
-                if self.accept_timeout is not None:
-                    break
                 continue
             t = threading.Thread(target=serve, args=(conn,), daemon=True)  # downloads are served concurrently
             t.start()

@@ -147,3 +147,91 @@ def test_quorum_round_with_missing_client():
     t.join(30)
     srv.close()
     assert agg is not None and all(torch.equal(agg[k], sd[k]) for k in sd)
+
+
+def test_untrusted_payloads_are_refused():
+    """The wire decoder accepts a pickled state_dict and nothing else: a payload that names any other global (the
+    classic ``os.system`` reduce) is rejected before anything runs, also when it hides inside a tensor's storage."""
+    import gzip
+    import io
+    import os
+    import pickle
+
+    from detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200.parallel import (
+        socket_transport as st)
+
+    class Evil:
+        def __reduce__(self):
+            return (os.system, ("echo pwned > /tmp/dcad_pwned",))
+
+    def gz(b):
+        buf = io.BytesIO()
+        with gzip.GzipFile(fileobj=buf, mode="wb", compresslevel=0) as f:
+            f.write(b)
+        return buf.getvalue()
+
+    if os.path.exists("/tmp/dcad_pwned"):
+        os.remove("/tmp/dcad_pwned")
+    with pytest.raises(pickle.UnpicklingError):
+        st.decompress_data(gz(pickle.dumps(Evil())))
+    # nested: a "storage" whose bytes are themselves a malicious pickle (what torch.storage._load_from_bytes would run)
+    nested = pickle.dumps(Evil())
+
+    class FakeStorage:
+        def __reduce__(self):
+            import torch.storage
+            return (torch.storage._load_from_bytes, (nested,))
+
+    with pytest.raises(Exception):
+        st.decompress_data(gz(pickle.dumps(FakeStorage())))
+    assert not os.path.exists("/tmp/dcad_pwned")
+    # the legitimate payload (tensors of several dtypes, a Parameter, the OrderedDict's _metadata) still round-trips
+    from collections import OrderedDict
+    sd = OrderedDict(a=torch.randn(3, 4), b=torch.arange(5), c=torch.randn(2).bfloat16(),
+                     p=torch.nn.Parameter(torch.randn(2)))
+    sd._metadata = OrderedDict({"": {"version": 1}})
+    back = st.decompress_data(st.compress_data(sd))
+    assert list(back) == list(sd) and back._metadata == sd._metadata
+    assert all(torch.equal(back[k], sd[k]) for k in sd)
+
+
+def test_server_refuses_remote_bind_and_oversized_payloads():
+    import socket as pysocket
+
+    from detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200.parallel import (
+        socket_transport as st)
+
+    with pytest.raises(ValueError):
+        st.FedServer(num_clients=1, host="0.0.0.0", save_path=None)
+    st.FedServer(num_clients=1, host="0.0.0.0", save_path=None, allow_remote=True)  # explicit opt-in is accepted
+    a, b = pysocket.socketpair()
+    try:
+        a.sendall(b"99999999999\n")
+        with pytest.raises(ValueError):
+            st.receive_chunked_data(b)
+    finally:
+        a.close()
+        b.close()
+
+
+def test_round_deadline_applies_quorum(tmp_path):
+    """A multi-round server whose second client never shows up: the collect phase ends at the round deadline, the
+    quorum (min_clients=1) is applied and the round completes with the client that did come."""
+    import threading
+
+    from detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200.parallel import (
+        socket_transport as st)
+
+    pr, ps = _free_port(), _free_port()
+    srv = st.FedServer(num_clients=2, port_recv=pr, port_send=ps, timeout=5, round_timeout=1.5, min_clients=1,
+                       save_path=None, aggregate=lambda sds: sds[0])
+    srv.open()
+    out = {}
+    t = threading.Thread(target=lambda: out.setdefault("agg", srv.run_round()), daemon=True)
+    t.start()
+    sd = {"w": torch.ones(4)}
+    assert st.send_model(sd, port=pr, timeout=5)
+    got = st.receive_aggregated_model(port=ps, timeout=10, max_retries=2)
+    t.join(timeout=20)
+    srv.close()
+    assert not t.is_alive() and got is not None and torch.equal(got["w"], sd["w"])
