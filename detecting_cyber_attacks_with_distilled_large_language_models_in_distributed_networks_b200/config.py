@@ -33,7 +33,8 @@ class FedConfig:
     data_fraction: float = 0.1
     synthetic_rows: int = 0            # >0: generate a synthetic CICIDS-shaped CSV when data_path is missing
     disjoint_shards: bool = False      # extension: clients sample disjoint interleaved shards
-    model_dir: str = "./distilbert-base-uncased"   # vocab.txt (+ optional weights) if present; synthetic vocab otherwise
+    model_dir: str = "./distilbert-base-uncased"   # vocab.txt and model.safetensors / pytorch_model.bin if present
+    pretrained: bool = True            # start from the encoder weights in model_dir (random init, logged, if absent)
     # model size overrides (tests / plumbing tier); None = DistilBERT-base
     n_layers: Optional[int] = None
     dim: Optional[int] = None

@@ -70,6 +70,11 @@ def run_client(cfg: FedConfig, transport: Optional[Transport] = None, backend=No
         kw = dict(dims=dims, batch=cfg.batch_size, seq=cfg.max_len, lr=cfg.lr, seed=cfg.resolved_seed())
         kw.update(backend_kwargs or {})
         backend = make_backend(cfg.backend, **kw)
+    if cfg.pretrained and not os.path.exists(model_path):
+        # reference client1.py:55-56: the encoder starts from the pretrained DistilBERT in model_dir (when present)
+        from ..models.pretrained import load_pretrained_encoder
+
+        load_pretrained_encoder(backend, cfg.model_dir, log)
     if os.path.exists(model_path):  # reference client1.py:375-377: continue from the last (aggregated) weights
         log.say(f"loading pre-trained model from {model_path}")
         backend.load_state_dict(torch.load(model_path, map_location="cpu"))

@@ -75,3 +75,35 @@ def test_arena_roundtrip_and_reference_checkpoint_format(tmp_path):
     assert torch.equal(a.flat, b.flat)
     with pytest.raises(KeyError):
         b.load_state_dict({"bogus": torch.zeros(1)})
+
+
+def test_pretrained_encoder_loader(tmp_path):
+    """An HF DistilBertModel saved with save_pretrained() (what ./distilbert-base-uncased is for the reference,
+    client1.py:55-56) lands in the encoder of the DDoSClassifier; the head keeps its own initialisation; a directory
+    without weights leaves the model alone."""
+    from transformers import DistilBertConfig, DistilBertModel
+
+    from detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200.models import (
+        arena as A, distilbert as D, pretrained as P)
+
+    dims = A.ModelDims(vocab_size=120, max_position=32, dim=64, n_heads=2, hidden_dim=128, n_layers=2)
+    hf = DistilBertModel(DistilBertConfig(vocab_size=120, max_position_embeddings=32, dim=64, n_heads=2,
+                                          hidden_dim=128, n_layers=2))
+    for ext_dir, safe in (("st", True), ("bin", False)):
+        d = tmp_path / ext_dir
+        hf.save_pretrained(d, safe_serialization=safe)
+        model = D.DDoSClassifier(dims)
+        head_before = model.state_dict()["classifier.weight"].clone()
+        said = []
+        n = P.load_pretrained_encoder(model, str(d), type("L", (), {"say": staticmethod(said.append)})())
+        sd = model.state_dict()
+        assert n == len(hf.state_dict()) == len(sd) - 2, said
+        for k, v in hf.state_dict().items():
+            assert torch.equal(sd["distilbert." + k], v), k
+        assert torch.equal(sd["classifier.weight"], head_before)
+    empty = tmp_path / "empty"
+    empty.mkdir()
+    model = D.DDoSClassifier(dims)
+    before = {k: v.clone() for k, v in model.state_dict().items()}
+    assert P.load_pretrained_encoder(model, str(empty)) == 0
+    assert all(torch.equal(v, model.state_dict()[k]) for k, v in before.items())
