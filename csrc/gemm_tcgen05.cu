@@ -14,7 +14,7 @@
 // warps 4..19 = epilogue (TMEM lane quarter = warp % 4; the four warps of a quarter split each staging slab).
 // Three mbarrier pipelines: smem full/empty, TMEM full/empty, plus bulk-group tracking of the TMA stores.
 //
-// Measured on B200 (tools/microbench_mma.py): a tcgen05.mma of N <= 128 costs ~80-110 cycles to issue regardless of
+// Measured on B200 (profiles/gemm_mainloop_anatomy.jsonl): a tcgen05.mma of N <= 128 costs ~80-110 cycles to issue regardless of
 // N, only N = 256 runs at the tensor-pipe rate (128 cycles) -- hence wide tiles, and split-K (not narrower tiles)
 // when a problem has too few tiles for 148 SMs.
 #include <mutex>

@@ -42,7 +42,7 @@ def _layer_stream(layer: int, site: int) -> int:
 @dataclass
 class GemmPlan:
     """(BLOCK_N, split_k) per GEMM of the step (M = tokens).  A tcgen05.mma of N <= 128 costs as much issue time as
-    one of N = 256 (tools/microbench_mma.py), so tiles are as wide as the problem allows and weight-gradient GEMMs,
+    one of N = 256 (profiles/gemm_mainloop_anatomy.jsonl), so tiles are as wide as the problem allows and weight-gradient GEMMs,
     whose output has few tiles, split the token (reduction) dimension instead.  Measured with tools/tune_gemm.py."""
     qkv_fwd: int = 256
     out_fwd: int = 128
@@ -630,10 +630,6 @@ class B200Engine:
         self._optimizer()
         self.launches_per_train_step = self._n_launch
 
-    def _unpack_inputs(self) -> None:
-        T, B = self.T, self.B
-        pass  # ids / lens / labels are views of d_in
-
     def set_batch(self, input_ids: torch.Tensor, lens: torch.Tensor, labels: torch.Tensor) -> None:
         """Device-side batch set-up (inputs already on the GPU, e.g. from the device-resident dataset)."""
         self.ids.copy_(input_ids.reshape(-1))
@@ -657,7 +653,6 @@ class B200Engine:
             g2 = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g2, stream=s):
                 self.d_in.copy_(self.h_in, non_blocking=True)
-                self._unpack_inputs()
                 self._train_step_kernels()
                 self.h_loss.copy_(self.loss_accum, non_blocking=True)
             self._graph_train_e2e = g2
@@ -701,7 +696,6 @@ class B200Engine:
             self._graph_train_e2e.replay()
         else:
             self.d_in.copy_(self.h_in, non_blocking=True)
-            self._unpack_inputs()
             self._train_step_kernels()
             self.h_loss.copy_(self.loss_accum, non_blocking=True)
         torch.cuda.current_stream().synchronize()

@@ -40,8 +40,8 @@ def _lib():
     return lib
 
 
-def _run_both(lib, M, N, K, split, epi, b_major, seed):
-    g = torch.Generator("cuda").manual_seed(seed)
+def _run_both(lib, M, N, K, split, epi, b_major, seed, check_mem=False):
+    g = torch.Generator(torch.device("cuda", torch.cuda.current_device())).manual_seed(seed)
     a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
     b = (torch.randn((N, K) if b_major == 0 else (K, N), device="cuda", generator=g) * 0.05).bfloat16()
     bias = torch.randn(N, device="cuda", generator=g)
@@ -57,8 +57,13 @@ def _run_both(lib, M, N, K, split, epi, b_major, seed):
     assert lib.dcad_gemm_bf16_splitk(*args, ws.data_ptr(), need, stream) == 0
     got = torch.full((M, N), float("nan"), device="cuda", dtype=torch.bfloat16)
     args[2] = got.data_ptr()
+    torch.cuda.synchronize()
+    free_before = torch.cuda.mem_get_info()[0]
     assert lib.dcad_gemm_bf16_splitk_static(*args, stream) == 0
     torch.cuda.synchronize()
+    if check_mem:
+        # the claim itself: the call took no device memory from the driver (nothing allocated, nothing freed)
+        assert torch.cuda.mem_get_info()[0] == free_before
     assert not torch.isnan(got.float()).any()
     assert torch.equal(got, want)
     # sanity against plain fp32 math so that "equal" cannot mean "equally wrong"
@@ -80,7 +85,7 @@ def test_built_in_scratch_matches_caller_workspace_on_consecutive_calls():
     _run_both(lib, 2048, 768, 3072, 3, EPI_BIAS, 0, seed=1)
     # call 2, immediately after, a smaller ragged problem with another epilogue and operand layout: it reuses the
     # scratch the first call filled
-    _run_both(lib, 520, 768, 1536, 4, EPI_DGELU, 1, seed=2)
+    _run_both(lib, 520, 768, 1536, 4, EPI_DGELU, 1, seed=2, check_mem=True)
     # a problem whose partial sums cannot fit in the built-in scratch is refused, not truncated
     assert lib.dcad_gemm_splitk_workspace_bytes(8192, 3072, 4) > cap
     dummy = torch.empty(8, device="cuda", dtype=torch.bfloat16)
@@ -88,3 +93,15 @@ def test_built_in_scratch_matches_caller_workspace_on_consecutive_calls():
                                           768, 768, 3072, None, None, None, 0, 0, 4, 256, 0,
                                           torch.cuda.current_stream().cuda_stream)
     assert rc == ERR_TOO_LARGE
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_every_gpu_has_its_own_built_in_scratch():
+    """One process driving two GPUs: the call made while GPU 1 is current must use GPU 1's copy of the scratch (and
+    GPU 1's kernel attributes), after GPU 0 has already been served."""
+    lib = _lib()
+    with torch.cuda.device(0):
+        _run_both(lib, 520, 768, 1536, 4, EPI_BIAS, 0, seed=3)
+    with torch.cuda.device(1):
+        _run_both(lib, 520, 768, 1536, 4, EPI_BIAS, 0, seed=4)
+        _run_both(lib, 2048, 768, 3072, 3, EPI_DGELU, 1, seed=5, check_mem=True)
