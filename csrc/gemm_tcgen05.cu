@@ -11,12 +11,24 @@
 //     wgrad    dW[N,K] = dY[T,N]^T X[T,K]        A MN-major, B MN-major   (fp32 out, optional split-K)
 //
 // Roles (640 threads): warp 0 = TMA producer, warp 1 = single-thread MMA issuer, warp 2 = TMEM owner,
-// warps 4..19 = epilogue (TMEM lane quarter = warp % 4; the four warps of a quarter split each staging slab).
-// Three mbarrier pipelines: smem full/empty, TMEM full/empty, plus bulk-group tracking of the TMA stores.
+// warps 4..19 = epilogue (TMEM lane quarter = warp % 4).  Three mbarrier pipelines: smem full/empty, TMEM full/empty,
+// plus bulk-group tracking of the TMA stores.
+//
+// Two epilogues are compiled (template parameter EPI, chosen per call by dcad_gemm_set_epilogue / DCAD_GEMM_EPI):
+//   EPI 0 "block": the 16 warps fill one [128 rows][128 B] slab together (the four warps of a lane quarter split its
+//                  64 columns), two block-wide barriers per slab, one thread issues the slab's TMA store, 2 slabs in
+//                  flight.
+//   EPI 1 "warp" : every epilogue warp owns a private [32 rows][128 B] staging box and issues its own TMA stores
+//                  (32-row boxes), so the epilogue has no block-wide barrier and no store waits for another warp's.
+//                  It also carries the 128 x 384 tile (BLOCK_N 384): two N = 192 accumulators fed by two MMAs per
+//                  k-step, which turns the N = 3072 GEMMs from 1.3 waves of 148 SMs (192 tiles of 128 x 256) into one
+//                  (128 tiles); its staging boxes alias the operand ring, idle once the tile's last MMA has retired.
 //
 // Measured on B200 (profiles/gemm_mainloop_anatomy.jsonl): a tcgen05.mma of N <= 128 costs ~80-110 cycles to issue regardless of
 // N, only N = 256 runs at the tensor-pipe rate (128 cycles) -- hence wide tiles, and split-K (not narrower tiles)
 // when a problem has too few tiles for 148 SMs.
+#include <stdlib.h>
+
 #include <mutex>
 #include <unordered_map>
 
@@ -31,6 +43,9 @@ constexpr int UMMA_K = 16;
 constexpr int SLAB_BYTES = BK * 128;       // one [BK][64] MN-major operand slab
 constexpr int STAGING_BYTES = BM * 128;    // one [128 rows][128 B] output slab (64 bf16 or 32 fp32 columns)
 constexpr int NUM_STAGING = 4;             // D ping-pong + aux_out ping-pong
+constexpr int BOX_ROWS = 32;               // EPI 1: output leaves in [32 rows][128 B] boxes (one TMEM lane quarter)
+constexpr int BOX_BYTES = BOX_ROWS * 128;  // 4 KB staging box
+constexpr int EPI_WARPS = 16;
 
 struct GemmParams {
     int M, N, K;
@@ -68,19 +83,34 @@ struct GemmGroup {
     int n;
 };
 
-template <int BN, int CG = 1>
+// EPI 0: BN <= 256, one accumulator of N = BN per tile, two TMEM accumulator stages (the epilogue of a tile overlaps
+// the main loop of the next), four 16 KB staging slabs beside the operand ring.
+// EPI 1: per-warp 4 KB staging boxes.  BN <= 256 as above; BN = 384: two N = 192 accumulators per tile fill the TMEM
+// (one accumulator stage), and the staging boxes (two per warp) alias the operand ring -- the producer does not refill
+// it before the epilogue's stores have read it (stg_free_bar).
+template <int BN, int CG = 1, int EPI = 0>
 struct GemmCfg {
+    static constexpr int NSUB = BN > 256 ? 2 : 1;   // MMAs (accumulators) per k-step
+    static constexpr int SUBN = BN / NSUB;          // UMMA N
+    static constexpr bool ALIAS = BN > 256;
+    static constexpr int ACC_STAGES = BN > 256 ? 1 : 2;
+    static constexpr int NBUF = ALIAS ? 2 : 1;      // EPI 1: staging boxes per epilogue warp
+    static constexpr int STAGING_TOTAL = EPI == 0 ? NUM_STAGING * STAGING_BYTES : EPI_WARPS * NBUF * BOX_BYTES;
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_ROWS = BN / CG;          // B rows (N) staged by one CTA
+    static constexpr int B_BOX_ROWS = B_ROWS > 256 ? B_ROWS / 2 : B_ROWS;  // a TMA box has at most 256 rows
     static constexpr int B_BYTES = B_ROWS * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    // 227 KB per CTA minus the staging slabs, the alignment slack and the static part (bias copy + barriers)
-    static constexpr int RING_BYTES = 232448 - NUM_STAGING * STAGING_BYTES - 1024 - (2 * BN * 4 + 512);
+    // 227 KB per CTA minus the staging area, the alignment slack and the static part (bias copy + barriers)
+    static constexpr int RING_BYTES = 232448 - (ALIAS ? 0 : STAGING_TOTAL) - 1024 - (2 * BN * 4 + 512);
     static constexpr int STAGES_RAW = RING_BYTES / STAGE_BYTES;
     static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
     static constexpr int ACC_STRIDE = pow2_ceil(BN);  // TMEM columns per accumulator stage
-    static constexpr int TMEM_COLS = 2 * ACC_STRIDE;  // two accumulator stages
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + NUM_STAGING * STAGING_BYTES + 1024;
+    static constexpr int TMEM_COLS = ACC_STAGES * ACC_STRIDE;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + (ALIAS ? 0 : STAGING_TOTAL) + 1024;
+    static_assert(EPI == 1 || BN <= 256, "the 384-wide tile needs the per-warp epilogue");
+    static_assert(TMEM_COLS <= 512, "accumulators exceed the 512 TMEM columns");
+    static_assert(!ALIAS || STAGES * STAGE_BYTES >= STAGING_TOTAL, "staging does not fit in the ring");
 };
 
 __device__ __forceinline__ unsigned long long gtimer() {
@@ -112,13 +142,16 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t
     (void)tmA; (void)tmB; (void)tmD; (void)tmAux;                                             \
     const int lu = (unit) - g.unit_begin[prob];
 
-template <int BN, int A_MAJOR, int B_MAJOR, int CG, int G>
+template <int BN, int A_MAJOR, int B_MAJOR, int CG, int G, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ GemmGroup<G> g) {
-    using Cfg = GemmCfg<BN, CG>;
+    using Cfg = GemmCfg<BN, CG, EPI>;
     constexpr int STAGES = Cfg::STAGES;
-    static_assert(BN % 64 == 0 && BN >= 64 && BN <= 256, "BLOCK_N must be a multiple of 64 in [64,256]");
+    constexpr int ACC_STAGES = Cfg::ACC_STAGES;
+    static_assert(BN % 64 == 0 && BN >= 64 && BN <= 512, "BLOCK_N must be a multiple of 64 in [64,512]");
+    static_assert(Cfg::SUBN % 16 == 0 && Cfg::SUBN <= 256, "UMMA N is a multiple of 16 up to 256");
     static_assert(CG == 1 || CG == 2, "cta_group is 1 or 2");
+    static_assert(CG == 1 || BN <= 256, "CTA-pair tiles carry one accumulator");
     static_assert(CG == 1 || B_MAJOR == kMajorK || Cfg::B_ROWS % 64 == 0, "MN-major B halves are whole 64-column slabs");
     static_assert(STAGES >= 2, "need at least a double-buffered operand ring");
 
@@ -127,6 +160,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ GemmGroup<G> g) {
     __shared__ __align__(8) uint64_t empty_bar[STAGES];
     __shared__ __align__(8) uint64_t tmem_full_bar[2];
     __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+    __shared__ __align__(8) uint64_t stg_free_bar;   // ALIAS tiles only: the epilogue's stores have read the ring
     __shared__ __align__(16) float s_bias[2][BN];
     __shared__ uint32_t tmem_base_smem;
 
@@ -134,7 +168,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ GemmGroup<G> g) {
     const uint32_t lane = lane_id();
     const uint32_t cta_rank = (CG == 2) ? cluster_ctarank() : 0u;  // 0 = leader (issues the MMAs), 1 = peer
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024-B alignment
-    const uint32_t staging_base = smem_base + STAGES * Cfg::STAGE_BYTES;
+    const uint32_t staging_base = Cfg::ALIAS ? smem_base : smem_base + STAGES * Cfg::STAGE_BYTES;
 
     if (warp == 0 && lane < static_cast<uint32_t>(g.n)) {
         tma_prefetch_desc(&g.tmA[lane]);
@@ -154,6 +188,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ GemmGroup<G> g) {
             // CG 1: every epilogue thread arrives; CG 2: one lane per epilogue warp of BOTH CTAs arrives on the leader
             mbar_init(smem_u32(&tmem_empty_bar[s]), CG == 1 ? EPI_THREADS : 2 * (EPI_THREADS / 32));
         }
+        mbar_init(smem_u32(&stg_free_bar), EPI_WARPS);
         fence_barrier_init();
     }
     if (warp == 2) {
@@ -180,7 +215,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ GemmGroup<G> g) {
 
     if (warp == 0) {
         // ===================== TMA producer =====================
-        uint32_t stage = 0, phase = 0;
+        uint32_t stage = 0, phase = 0, tiles_done = 0;
         for (int unit = unit0; unit < num_units; unit += unit_step) {
             DCAD_SELECT_PROBLEM(unit)
             const int tile = lu / p.split_k, split = lu % p.split_k;
@@ -189,6 +224,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ GemmGroup<G> g) {
             const int n_row0 = n_blk * BN + static_cast<int>(cta_rank) * Cfg::B_ROWS;  // this CTA's share of B
             const int kb0 = split * p.kb_per_split;
             const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
+            if constexpr (Cfg::ALIAS) {  // the previous tile's output is still being read out of the ring
+                if (tiles_done > 0) mbar_wait(smem_u32(&stg_free_bar), (tiles_done - 1u) & 1u);
+                ++tiles_done;
+            }
             for (int kb = kb0; kb < kb1; ++kb) {
                 mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
                 if (lane == 0) {
@@ -208,7 +247,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ GemmGroup<G> g) {
                         for (int c = 0; c < BM / 64; ++c) load(sA + c * SLAB_BYTES, &tmA, m_blk * BM + c * 64, kb * BK);
                     }
                     if constexpr (B_MAJOR == kMajorK) {
-                        load(sB, &tmB, kb * BK, n_row0);
+#pragma unroll
+                        for (int h = 0; h < Cfg::B_ROWS / Cfg::B_BOX_ROWS; ++h)
+                            load(sB + h * Cfg::B_BOX_ROWS * 128, &tmB, kb * BK, n_row0 + h * Cfg::B_BOX_ROWS);
                     } else {
 #pragma unroll
                         for (int c = 0; c < Cfg::B_ROWS / 64; ++c)
@@ -223,7 +264,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ GemmGroup<G> g) {
     } else if (warp == 1 && (CG == 1 || cta_rank == 0)) {
         // ===================== MMA issuer (one thread; of the leader CTA when CG = 2) =====================
         // Descriptors are built once; per MMA only the 14-bit start-address field (16-byte units) advances.
-        constexpr uint32_t idesc = make_idesc_bf16(BM * CG, BN, A_MAJOR, B_MAJOR);
+        constexpr uint32_t idesc = make_idesc_bf16(BM * CG, Cfg::SUBN, A_MAJOR, B_MAJOR);
+        // second accumulator of a wide tile: B rows SUBN.. of the stage (K-major: SUBN rows of 128 B; MN-major:
+        // SUBN/64 slabs of 8 KB) -- the same byte offset either way
+        constexpr uint32_t B_SUBSTEP = (Cfg::SUBN * 128) >> 4;
         constexpr uint32_t A_KSTEP = (A_MAJOR == kMajorK ? UMMA_K * 2 : UMMA_K * 128) >> 4;
         constexpr uint32_t B_KSTEP = (B_MAJOR == kMajorK ? UMMA_K * 2 : UMMA_K * 128) >> 4;
         const uint64_t a_desc0 = (A_MAJOR == kMajorK) ? make_smem_desc_sw128(smem_base, 16, 1024)
@@ -252,9 +296,14 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ GemmGroup<G> g) {
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k) {
                         const uint64_t adesc = (static_cast<uint64_t>(a_hi) << 32) | (a_lo + k * A_KSTEP);
-                        const uint64_t bdesc = (static_cast<uint64_t>(b_hi) << 32) | (b_lo + k * B_KSTEP);
-                        if constexpr (CG == 1) umma_bf16_ss(tmem_d, adesc, bdesc, idesc, (kb != kb0 || k != 0) ? 1u : 0u);
-                        else umma_bf16_ss_cg2(tmem_d, adesc, bdesc, idesc, (kb != kb0 || k != 0) ? 1u : 0u);
+                        const uint32_t acc = (kb != kb0 || k != 0) ? 1u : 0u;
+#pragma unroll
+                        for (int h = 0; h < Cfg::NSUB; ++h) {
+                            const uint64_t bdesc =
+                                (static_cast<uint64_t>(b_hi) << 32) | (b_lo + k * B_KSTEP + h * B_SUBSTEP);
+                            if constexpr (CG == 1) umma_bf16_ss(tmem_d + h * Cfg::SUBN, adesc, bdesc, idesc, acc);
+                            else umma_bf16_ss_cg2(tmem_d, adesc, bdesc, idesc, acc);
+                        }
                     }
                     if constexpr (CG == 1) {
                         umma_commit(smem_u32(&empty_bar[stage]));  // frees the smem slot when the MMAs retire
@@ -267,21 +316,191 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ GemmGroup<G> g) {
                 __syncwarp();
                 if (++stage == STAGES) { stage = 0; phase ^= 1u; }
             }
-            if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1u; }
+            if (++acc_stage == ACC_STAGES) { acc_stage = 0; acc_phase ^= 1u; }
         }
         DCAD_STAMP(3);
     } else if (warp >= 4) {
-        // ===================== epilogue (16 warps) =====================
-        // Output leaves through [128 rows][128 B] slabs staged in 128B-swizzled smem and written by TMA: 64 bf16 or
-        // 32 fp32 columns per slab.  Warp (q, part) owns rows 32q..32q+31 and quarter `part` of every slab, so a
-        // thread converts 16 bf16 (or moves 8 fp32) columns per slab: the GELU / dGELU epilogues are ALU-bound and
-        // need all the lanes they can get.
+      if constexpr (EPI == 0) {
+            // ===================== epilogue (16 warps) =====================
+            // Output leaves through [128 rows][128 B] slabs staged in 128B-swizzled smem and written by TMA: 64 bf16 or
+            // 32 fp32 columns per slab.  Warp (q, part) owns rows 32q..32q+31 and quarter `part` of every slab, so a
+            // thread converts 16 bf16 (or moves 8 fp32) columns per slab: the GELU / dGELU epilogues are ALU-bound and
+            // need all the lanes they can get.
+            const uint32_t q = warp & 3u;
+            const int part = static_cast<int>(warp - 4) >> 2;  // 0..3
+            const int ep_tid = static_cast<int>(threadIdx.x) - 128;
+            const int r_in_tile = q * 32 + lane;
+            uint32_t acc_stage = 0, acc_phase = 0, slab_ctr = 0;
+            for (int unit = unit0; unit < num_units; unit += unit_step) {
+                DCAD_SELECT_PROBLEM(unit)
+                const bool has_bias = (p.epi == DCAD_EPI_BIAS || p.epi == DCAD_EPI_BIAS_GELU);
+                const int tile = lu / p.split_k;
+                const int m_blk = (tile % p.num_m_blocks) * CG + static_cast<int>(cta_rank);
+                const int n_blk = tile / p.num_m_blocks;
+                const int n_base = n_blk * BN;
+                const bool tile_ok = m_blk * BM < p.M;  // the peer's half of a pair tile may lie wholly past M
+                const int out_row0 = (lu % p.split_k) * p.ws_row_stride + m_blk * BM;  // ws_row_stride == 0 unless workspace mode
+                const int row = m_blk * BM + r_in_tile;
+                const bool row_ok = row < p.M;
+                // Padded token rows (tile = one 128-token sequence): the GELU / dGELU arithmetic is skipped for them and
+                // zeros are written -- nothing downstream reads them and their gradients are exactly zero.  The epilogue
+                // is ALU-bound (two MUFU per element), and a third of the rows of a flow-sentence batch are padding.
+                const bool row_live = row_ok && (p.row_lens == nullptr || r_in_tile < __ldg(p.row_lens + m_blk));
+                if (has_bias) {  // stage this tile's bias while the MMAs are still running
+                    if (ep_tid < BN)
+                        s_bias[acc_stage][ep_tid] = (n_base + ep_tid < p.N) ? __ldg(p.bias + n_base + ep_tid) : 0.f;
+                }
+                const __nv_bfloat16* aux_row =
+                    (p.epi == DCAD_EPI_DGELU && row_ok) ? p.aux + static_cast<size_t>(row) * p.ldaux + n_base : nullptr;
+                mbar_wait(smem_u32(&tmem_full_bar[acc_stage]), acc_phase);
+                tc_fence_after();
+                if (warp == 4) DCAD_STAMP(4);
+                const uint32_t t_row = tmem_base + acc_stage * Cfg::ACC_STRIDE + ((q * 32u) << 16);
+
+                if (!p.out_fp32) {
+                    // ---- bf16 output: 64-column slabs, this thread converts 16 columns per slab ----
+    #pragma unroll 1
+                    for (int s = 0; s < BN / 64; ++s) {
+                        const uint32_t buf = slab_ctr & 1u;
+                        const int c0 = s * 64 + part * 16;  // first accumulator column handled by this thread
+                        uint32_t r[16];
+                        tmem_ld_32x32b_x16(t_row + c0, r);
+                        uint4 av[2];
+    #pragma unroll
+                        for (int j = 0; j < 2; ++j)
+                            av[j] = (aux_row && n_base + c0 + j * 8 < p.N)
+                                        ? __ldg(reinterpret_cast<const uint4*>(aux_row + c0) + j) : make_uint4(0, 0, 0, 0);
+                        if (ep_tid == 0) bulk_wait_group_read<1>();  // the store that last read staging[buf] is done
+                        epi_bar_sync();                               // (also publishes s_bias on the first slab)
+                        tmem_ld_wait();
+                        float v[16];
+    #pragma unroll
+                        for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+                        if (has_bias) {
+                            const float4* bs = reinterpret_cast<const float4*>(&s_bias[acc_stage][c0]);
+    #pragma unroll
+                            for (int j = 0; j < 16; j += 4) {
+                                const float4 b = bs[j >> 2];
+                                v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
+                            }
+                        }
+                        const uint32_t sD = staging_base + buf * STAGING_BYTES;
+                        if (p.epi == DCAD_EPI_BIAS_GELU) {
+                            if (p.has_aux_out) {
+                                const uint32_t sX = staging_base + (2 + buf) * STAGING_BYTES;
+    #pragma unroll
+                                for (int j = 0; j < 2; ++j)
+                                    st_shared_v4(sX + sw128_offset(r_in_tile, part * 2 + j),
+                                                 pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                                                 pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+                            }
+                            if (row_live) {
+    #pragma unroll
+                                for (int j = 0; j < 16; ++j) v[j] = gelu_erf(v[j]);
+                            } else {
+    #pragma unroll
+                                for (int j = 0; j < 16; ++j) v[j] = 0.f;
+                            }
+                        } else if (p.epi == DCAD_EPI_DGELU && !row_live) {
+    #pragma unroll
+                            for (int j = 0; j < 16; ++j) v[j] = 0.f;
+                        } else if (p.epi == DCAD_EPI_DGELU) {
+    #pragma unroll
+                            for (int j = 0; j < 2; ++j) {
+                                const float2 a0 = unpack_bf16x2(av[j].x), a1 = unpack_bf16x2(av[j].y);
+                                const float2 a2 = unpack_bf16x2(av[j].z), a3 = unpack_bf16x2(av[j].w);
+                                v[8 * j] *= dgelu_erf(a0.x); v[8 * j + 1] *= dgelu_erf(a0.y);
+                                v[8 * j + 2] *= dgelu_erf(a1.x); v[8 * j + 3] *= dgelu_erf(a1.y);
+                                v[8 * j + 4] *= dgelu_erf(a2.x); v[8 * j + 5] *= dgelu_erf(a2.y);
+                                v[8 * j + 6] *= dgelu_erf(a3.x); v[8 * j + 7] *= dgelu_erf(a3.y);
+                            }
+                        }
+    #pragma unroll
+                        for (int j = 0; j < 2; ++j)
+                            st_shared_v4(sD + sw128_offset(r_in_tile, part * 2 + j),
+                                         pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                                         pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+                        if (p.colsum) {
+                            // bias gradient of the layer that consumes this output: the warp's 32 rows x 16 columns are
+                            // reduced with a shuffle butterfly, one fp32 atomic per column and warp
+                            if (!row_ok) {
+    #pragma unroll
+                                for (int j = 0; j < 16; ++j) v[j] = 0.f;
+                            }
+                            warp_colsum<16>(v, lane);
+                            const int col = n_base + c0 + static_cast<int>(lane);
+                            if (lane < 16 && col < p.N) atomicAdd(p.colsum + col, v[0]);
+                        }
+                        fence_proxy_async_smem();
+                        epi_bar_sync();
+                        if (ep_tid == 0) {
+                            if (tile_ok && n_base + s * 64 < p.N) {
+                                tma_store_2d(&tmD, sD, n_base + s * 64, m_blk * BM);
+                                if (p.epi == DCAD_EPI_BIAS_GELU && p.has_aux_out)
+                                    tma_store_2d(&tmAux, staging_base + (2 + buf) * STAGING_BYTES, n_base + s * 64, m_blk * BM);
+                            }
+                            bulk_commit_group();
+                        }
+                        ++slab_ctr;
+                    }
+                } else {
+                    // ---- fp32 output (weight gradients): 32-column slabs, this thread moves 8 columns per slab ----
+    #pragma unroll 1
+                    for (int s = 0; s < BN / 32; ++s) {
+                        const uint32_t buf = slab_ctr & 1u;
+                        const int c0 = s * 32 + part * 8;
+                        uint32_t r[8];
+                        tmem_ld_32x32b_x8(t_row + c0, r);
+                        if (ep_tid == 0) bulk_wait_group_read<1>();
+                        epi_bar_sync();
+                        tmem_ld_wait();
+                        const uint32_t sD = staging_base + buf * STAGING_BYTES;
+    #pragma unroll
+                        for (int j = 0; j < 2; ++j)
+                            st_shared_v4(sD + sw128_offset(r_in_tile, part * 2 + j), r[4 * j], r[4 * j + 1], r[4 * j + 2],
+                                         r[4 * j + 3]);
+                        fence_proxy_async_smem();
+                        epi_bar_sync();
+                        if (ep_tid == 0) {
+                            if (tile_ok && n_base + s * 32 < p.N) {
+                                if ((p.split_k > 1 && p.ws_row_stride == 0) || p.out_fp32 == 2) tma_reduce_add_2d(&tmD, sD, n_base + s * 32, out_row0);
+                                else tma_store_2d(&tmD, sD, n_base + s * 32, out_row0);
+                            }
+                            bulk_commit_group();
+                        }
+                        ++slab_ctr;
+                    }
+                }
+                tc_fence_before();
+                if constexpr (CG == 1) {
+                    mbar_arrive(smem_u32(&tmem_empty_bar[acc_stage]));
+                } else {  // the leader's MMA thread waits for the epilogues of both CTAs
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_remote(smem_u32(&tmem_empty_bar[acc_stage]), 0);
+                }
+                if (warp == 4) DCAD_STAMP(5);
+                if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1u; }
+            }
+            if (ep_tid == 0) bulk_wait_group<0>();  // all output writes have landed before the CTA retires
+    
+      } else {
+        // ===================== epilogue, EPI 1 (16 independent warps) =====================
+        // Warp (q, part): TMEM lanes (= tile rows) 32q..32q+31, and the 64-column (bf16 out) or 32-column (fp32 out)
+        // slabs part, part+4, ... of the tile.  A slab leaves as one [32 rows][128 B] box: tcgen05.ld -> registers
+        // (bias / GELU / dGELU) -> the warp's private swizzled staging box -> one TMA store issued by lane 0.  Nothing
+        // here synchronises with another warp, and a box is reused only after its own store has read it.
         const uint32_t q = warp & 3u;
         const int part = static_cast<int>(warp - 4) >> 2;  // 0..3
         const int ep_tid = static_cast<int>(threadIdx.x) - 128;
         const int r_in_tile = q * 32 + lane;
-        uint32_t acc_stage = 0, acc_phase = 0, slab_ctr = 0;
-        for (int unit = unit0; unit < num_units; unit += unit_step) {
+        const uint32_t stg0 = staging_base + (warp - 4) * (Cfg::NBUF * BOX_BYTES);
+        uint32_t acc_stage = 0, acc_phase = 0, st_ctr = 0, tile_ctr = 0;
+        auto box_acquire = [&]() -> uint32_t {  // a staging box that no TMA store is still reading
+            if (lane == 0) bulk_wait_group_read<Cfg::NBUF - 1>();
+            __syncwarp();
+            return stg0 + (st_ctr % Cfg::NBUF) * BOX_BYTES;
+        };
+        for (int unit = unit0; unit < num_units; unit += unit_step, ++tile_ctr) {
             DCAD_SELECT_PROBLEM(unit)
             const bool has_bias = (p.epi == DCAD_EPI_BIAS || p.epi == DCAD_EPI_BIAS_GELU);
             const int tile = lu / p.split_k;
@@ -289,16 +508,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ GemmGroup<G> g) {
             const int n_blk = tile / p.num_m_blocks;
             const int n_base = n_blk * BN;
             const bool tile_ok = m_blk * BM < p.M;  // the peer's half of a pair tile may lie wholly past M
-            const int out_row0 = (lu % p.split_k) * p.ws_row_stride + m_blk * BM;  // ws_row_stride == 0 unless workspace mode
+            const int box_row0 = m_blk * BM + static_cast<int>(q) * BOX_ROWS;
+            const int out_row0 = (lu % p.split_k) * p.ws_row_stride + box_row0;  // ws_row_stride == 0 unless workspace mode
             const int row = m_blk * BM + r_in_tile;
             const bool row_ok = row < p.M;
-            // Padded token rows (tile = one 128-token sequence): the GELU / dGELU arithmetic is skipped for them and
-            // zeros are written -- nothing downstream reads them and their gradients are exactly zero.  The epilogue
-            // is ALU-bound (two MUFU per element), and a third of the rows of a flow-sentence batch are padding.
             const bool row_live = row_ok && (p.row_lens == nullptr || r_in_tile < __ldg(p.row_lens + m_blk));
+            float* bias_s = s_bias[tile_ctr & 1u];
             if (has_bias) {  // stage this tile's bias while the MMAs are still running
-                if (ep_tid < BN)
-                    s_bias[acc_stage][ep_tid] = (n_base + ep_tid < p.N) ? __ldg(p.bias + n_base + ep_tid) : 0.f;
+                if (ep_tid < BN) bias_s[ep_tid] = (n_base + ep_tid < p.N) ? __ldg(p.bias + n_base + ep_tid) : 0.f;
+                // publishes the bias; no warp can be two tiles ahead of another (it would have to pass the next
+                // tile's barrier), so the two copies never collide
+                epi_bar_sync();
             }
             const __nv_bfloat16* aux_row =
                 (p.epi == DCAD_EPI_DGELU && row_ok) ? p.aux + static_cast<size_t>(row) * p.ldaux + n_base : nullptr;
@@ -308,117 +528,116 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ GemmGroup<G> g) {
             const uint32_t t_row = tmem_base + acc_stage * Cfg::ACC_STRIDE + ((q * 32u) << 16);
 
             if (!p.out_fp32) {
-                // ---- bf16 output: 64-column slabs, this thread converts 16 columns per slab ----
+                // ---- bf16 output: 64-column slabs, converted 16 columns at a time ----
+                const bool two_pass = (p.epi == DCAD_EPI_BIAS_GELU && p.has_aux_out);
 #pragma unroll 1
-                for (int s = 0; s < BN / 64; ++s) {
-                    const uint32_t buf = slab_ctr & 1u;
-                    const int c0 = s * 64 + part * 16;  // first accumulator column handled by this thread
-                    uint32_t r[16];
-                    tmem_ld_32x32b_x16(t_row + c0, r);
-                    uint4 av[2];
+                for (int s = part; s < BN / 64; s += 4) {
+                    const int c0 = s * 64;
+                    const bool do_store = tile_ok && n_base + c0 < p.N;
+#pragma unroll 1
+                    for (int pass = two_pass ? 0 : 1; pass < 2; ++pass) {
+                        // pass 0 (lin1 forward in training): the pre-activation, kept for the backward; pass 1: D
+                        const uint32_t sD = box_acquire();
+#pragma unroll 1
+                        for (int h = 0; h < 4; ++h) {
+                            const int ch = c0 + h * 16;  // first accumulator column of this quarter-slab
+                            uint32_t r[16];
+                            tmem_ld_32x32b_x16(t_row + ch, r);
+                            uint4 av[2];
+                            if (p.epi == DCAD_EPI_DGELU) {
 #pragma unroll
-                    for (int j = 0; j < 2; ++j)
-                        av[j] = (aux_row && n_base + c0 + j * 8 < p.N)
-                                    ? __ldg(reinterpret_cast<const uint4*>(aux_row + c0) + j) : make_uint4(0, 0, 0, 0);
-                    if (ep_tid == 0) bulk_wait_group_read<1>();  // the store that last read staging[buf] is done
-                    epi_bar_sync();                               // (also publishes s_bias on the first slab)
-                    tmem_ld_wait();
-                    float v[16];
+                                for (int j = 0; j < 2; ++j)
+                                    av[j] = (aux_row && row_live && n_base + ch + j * 8 < p.N)
+                                                ? __ldg(reinterpret_cast<const uint4*>(aux_row + ch) + j)
+                                                : make_uint4(0, 0, 0, 0);
+                            }
+                            tmem_ld_wait();
+                            float v[16];
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
-                    if (has_bias) {
-                        const float4* bs = reinterpret_cast<const float4*>(&s_bias[acc_stage][c0]);
+                            for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+                            if (has_bias) {
+                                const float4* bs = reinterpret_cast<const float4*>(bias_s + ch);
 #pragma unroll
-                        for (int j = 0; j < 16; j += 4) {
-                            const float4 b = bs[j >> 2];
-                            v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
-                        }
-                    }
-                    const uint32_t sD = staging_base + buf * STAGING_BYTES;
-                    if (p.epi == DCAD_EPI_BIAS_GELU) {
-                        if (p.has_aux_out) {
-                            const uint32_t sX = staging_base + (2 + buf) * STAGING_BYTES;
+                                for (int j = 0; j < 16; j += 4) {
+                                    const float4 b = bs[j >> 2];
+                                    v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
+                                }
+                            }
+                            if (p.epi == DCAD_EPI_BIAS_GELU && pass == 1) {
+                                if (row_live) {
+#pragma unroll
+                                    for (int j = 0; j < 16; ++j) v[j] = gelu_erf(v[j]);
+                                } else {
+#pragma unroll
+                                    for (int j = 0; j < 16; ++j) v[j] = 0.f;
+                                }
+                            } else if (p.epi == DCAD_EPI_DGELU) {
+                                if (row_live) {
+#pragma unroll
+                                    for (int j = 0; j < 2; ++j) {
+                                        const float2 a0 = unpack_bf16x2(av[j].x), a1 = unpack_bf16x2(av[j].y);
+                                        const float2 a2 = unpack_bf16x2(av[j].z), a3 = unpack_bf16x2(av[j].w);
+                                        v[8 * j] *= dgelu_erf(a0.x); v[8 * j + 1] *= dgelu_erf(a0.y);
+                                        v[8 * j + 2] *= dgelu_erf(a1.x); v[8 * j + 3] *= dgelu_erf(a1.y);
+                                        v[8 * j + 4] *= dgelu_erf(a2.x); v[8 * j + 5] *= dgelu_erf(a2.y);
+                                        v[8 * j + 6] *= dgelu_erf(a3.x); v[8 * j + 7] *= dgelu_erf(a3.y);
+                                    }
+                                } else {
+#pragma unroll
+                                    for (int j = 0; j < 16; ++j) v[j] = 0.f;
+                                }
+                            }
 #pragma unroll
                             for (int j = 0; j < 2; ++j)
-                                st_shared_v4(sX + sw128_offset(r_in_tile, part * 2 + j),
+                                st_shared_v4(sD + sw128_offset(lane, h * 2 + j),
                                              pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
                                              pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+                            if (p.colsum && pass == 1) {
+                                // bias gradient of the layer that consumes this output: the warp's 32 rows x 16 columns
+                                // are reduced with a shuffle butterfly, one fp32 atomic per column and warp
+                                if (!row_ok) {
+#pragma unroll
+                                    for (int j = 0; j < 16; ++j) v[j] = 0.f;
+                                }
+                                warp_colsum<16>(v, lane);
+                                const int col = n_base + ch + static_cast<int>(lane);
+                                if (lane < 16 && col < p.N) atomicAdd(p.colsum + col, v[0]);
+                            }
                         }
-                        if (row_live) {
-#pragma unroll
-                            for (int j = 0; j < 16; ++j) v[j] = gelu_erf(v[j]);
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 16; ++j) v[j] = 0.f;
+                        fence_proxy_async_smem();
+                        __syncwarp();
+                        if (lane == 0) {
+                            if (do_store) {
+                                if (pass == 0) tma_store_2d(&tmAux, sD, n_base + c0, box_row0);
+                                else tma_store_2d(&tmD, sD, n_base + c0, out_row0);
+                            }
+                            bulk_commit_group();  // (also when nothing was stored: box reuse counts groups)
                         }
-                    } else if (p.epi == DCAD_EPI_DGELU && !row_live) {
-#pragma unroll
-                        for (int j = 0; j < 16; ++j) v[j] = 0.f;
-                    } else if (p.epi == DCAD_EPI_DGELU) {
-#pragma unroll
-                        for (int j = 0; j < 2; ++j) {
-                            const float2 a0 = unpack_bf16x2(av[j].x), a1 = unpack_bf16x2(av[j].y);
-                            const float2 a2 = unpack_bf16x2(av[j].z), a3 = unpack_bf16x2(av[j].w);
-                            v[8 * j] *= dgelu_erf(a0.x); v[8 * j + 1] *= dgelu_erf(a0.y);
-                            v[8 * j + 2] *= dgelu_erf(a1.x); v[8 * j + 3] *= dgelu_erf(a1.y);
-                            v[8 * j + 4] *= dgelu_erf(a2.x); v[8 * j + 5] *= dgelu_erf(a2.y);
-                            v[8 * j + 6] *= dgelu_erf(a3.x); v[8 * j + 7] *= dgelu_erf(a3.y);
-                        }
+                        ++st_ctr;
                     }
-#pragma unroll
-                    for (int j = 0; j < 2; ++j)
-                        st_shared_v4(sD + sw128_offset(r_in_tile, part * 2 + j),
-                                     pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
-                                     pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
-                    if (p.colsum) {
-                        // bias gradient of the layer that consumes this output: the warp's 32 rows x 16 columns are
-                        // reduced with a shuffle butterfly, one fp32 atomic per column and warp
-                        if (!row_ok) {
-#pragma unroll
-                            for (int j = 0; j < 16; ++j) v[j] = 0.f;
-                        }
-                        warp_colsum<16>(v, lane);
-                        const int col = n_base + c0 + static_cast<int>(lane);
-                        if (lane < 16 && col < p.N) atomicAdd(p.colsum + col, v[0]);
-                    }
-                    fence_proxy_async_smem();
-                    epi_bar_sync();
-                    if (ep_tid == 0) {
-                        if (tile_ok && n_base + s * 64 < p.N) {
-                            tma_store_2d(&tmD, sD, n_base + s * 64, m_blk * BM);
-                            if (p.epi == DCAD_EPI_BIAS_GELU && p.has_aux_out)
-                                tma_store_2d(&tmAux, staging_base + (2 + buf) * STAGING_BYTES, n_base + s * 64, m_blk * BM);
-                        }
-                        bulk_commit_group();
-                    }
-                    ++slab_ctr;
                 }
             } else {
-                // ---- fp32 output (weight gradients): 32-column slabs, this thread moves 8 columns per slab ----
+                // ---- fp32 output (weight gradients, split-K partials): 32-column slabs ----
 #pragma unroll 1
-                for (int s = 0; s < BN / 32; ++s) {
-                    const uint32_t buf = slab_ctr & 1u;
-                    const int c0 = s * 32 + part * 8;
-                    uint32_t r[8];
-                    tmem_ld_32x32b_x8(t_row + c0, r);
-                    if (ep_tid == 0) bulk_wait_group_read<1>();
-                    epi_bar_sync();
+                for (int s = part; s < BN / 32; s += 4) {
+                    const int c0 = s * 32;
+                    uint32_t r[32];
+                    tmem_ld_32x32b_x32(t_row + c0, r);
+                    const uint32_t sD = box_acquire();
                     tmem_ld_wait();
-                    const uint32_t sD = staging_base + buf * STAGING_BYTES;
 #pragma unroll
-                    for (int j = 0; j < 2; ++j)
-                        st_shared_v4(sD + sw128_offset(r_in_tile, part * 2 + j), r[4 * j], r[4 * j + 1], r[4 * j + 2],
-                                     r[4 * j + 3]);
+                    for (int j = 0; j < 8; ++j)
+                        st_shared_v4(sD + sw128_offset(lane, j), r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
                     fence_proxy_async_smem();
-                    epi_bar_sync();
-                    if (ep_tid == 0) {
-                        if (tile_ok && n_base + s * 32 < p.N) {
-                            if ((p.split_k > 1 && p.ws_row_stride == 0) || p.out_fp32 == 2) tma_reduce_add_2d(&tmD, sD, n_base + s * 32, out_row0);
-                            else tma_store_2d(&tmD, sD, n_base + s * 32, out_row0);
+                    __syncwarp();
+                    if (lane == 0) {
+                        if (tile_ok && n_base + c0 < p.N) {
+                            if ((p.split_k > 1 && p.ws_row_stride == 0) || p.out_fp32 == 2) tma_reduce_add_2d(&tmD, sD, n_base + c0, out_row0);
+                            else tma_store_2d(&tmD, sD, n_base + c0, out_row0);
                         }
                         bulk_commit_group();
                     }
-                    ++slab_ctr;
+                    ++st_ctr;
                 }
             }
             tc_fence_before();
@@ -428,10 +647,18 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ GemmGroup<G> g) {
                 __syncwarp();
                 if (lane == 0) mbar_arrive_remote(smem_u32(&tmem_empty_bar[acc_stage]), 0);
             }
+            if constexpr (Cfg::ALIAS) {  // hand the ring back to the producer once this warp's stores have read it
+                if (lane == 0) {
+                    bulk_wait_group_read<0>();
+                    mbar_arrive(smem_u32(&stg_free_bar));
+                }
+                __syncwarp();
+            }
             if (warp == 4) DCAD_STAMP(5);
-            if (++acc_stage == 2) { acc_stage = 0; acc_phase ^= 1u; }
+            if (++acc_stage == ACC_STAGES) { acc_stage = 0; acc_phase ^= 1u; }
         }
-        if (ep_tid == 0) bulk_wait_group<0>();  // all output writes have landed before the CTA retires
+        if (lane == 0) bulk_wait_group<0>();  // this warp's output writes have landed before the CTA retires
+      }
     }
 
     tc_fence_before();
@@ -553,10 +780,10 @@ static int num_sms() {
     return n;
 }
 
-template <int BN, int A_MAJOR, int B_MAJOR, int CG, int G>
+template <int BN, int A_MAJOR, int B_MAJOR, int CG, int G, int EPI>
 static int launch_gemm(const GemmGroup<G>& g, int max_ctas, cudaStream_t stream) {
-    using Cfg = GemmCfg<BN, CG>;
-    auto kern = gemm_bf16_tcgen05_kernel<BN, A_MAJOR, B_MAJOR, CG, G>;
+    using Cfg = GemmCfg<BN, CG, EPI>;
+    auto kern = gemm_bf16_tcgen05_kernel<BN, A_MAJOR, B_MAJOR, CG, G, EPI>;
     static DeviceOnce once;
     DCAD_CUDA_TRY(ensure_dynamic_smem(kern, Cfg::SMEM_BYTES, once));
     int grid = g.unit_begin[g.n];  // work units = CTAs (CG 1) or CTA pairs (CG 2)
@@ -570,6 +797,21 @@ static int launch_gemm(const GemmGroup<G>& g, int max_ctas, cudaStream_t stream)
 
 using namespace dcad;
 
+// which epilogue the dispatch picks: 0 = block-wide slabs, 1 = per-warp boxes.  DCAD_GEMM_EPI presets it.
+static int g_gemm_epi = -1;
+static int gemm_epi_mode() {
+    if (g_gemm_epi < 0) {
+        const char* e = getenv("DCAD_GEMM_EPI");
+        g_gemm_epi = (e && e[0] == '1') ? 1 : 0;
+    }
+    return g_gemm_epi;
+}
+extern "C" int dcad_gemm_set_epilogue(int mode) {
+    const int prev = gemm_epi_mode();
+    if (mode == 0 || mode == 1) g_gemm_epi = mode;
+    return prev;
+}
+
 static unsigned long long* g_gemm_timing = nullptr;
 // profiling aid: when set, CTA 0 of every following GEMM writes 7 globaltimer stamps (ns) to this device buffer
 extern "C" void dcad_gemm_set_timing_buffer(void* dev_ptr) { g_gemm_timing = reinterpret_cast<unsigned long long*>(dev_ptr); }
@@ -580,8 +822,8 @@ extern "C" void dcad_gemm_set_timing_buffer(void* dev_ptr) { g_gemm_timing = rei
 static int build_problem(GemmParams& p, CUtensorMap& tmA, CUtensorMap& tmB, CUtensorMap& tmD, CUtensorMap& tmAux,
                          const void* A, const void* B, void* D, int M, int N, int K, int a_major, int b_major, int lda,
                          int ldb, int ldd, const float* bias, const void* aux, void* aux_out, int ldaux, int epi,
-                         int out_fp32, int split_k, int ws_row_stride, int bn, int cg, float* colsum = nullptr,
-                         const int* row_lens = nullptr) {
+                         int out_fp32, int split_k, int ws_row_stride, int bn, int cg, int epi_mode,
+                         float* colsum = nullptr, const int* row_lens = nullptr) {
     if (M <= 0 || N <= 0 || K <= 0) return DCAD_ERR_BAD_SHAPE;
     if (colsum && out_fp32) return DCAD_ERR_BAD_ARGUMENT;
     if ((N % 8) || (ldd % 8) || (lda % 8) || (ldb % 8)) return DCAD_ERR_BAD_ALIGNMENT;
@@ -612,14 +854,17 @@ static int build_problem(GemmParams& p, CUtensorMap& tmA, CUtensorMap& tmB, CUte
     if (a_major == kMajorK) rc = make_tensor_map_2d(&tmA, A, M, K, lda, BM, BK, 2);   // A stored [M][lda]
     else                    rc = make_tensor_map_2d(&tmA, A, K, M, lda, BK, 64, 2);   // A stored [K][lda]
     if (rc) return rc;
-    if (b_major == kMajorK) rc = make_tensor_map_2d(&tmB, B, N, K, ldb, bn / cg, BK, 2);  // B stored [N][ldb]
+    const int b_box_rows = (bn / cg > 256) ? bn / cg / 2 : bn / cg;  // GemmCfg::B_BOX_ROWS
+    if (b_major == kMajorK) rc = make_tensor_map_2d(&tmB, B, N, K, ldb, b_box_rows, BK, 2);  // B stored [N][ldb]
     else                    rc = make_tensor_map_2d(&tmB, B, K, N, ldb, BK, 64, 2);   // B stored [K][ldb]
     if (rc) return rc;
     const uint64_t d_rows = ws_row_stride > 0 ? static_cast<uint64_t>(ws_row_stride) * split_k : static_cast<uint64_t>(M);
-    rc = out_fp32 ? make_tensor_map_2d(&tmD, D, d_rows, N, ldd, BM, 32, 4) : make_tensor_map_2d(&tmD, D, d_rows, N, ldd, BM, 64, 2);
+    const int d_box_rows = epi_mode == 1 ? BOX_ROWS : BM;  // per-warp boxes or whole-tile slabs
+    rc = out_fp32 ? make_tensor_map_2d(&tmD, D, d_rows, N, ldd, d_box_rows, 32, 4)
+                  : make_tensor_map_2d(&tmD, D, d_rows, N, ldd, d_box_rows, 64, 2);
     if (rc) return rc;
     if (p.has_aux_out) {
-        rc = make_tensor_map_2d(&tmAux, aux_out, M, N, p.ldaux, BM, 64, 2);
+        rc = make_tensor_map_2d(&tmAux, aux_out, M, N, p.ldaux, d_box_rows, 64, 2);
         if (rc) return rc;
     } else {
         tmAux = tmD;
@@ -639,20 +884,23 @@ static int gemm_dispatch(const void* A, const void* B, void* D, int M, int N, in
                          float* colsum = nullptr, const int* row_lens = nullptr) {
     int bn, cg;
     parse_tile(block_n, N, bn, cg);
+    const int em = (bn > 256) ? 1 : gemm_epi_mode();  // the 384-wide tile exists with the per-warp epilogue only
     GemmGroup<1> g;
     int rc = build_problem(g.p[0], g.tmA[0], g.tmB[0], g.tmD[0], g.tmAux[0], A, B, D, M, N, K, a_major, b_major, lda,
-                           ldb, ldd, bias, aux, aux_out, ldaux, epi, out_fp32, split_k, ws_row_stride, bn, cg, colsum, row_lens);
+                           ldb, ldd, bias, aux, aux_out, ldaux, epi, out_fp32, split_k, ws_row_stride, bn, cg, em, colsum,
+                           row_lens);
     if (rc) return rc;
     g.n = 1;
     g.unit_begin[0] = 0;
     g.unit_begin[1] = g.p[0].num_m_blocks * g.p[0].num_n_blocks * g.p[0].split_k;
 
-#define DCAD_GEMM_CASE(BN_, AM_, BM_) \
-    if (cg == 1 && bn == BN_ && a_major == AM_ && b_major == BM_) \
-        return launch_gemm<BN_, AM_, BM_, 1, 1>(g, max_ctas, s);
-#define DCAD_GEMM_CASE2(BN_, AM_, BM_) \
-    if (cg == 2 && bn == BN_ && a_major == AM_ && b_major == BM_) \
-        return launch_gemm<BN_, AM_, BM_, 2, 1>(g, max_ctas, s);
+#define DCAD_GEMM_CASE_CG(BN_, AM_, BM_, CG_)                                             \
+    if (cg == CG_ && bn == BN_ && a_major == AM_ && b_major == BM_) {                     \
+        if (em == 1) return launch_gemm<BN_, AM_, BM_, CG_, 1, 1>(g, max_ctas, s);        \
+        return launch_gemm<BN_, AM_, BM_, CG_, 1, 0>(g, max_ctas, s);                     \
+    }
+#define DCAD_GEMM_CASE(BN_, AM_, BM_) DCAD_GEMM_CASE_CG(BN_, AM_, BM_, 1)
+#define DCAD_GEMM_CASE2(BN_, AM_, BM_) DCAD_GEMM_CASE_CG(BN_, AM_, BM_, 2)
     DCAD_GEMM_CASE2(128, 0, 0)
     DCAD_GEMM_CASE2(192, 0, 0)
     DCAD_GEMM_CASE2(256, 0, 0)
@@ -660,7 +908,6 @@ static int gemm_dispatch(const void* A, const void* B, void* D, int M, int N, in
     DCAD_GEMM_CASE2(256, 0, 1)
     DCAD_GEMM_CASE2(128, 1, 1)
     DCAD_GEMM_CASE2(256, 1, 1)
-#undef DCAD_GEMM_CASE2
     DCAD_GEMM_CASE(64, 0, 0)
     DCAD_GEMM_CASE(128, 0, 0)
     DCAD_GEMM_CASE(192, 0, 0)
@@ -674,6 +921,10 @@ static int gemm_dispatch(const void* A, const void* B, void* D, int M, int N, in
     DCAD_GEMM_CASE(192, 1, 1)
     DCAD_GEMM_CASE(256, 1, 1)
 #undef DCAD_GEMM_CASE
+#undef DCAD_GEMM_CASE2
+#undef DCAD_GEMM_CASE_CG
+    if (cg == 1 && bn == 384 && a_major == 0 && b_major == 0) return launch_gemm<384, 0, 0, 1, 1, 1>(g, max_ctas, s);
+    if (cg == 1 && bn == 384 && a_major == 0 && b_major == 1) return launch_gemm<384, 0, 1, 1, 1, 1>(g, max_ctas, s);
     return DCAD_ERR_UNSUPPORTED_TILE;
 }
 
@@ -687,6 +938,7 @@ extern "C" int dcad_gemm_bf16_group(int n, const void* const* A, const void* con
     if (out_fp32 != 1 && out_fp32 != 2) return DCAD_ERR_BAD_ARGUMENT;
     if (block_n <= 0 || (block_n & DCAD_TILE_PAIR)) return DCAD_ERR_UNSUPPORTED_TILE;
     const int bn = block_n;
+    const int em = gemm_epi_mode();
     GemmGroup<DCAD_GEMM_GROUP_MAX> g;
     g.n = n;
     g.unit_begin[0] = 0;
@@ -694,15 +946,17 @@ extern "C" int dcad_gemm_bf16_group(int n, const void* const* A, const void* con
         const int j = i < n ? i : 0;  // unused slots mirror problem 0 (never selected)
         int rc = build_problem(g.p[i], g.tmA[i], g.tmB[i], g.tmD[i], g.tmAux[i], A[j], B[j], D[j], M[j], N[j], K[j],
                                a_major, b_major, lda[j], ldb[j], ldd[j], nullptr, nullptr, nullptr, 0, DCAD_EPI_NONE,
-                               out_fp32, split_k[j], 0, bn, 1);
+                               out_fp32, split_k[j], 0, bn, 1, em);
         if (rc) return rc;
         g.unit_begin[i + 1] = g.unit_begin[i] +
                               (i < n ? g.p[i].num_m_blocks * g.p[i].num_n_blocks * g.p[i].split_k : 0);
     }
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-#define DCAD_GROUP_CASE(BN_, AM_, BM_) \
-    if (bn == BN_ && a_major == AM_ && b_major == BM_) \
-        return launch_gemm<BN_, AM_, BM_, 1, DCAD_GEMM_GROUP_MAX>(g, max_ctas, s);
+#define DCAD_GROUP_CASE(BN_, AM_, BM_)                                                              \
+    if (bn == BN_ && a_major == AM_ && b_major == BM_) {                                            \
+        if (em == 1) return launch_gemm<BN_, AM_, BM_, 1, DCAD_GEMM_GROUP_MAX, 1>(g, max_ctas, s);  \
+        return launch_gemm<BN_, AM_, BM_, 1, DCAD_GEMM_GROUP_MAX, 0>(g, max_ctas, s);               \
+    }
     DCAD_GROUP_CASE(128, 1, 1)
     DCAD_GROUP_CASE(256, 1, 1)
     DCAD_GROUP_CASE(256, 0, 1)

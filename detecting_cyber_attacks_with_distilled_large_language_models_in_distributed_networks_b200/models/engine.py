@@ -46,9 +46,14 @@ class GemmPlan:
     whose output has few tiles, split the token (reduction) dimension instead.  Measured with tools/tune_gemm.py."""
     qkv_fwd: int = 256
     out_fwd: int = 128
-    lin1_fwd: int = 192
+    # N = 3072: 128 x 256 tiles are 192 tiles = 1.3 waves of 148 SMs, so 192-wide tiles on 128 CTAs x 2 tiles were the
+    # measured best.  DCAD_GEMM_WIDE=1 selects 128 x 384 tiles (two N = 192 accumulators per k-step): 128 tiles = one
+    # wave, one tile per CTA (per-warp epilogue; see csrc/gemm_tcgen05.cu).
+    lin1_fwd: int = field(default_factory=lambda: int(os.environ.get(
+        "DCAD_LIN1_FWD_BN", "384" if os.environ.get("DCAD_GEMM_WIDE", "0") != "0" else "192")))
     lin2_fwd: tuple = (256, 3)     # (BLOCK_N, split_k): K = 3072, only 48 output tiles -> workspace split-K
-    lin2_dgrad: int = 192   # -> [T, 3072]
+    lin2_dgrad: int = field(default_factory=lambda: int(os.environ.get(
+        "DCAD_LIN2_DGRAD_BN", "384" if os.environ.get("DCAD_GEMM_WIDE", "0") != "0" else "192")))   # -> [T, 3072]
     # 256 tiles: 128 CTAs x 2 tiles costs the same as 148 CTAs with a ragged second wave (tools/tune_wide.py) and
     # leaves 20 SMs to the weight-gradient branch
     lin2_dgrad_ctas: int = field(default_factory=lambda: int(os.environ.get("DCAD_LIN2_DGRAD_CTAS", "128")))

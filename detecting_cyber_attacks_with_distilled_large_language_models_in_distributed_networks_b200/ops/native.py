@@ -68,6 +68,12 @@ def set_pdl(enabled: bool) -> bool:
     return bool(lib().dcad_set_pdl(1 if enabled else 0))
 
 
+def set_gemm_epilogue(mode: int) -> int:
+    """0 = block-wide slab epilogue, 1 = per-warp 32-row boxes (see ``dcad_gemm_set_epilogue``).  Returns the previous
+    mode.  ``block_n=384`` always runs the per-warp epilogue."""
+    return int(lib().dcad_gemm_set_epilogue(int(mode)))
+
+
 def check(rc: int, what: str) -> None:
     if rc == 0:
         return
@@ -94,6 +100,7 @@ def _declare(L: ctypes.CDLL) -> None:
     P, I, F, L64, U32 = c_void_p, c_int, c_float, c_int64, c_uint32
     sig("dcad_version", [])
     sig("dcad_set_pdl", [I])
+    sig("dcad_gemm_set_epilogue", [I])
     sig("dcad_set_adam_blocks_per_sm", [I])
     sig("dcad_gemm_bf16", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, I, I, P])
     sig("dcad_gemm_bf16_colsum", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, P, P, P])

@@ -48,6 +48,14 @@ int dcad_version(void);
  * made after the call. */
 int dcad_set_pdl(int enabled);
 
+/* Epilogue of the tcgen05 GEMMs below (replaces what cuBLAS's epilogue does for the reference's nn.Linear calls,
+ * client1.py:61 -> transformers modeling_distilbert.py:187-226).  0 = block-wide: the 16 epilogue warps fill one
+ * [128 rows][128 B] slab together and one thread stores it; 1 = per-warp: every epilogue warp stages and TMA-stores its
+ * own [32 rows][128 B] boxes, no block-wide barrier.  block_n = 384 (128 x 384 tiles, two N = 192 accumulators) always
+ * uses 1.  The environment variable DCAD_GEMM_EPI presets it (default 0).  Returns the previous mode; takes effect
+ * for launches and graph captures made after the call. */
+int dcad_gemm_set_epilogue(int mode);
+
 /* bf16 x bf16 -> fp32-accumulated GEMM on tcgen05 tensor cores (TMA-fed, TMEM accumulators, persistent, TMA-store
  * epilogue).
  *   D[M,N] = epilogue( sum_k A(m,k) * B(n,k) )

@@ -52,6 +52,9 @@ def time_graph(fn, iters=20, reps=5):
 
 
 def main():
+    # GEMM_EPI=1: time everything with the per-warp epilogue (dcad_gemm_set_epilogue); results go to *_epi1.json
+    epi_mode = int(os.environ.get("GEMM_EPI", "0"))
+    nv.set_gemm_epilogue(epi_mode)
     torch.manual_seed(0)
     dev = "cuda"
     res = []
@@ -70,6 +73,8 @@ def main():
         P = nv.TILE_PAIR  # "p" prefix below = 256 x bn tile on a CTA pair (cta_group::2)
         lab = lambda bn: ("p" if bn & P else "") + str(bn & ~P)  # noqa: E731
         cands = [(bn, 1) for bn in (64, 128, 192, 256) if N % bn == 0]
+        if N % 384 == 0 and am == 0 and N >= 1536:
+            cands.append((384, 1))  # 128 x 384 tiles (two N = 192 accumulators), per-warp epilogue
         cands += [(bn | P, 1) for bn in (128, 192, 256) if N % bn == 0 and not (bn == 192 and bm == 1)]
         if wgrad:
             cands = [(bn, sk) for bn in (128, 256, 128 | P, 256 | P) for sk in (1, 2, 3, 4, 8)]
@@ -110,7 +115,8 @@ def main():
     totc = sum(r["cublas_us"] for r in res) * 6
     print(f"sum over 6 layers: ours(best) {tot:.0f} us, cuBLAS (no epilogues) {totc:.0f} us")
     os.makedirs(ROOT / "gpurun_out", exist_ok=True)
-    (ROOT / "gpurun_out" / (f"tune_gemm_T{T}.json" if T != 2048 else "tune_gemm.json")).write_text(json.dumps(res, indent=1))
+    name = (f"tune_gemm_T{T}" if T != 2048 else "tune_gemm") + ("_epi1" if epi_mode else "") + ".json"
+    (ROOT / "gpurun_out" / name).write_text(json.dumps(res, indent=1))
 
 
 if __name__ == "__main__":
