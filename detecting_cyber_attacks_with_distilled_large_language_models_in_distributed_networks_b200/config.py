@@ -10,7 +10,7 @@ import dataclasses
 from dataclasses import dataclass, field
 from typing import Optional
 
-TRANSPORTS = ("nvswitch", "nvswitch-oneshot", "nccl", "socket", "none")
+TRANSPORTS = ("auto", "nvswitch", "nvswitch-oneshot", "nvls", "nvswitch-bf16", "nccl", "socket", "none")
 
 
 @dataclass
@@ -19,7 +19,8 @@ class FedConfig:
     num_clients: int = 2
     client_id: int = 1                 # 1-based, like the reference's "Client 1" / "Client 2"
     rounds: int = 1
-    transport: str = "socket"          # nvswitch | nvswitch-oneshot | nccl (baseline) | socket | none
+    transport: str = "socket"          # auto (NVLS from 4 GPUs up, else two-shot) | nvswitch (two-shot) | nvswitch-oneshot |
+                                       # nvls | nvswitch-bf16 (bf16 exchange) | nccl (baseline) | socket | none
     gpus_per_client: int = 1
     # training (reference literals)
     local_epochs: int = 3

@@ -18,7 +18,9 @@ from ..config import FedConfig
 from ..models.arena import ArenaLayout
 from ..ops import native as nv
 from .client import run_client
-from .transport import LoopbackTransport, NcclTransport, NvSwitchDPTransport, NvSwitchTransport, Transport
+from .rounds import RoundCoordinator
+from .transport import (AUTO, LoopbackTransport, NcclTransport, NvSwitchBf16Transport, NvSwitchDPTransport,
+                        NvSwitchTransport, Transport)
 
 
 def _env_int(k: str, d: int) -> int:
@@ -63,18 +65,42 @@ def launch(cfg: FedConfig) -> None:
         dpg = DPGroup.build(rank, world, G, ArenaLayout(ccfg.model_dims()))
         backend_kwargs.update(dp=dpg, init_seed=ccfg.client_id)
         transport = NvSwitchDPTransport(dpg) if world // G > 1 else LoopbackTransport(1)
-    elif world > 1 and use_cuda and cfg.transport.startswith("nvswitch"):
-        from ..parallel.p2p import ONE_SHOT, TWO_SHOT, PeerGroup
+    elif world > 1 and use_cuda and cfg.transport in ("nvswitch", "nvswitch-oneshot", "nvls", "auto", "nvswitch-bf16"):
+        from ..parallel import p2p
+        from ..utils.faults import FaultPlan
 
         layout = ArenaLayout(ccfg.model_dims())
-        one = cfg.transport.endswith("oneshot")
-        group = PeerGroup(rank, world, layout.total, layout.gemm_end, with_out_buffer=one)
-        backend_kwargs.update(flat_params=group.arena_tensor(), bf16_params=group.mirror_tensor())
-        transport = NvSwitchTransport(group, ONE_SHOT if one else TWO_SHOT)
+        plan = FaultPlan.parse(cfg.faults) if cfg.faults else FaultPlan.from_env()
+        coord = _coordinator(cfg, rank, world)
+        if cfg.transport == "nvswitch-bf16":
+            xgroup = p2p.PeerGroup(rank, world, layout.total, 0, arena_dtype=torch.bfloat16)
+            transport = NvSwitchBf16Transport(xgroup, coord, plan, ccfg.client_id)
+        else:
+            one = cfg.transport == "nvswitch-oneshot"
+            group = None
+            if cfg.transport in ("nvls", "auto"):
+                # symmetric memory (allocator + handle exchange only) also carries the NVLink multicast mapping
+                try:
+                    group = p2p.SymmPeerGroup(rank, world, layout.total, layout.gemm_end)
+                except Exception as e:  # noqa: BLE001
+                    if rank == 0:
+                        print(f"[launch] symmetric-memory group unavailable ({e!r}); using cudaMalloc + IPC (two-shot)",
+                              file=sys.stderr)
+                if group is not None and cfg.transport == "nvls" and not group.has_nvls and rank == 0:
+                    print("[launch] this host exposes no NVLink multicast: --transport nvls runs the two-shot kernel",
+                          file=sys.stderr)
+            if group is None:
+                group = p2p.PeerGroup(rank, world, layout.total, layout.gemm_end, with_out_buffer=one)
+            backend_kwargs.update(flat_params=group.arena_tensor(), bf16_params=group.mirror_tensor())
+            mode = {"nvswitch": p2p.TWO_SHOT, "nvswitch-oneshot": p2p.ONE_SHOT, "nvls": p2p.NVLS, "auto": AUTO}[cfg.transport]
+            transport = NvSwitchTransport(group, mode, coordinator=coord, faults=plan, client_id=ccfg.client_id)
     elif world > 1 and use_cuda and cfg.transport == "nccl":
         transport = NcclTransport()
     elif world > 1:
-        transport = _GlooTransport()
+        from ..utils.faults import FaultPlan
+
+        plan = FaultPlan.parse(cfg.faults) if cfg.faults else FaultPlan.from_env()
+        transport = _StoreTransport(_coordinator(cfg, rank, world), rank, plan, ccfg.client_id)
     else:
         transport = LoopbackTransport(1)
     try:
@@ -92,17 +118,41 @@ def launch(cfg: FedConfig) -> None:
             dist.destroy_process_group()
 
 
-class _GlooTransport(Transport):
-    """CPU multi-process FedAvg (plumbing tier, no GPU): gather state_dicts on every rank, average with the
-    reference's arithmetic in client order."""
-    name = "gloo"
+def _coordinator(cfg: FedConfig, rank: int, world: int) -> RoundCoordinator:
+    """Round agreement over the job's rendezvous store (owned by the launcher process, not by any client)."""
+    import torch.distributed as dist
+    from torch.distributed import distributed_c10d as c10d
+
+    store = dist.PrefixStore("dcad_rounds", c10d._get_default_store())
+    deadline = cfg.round_timeout if cfg.round_timeout is not None else cfg.timeout
+    return RoundCoordinator(store, rank, world, deadline_s=deadline, min_clients=cfg.min_clients)
+
+
+class _StoreTransport(Transport):
+    """CPU multi-process FedAvg (plumbing tier, no GPU): the participants of a round (fed/rounds.py: deadline +
+    quorum, so a client that sits the round out does not block the others) publish their state_dicts in the
+    rendezvous store and every participant averages them with the reference's arithmetic in client order."""
+    name = "store"
+
+    def __init__(self, coordinator: RoundCoordinator, rank: int, faults=None, client_id: int = 0):
+        self.coord, self.rank, self.faults, self.client_id = coordinator, rank, faults, client_id
+        self.round_idx = 0
 
     def aggregate(self, backend) -> bool:
-        import torch.distributed as dist
+        import io
 
         from ..parallel.fedavg import fedavg_state_dicts_cpu
 
-        sds = [None] * dist.get_world_size()
-        dist.all_gather_object(sds, {k: v.cpu() for k, v in backend.state_dict().items()})
+        rnd, self.round_idx = self.round_idx, self.round_idx + 1
+        take_part = not (self.faults and not self.faults.before_upload(self.client_id, rnd))
+        store = self.coord.store
+        if take_part:
+            buf = io.BytesIO()
+            torch.save({k: v.cpu() for k, v in backend.state_dict().items()}, buf)
+            store.set(f"sd/r{rnd}/{self.rank}", buf.getvalue())
+        members = self.coord.agree(rnd, take_part=take_part)
+        if members is None:
+            return False
+        sds = [torch.load(io.BytesIO(store.get(f"sd/r{rnd}/{m}")), weights_only=True) for m in members]
         backend.load_state_dict(fedavg_state_dicts_cpu(sds))
         return True

@@ -1,7 +1,13 @@
 """Aggregation transports behind one interface: ``aggregate(backend) -> bool`` makes the backend's parameters the
-FedAvg of all clients' parameters (True on success).
+FedAvg of all clients' parameters (True on success).  ``aggregate_async(backend)`` starts the same round and returns a
+handle whose ``wait()`` gives the result: the NVSwitch transports launch their kernel on a side stream and return at
+once, so the caller can stage the next round's batches and write the local round's files while the GPUs average
+(BASELINE config 3; the reference is strictly serial, server.py:116-137 / client1.py:391-395).
 
-    NvSwitchTransport   product path: peer-memory kernel over NVLink/NVSwitch (parallel/p2p.py), in place, no NCCL
+    NvSwitchTransport   product path: peer-memory kernel over NVLink/NVSwitch (parallel/p2p.py), in place, no NCCL;
+                        two-shot P2P, one-shot, or NVLS multimem (auto: NVLS from 4 clients up when the host has
+                        NVLink multicast); deadline + quorum through fed/rounds.py
+    NvSwitchBf16Transport  same, exchanging bf16 copies of the parameters (half the NVLink bytes)
     NcclTransport       measured baseline: ncclAllReduce + scale + cast
     SocketTransport     cross-host fallback: the reference's wire protocol (parallel/socket_transport.py)
     LoopbackTransport   in-process fake for tests: N backends in one process, CPU arithmetic of the reference
@@ -48,26 +54,147 @@ class SocketTransport(Transport):
         return True
 
 
+class Pending:
+    """Result of ``aggregate_async``: ``wait()`` blocks until the round is over and returns its success."""
+
+    def __init__(self, result: Optional[bool] = None, finish=None):
+        self._result, self._finish = result, finish
+
+    def wait(self) -> bool:
+        if self._result is None:
+            self._result = bool(self._finish())
+            self._finish = None
+        return self._result
+
+
+def _aggregate_async_default(self, backend) -> Pending:
+    return Pending(self.aggregate(backend))
+
+
+Transport.aggregate_async = _aggregate_async_default  # transports without a device-side round run it synchronously
+
+AUTO = -1  # NvSwitchTransport mode: NVLS when the group has a multicast mapping and >= 4 clients, else two-shot
+
+
 class NvSwitchTransport(Transport):
-    """The backend's engine must have been built on ``group.arena_tensor()`` / ``group.mirror_tensor()``."""
+    """The backend's engine must have been built on ``group.arena_tensor()`` / ``group.mirror_tensor()``.
+
+    ``coordinator`` (fed/rounds.RoundCoordinator): every round first agrees on the participants (deadline + quorum), so
+    a client that died or straggles costs the others one deadline instead of the round; without it every rank of the
+    group is expected (bench, tests).  ``faults`` (utils/faults.FaultPlan) can make this client sit rounds out."""
     name = "nvswitch"
 
-    def __init__(self, group, mode: int = 0, weights: Optional[Sequence[float]] = None):
+    def __init__(self, group, mode: int = 0, weights: Optional[Sequence[float]] = None, coordinator=None,
+                 faults=None, client_id: int = 0, local_cast: bool = True, log: Optional[EventLog] = None):
         self.group, self.mode, self.weights = group, mode, weights
+        self.coordinator, self.faults, self.client_id = coordinator, faults, client_id
+        self.local_cast, self.log = local_cast, log
+        self.round_idx = 0
+        self._stream: Optional[torch.cuda.Stream] = None
+        self.last_members: Optional[List[int]] = None
+
+    def resolved_mode(self, n_members: int) -> int:
+        from ..parallel.p2p import NVLS, TWO_SHOT
+
+        if self.mode != AUTO:
+            return self.mode
+        full = n_members == self.group.world
+        # measured (profiles/README.md): two-shot wins at 2 GPUs (0.52 vs 0.84 ms), NVLS from 4 up (0.73 vs 0.95 at 8)
+        return NVLS if (getattr(self.group, "has_nvls", False) and full and n_members >= 4) else TWO_SHOT
+
+    def aggregate_async(self, backend) -> Pending:
+        rnd, self.round_idx = self.round_idx, self.round_idx + 1
+        take_part = not (self.faults and not self.faults.before_upload(self.client_id, rnd))
+        members = None
+        if self.coordinator is not None:
+            members = self.coordinator.agree(rnd, take_part=take_part)
+            if self.log is not None:
+                self.log.event("round_members", round=rnd + 1, members=members, waited_s=self.coordinator.last_wait_s)
+            if members is None:
+                return Pending(False)
+        elif not take_part:
+            return Pending(False)
+        self.last_members = members
+        n = len(members) if members is not None else self.group.world
+        mode = self.resolved_mode(n)
+        weights = self.weights
+        if weights is not None and members is not None and len(weights) != n:
+            tot = float(sum(weights[m] for m in members))
+            weights = [weights[m] / tot for m in members]
+        cur = torch.cuda.current_stream()
+        if self._stream is None:
+            self._stream = torch.cuda.Stream()
+        side = self._stream
+        side.wait_stream(cur)  # local training (and the state_dict snapshot taken for the local files) precede the round
+        kw = dict(weights=weights, participants=members, epoch=rnd + 1, stream=side)
+        if hasattr(self.group, "multicast_ptr"):
+            kw["local_cast"] = self.local_cast
+        t_launch = torch.cuda.Event(enable_timing=True)
+        t_done = torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(side):
+            t_launch.record(side)
+            self.group.fedavg(mode, **kw)
+            t_done.record(side)
+
+        def finish() -> bool:
+            torch.cuda.current_stream().wait_event(t_done)  # whatever the caller enqueues next sees the averaged model
+            t_done.synchronize()
+            self.last_round_ms = t_launch.elapsed_time(t_done)
+            if self.group.error_flag():
+                return False
+            if mode == 1:  # one-shot wrote the separate output buffer: adopt it
+                eng = backend.engine
+                eng.arena.flat.copy_(self.group.out_tensor())
+                eng.refresh_bf16()
+            return True
+
+        return Pending(None, finish)
 
     def aggregate(self, backend) -> bool:
-        self.group.fedavg(self.mode, weights=self.weights)
-        torch.cuda.current_stream().synchronize()
-        if self.group.error_flag():
-            return False
-        if self.mode == 1:  # one-shot wrote the separate output buffer: adopt it
-            eng = backend.engine
-            eng.arena.flat.copy_(self.group.out_tensor())
-            eng.refresh_bf16()
-        return True
+        return self.aggregate_async(backend).wait()
 
     def close(self) -> None:
         self.group.close()
+
+
+class NvSwitchBf16Transport(Transport):
+    """bf16 parameter exchange (BASELINE configs 3 and 5): every client casts its fp32 master arena into a bf16
+    exchange arena in peer memory, the two-shot kernel averages those (fp32 accumulation, one rounding of the mean),
+    and the mean is cast back into the fp32 master arena and the bf16 compute copy.  Half the NVLink bytes of the fp32
+    round; the price is that the averaged master weights carry bf16 precision (8 mantissa bits) after every round --
+    the reference averages in fp32 (server.py:73-76), so this is an opt-in (``--transport nvswitch-bf16``)."""
+    name = "nvswitch-bf16"
+
+    def __init__(self, xgroup, coordinator=None, faults=None, client_id: int = 0, log: Optional[EventLog] = None):
+        self.xgroup, self.coordinator, self.faults, self.client_id, self.log = xgroup, coordinator, faults, client_id, log
+        self.round_idx = 0
+
+    def aggregate(self, backend) -> bool:
+        from ..ops import native as nv
+        from ..parallel.p2p import TWO_SHOT
+
+        rnd, self.round_idx = self.round_idx, self.round_idx + 1
+        take_part = not (self.faults and not self.faults.before_upload(self.client_id, rnd))
+        members = None
+        if self.coordinator is not None:
+            members = self.coordinator.agree(rnd, take_part=take_part)
+            if members is None:
+                return False
+        elif not take_part:
+            return False
+        eng = backend.engine
+        x = self.xgroup.arena_tensor()                       # bf16 [total]
+        nv.cast_f32_bf16(eng.arena.flat, x)
+        self.xgroup.fedavg(TWO_SHOT, participants=members, with_mirror=False, epoch=rnd + 1)
+        torch.cuda.current_stream().synchronize()
+        if self.xgroup.error_flag():
+            return False
+        eng.arena.flat.copy_(x)                              # bf16 -> fp32 master weights
+        eng.arena.bf16.copy_(x[: eng.arena.layout.gemm_end])
+        return True
+
+    def close(self) -> None:
+        self.xgroup.close()
 
 
 class NvSwitchDPTransport(Transport):

@@ -75,13 +75,17 @@ class PeerGroup:
 
     def fedavg(self, mode: int = TWO_SHOT, weights: Optional[Sequence[float]] = None,
                participants: Optional[Sequence[int]] = None, with_mirror: bool = True, max_ctas: int = 0,
-               stream=None) -> None:
+               stream=None, epoch: Optional[int] = None) -> None:
         """Launch this rank's share of the aggregation (all participating ranks must call it).  In place for two-shot;
-        one-shot writes the ``out`` buffer.  ``participants`` restricts the average to a subset (quorum)."""
+        one-shot writes the ``out`` buffer.  ``participants`` restricts the average to a subset (quorum).  ``epoch``
+        (strictly increasing, the same on every participant — e.g. the round number + 1) replaces the group's own
+        launch counter, which drifts apart when a client sits a round out."""
         ranks = list(range(self.world)) if participants is None else list(participants)
         if self.rank not in ranks:
             return
-        self.epoch += 1
+        if mode == NVLS:
+            mode = TWO_SHOT  # (this group has no multicast mapping)
+        self.epoch = self.epoch + 1 if epoch is None else int(epoch)
         sel = lambda lst: [lst[r] for r in ranks]  # noqa: E731
         nv.fedavg_p2p(sel(self.arena_ptrs), sel(self.pad_ptrs), ranks.index(self.rank), self.arena_elems, self.epoch,
                       out_ptrs=sel(self.out_ptrs) if mode == ONE_SHOT else None,
@@ -156,15 +160,32 @@ class SymmPeerGroup:
         return None
 
     def fedavg(self, mode: int = NVLS, weights: Optional[Sequence[float]] = None, with_mirror: bool = True,
-               max_ctas: int = 0, stream=None) -> None:
-        self.epoch += 1
-        if mode == NVLS and self.has_nvls and weights is None:
-            nv.fedavg_nvls(self.multicast_ptr, self.multicast_ptr + self._mirror_off if with_mirror else 0,
+               max_ctas: int = 0, stream=None, participants: Optional[Sequence[int]] = None,
+               epoch: Optional[int] = None, local_cast: bool = False) -> None:
+        """``mode`` NVLS: in-switch reduction (all ranks, unweighted); it falls back to the two-shot kernel over the
+        unicast peer pointers when the host has no multicast, when per-client weights are given, or when only a
+        subset of the clients takes part (the multicast mapping always spans every rank).
+
+        ``local_cast`` (NVLS only): the kernel averages the fp32 arena alone and every GPU then derives its bf16
+        compute copy from its own arena with a local cast kernel, instead of every rank multicasting the bf16 copy of
+        its shard to all others -- (N-1)/N x 85 MB less NVLink ingress per GPU for 255 MB of local HBM traffic."""
+        ranks = list(range(self.world)) if participants is None else list(participants)
+        if self.rank not in ranks:
+            return
+        self.epoch = self.epoch + 1 if epoch is None else int(epoch)
+        full = len(ranks) == self.world
+        if mode == NVLS and self.has_nvls and weights is None and full:
+            bcast_mirror = with_mirror and not local_cast
+            nv.fedavg_nvls(self.multicast_ptr, self.multicast_ptr + self._mirror_off if bcast_mirror else 0,
                            self.pad_ptrs, self.rank, self.arena_elems, self.epoch, bf16_begin=0,
-                           bf16_end=self.mirror_elems if with_mirror else 0, max_ctas=max_ctas, stream=stream)
+                           bf16_end=self.mirror_elems if bcast_mirror else 0, max_ctas=max_ctas, stream=stream)
+            if with_mirror and local_cast and self.mirror_elems:
+                # stream-ordered behind the kernel, whose end handshake means every rank's shard has landed here
+                nv.cast_f32_bf16(self.arena_tensor()[: self.mirror_elems], self.mirror_tensor(), stream=stream)
         else:
-            nv.fedavg_p2p(self.arena_ptrs, self.pad_ptrs, self.rank, self.arena_elems, self.epoch,
-                          mirror_ptrs=self.mirror_ptrs if (with_mirror and self.mirror_elems) else None,
+            sel = lambda lst: [lst[r] for r in ranks]  # noqa: E731
+            nv.fedavg_p2p(sel(self.arena_ptrs), sel(self.pad_ptrs), ranks.index(self.rank), self.arena_elems, self.epoch,
+                          mirror_ptrs=sel(self.mirror_ptrs) if (with_mirror and self.mirror_elems) else None,
                           weights=weights, mode=TWO_SHOT, bf16_begin=0,
                           bf16_end=self.mirror_elems if with_mirror else 0, max_ctas=max_ctas, stream=stream)
 
