@@ -22,6 +22,8 @@ class FedConfig:
     transport: str = "socket"          # auto (NVLS from 4 GPUs up, else two-shot) | nvswitch (two-shot) | nvswitch-oneshot |
                                        # nvls | nvswitch-bf16 (bf16 exchange) | nccl (baseline) | socket | none
     gpus_per_client: int = 1
+    overlap_rounds: bool = True        # start the aggregation asynchronously and write the local round's files / stage
+                                       # the next round's first epoch while it runs (BASELINE config 3)
     # training (reference literals)
     local_epochs: int = 3
     batch_size: int = 16

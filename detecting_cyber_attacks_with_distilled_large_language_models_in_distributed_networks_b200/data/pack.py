@@ -73,3 +73,47 @@ def iterate_batches(split: PackedSplit, batch_size: int, shuffle: bool = False,
         else:
             ix = perm[s:e]
             yield split.input_ids[ix], split.lens[ix], split.labels[ix]
+
+
+@dataclass
+class StagedEpoch:
+    """One shuffled epoch laid out for the step engine: ``steps[i]`` is the packed input record of full batch ``i``
+    (``ids[B*S] | lens[B] | labels[B]``, int32 — the layout of ``B200Engine.d_in``), ``tail`` the ragged last batch."""
+    steps: torch.Tensor                                               # [n_full, B*S + 2*B] int32
+    tail: Optional[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]]   # (ids [b,S], lens [b], labels [b]) or None
+
+    def __len__(self) -> int:
+        return int(self.steps.shape[0]) + (1 if self.tail is not None else 0)
+
+
+def stage_shuffled_epoch(split: PackedSplit, batch_size: int, generator: Optional[torch.Generator] = None,
+                         rank: int = 0, world: int = 1) -> StagedEpoch:
+    """Draws the epoch's permutation (the same draw ``iterate_batches(shuffle=True)`` makes) and gathers the WHOLE
+    epoch once: one gather per epoch and one small device copy per step instead of a gather and three copies per step
+    (the reference re-tokenises every sample every epoch, client1.py:36-45).  The gather is what is staged for the
+    next round while a federated aggregation is in flight.
+
+    ``world > 1`` (data-parallel client): every GPU draws the same permutation; global step ``i`` covers
+    ``world * batch_size`` consecutive samples of it and GPU ``rank`` takes its ``batch_size`` slice.  The ragged
+    remainder of the epoch is then shared out as one smaller last step of equal size per GPU (at most ``world - 1``
+    samples are left over), so every GPU runs the same number of steps."""
+    n, S = len(split), split.seq_len
+    dev = split.input_ids.device
+    if generator is not None and generator.device != dev:
+        perm = torch.randperm(n, generator=generator).to(dev)
+    else:
+        perm = torch.randperm(n, generator=generator, device=dev)
+    per_step = batch_size * world
+    n_full = n // per_step
+    ix = perm[: n_full * per_step].view(n_full, world, batch_size)[:, rank, :].reshape(-1)
+    steps = torch.empty(n_full, batch_size * S + 2 * batch_size, dtype=torch.int32, device=dev)
+    steps[:, : batch_size * S] = split.input_ids[ix].view(n_full, batch_size * S)
+    steps[:, batch_size * S: batch_size * S + batch_size] = split.lens[ix].view(n_full, batch_size)
+    steps[:, batch_size * S + batch_size:] = split.labels[ix].view(n_full, batch_size)
+    tail = None
+    rest = perm[n_full * per_step:]
+    b = int(rest.numel()) // world
+    if b > 0:
+        tx = rest[rank * b: (rank + 1) * b]
+        tail = (split.input_ids[tx], split.lens[tx], split.labels[tx])
+    return StagedEpoch(steps, tail)

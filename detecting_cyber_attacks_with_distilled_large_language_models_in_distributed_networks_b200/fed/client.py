@@ -1,15 +1,18 @@
 """A federated client, start to finish — the parametrised replacement for the copy-pasted ``client1.py`` /
 ``client2.py`` (reference ``main`` client1.py:353-411; call stack in SURVEY.md §3.1).
 
-Per round: train locally -> evaluate (val, test) -> write ``clientN_local_metrics.csv`` -> save ``clientN_model.pth`` ->
-aggregate through the configured transport -> evaluate the aggregated model -> ``clientN_aggregated_metrics.csv`` ->
-plots -> save again.  File names, CSV schema, plot names and the resume-from-``clientN_model.pth`` behaviour match the
+Per round: train locally -> evaluate (val, test) -> START the aggregation (``transport.aggregate_async``: on the
+NVSwitch path the kernel runs on a side stream) and, while it is in flight, write ``clientN_local_metrics.csv`` and
+``clientN_model.pth`` and stage the next round's first shuffled epoch -> wait for the aggregation -> evaluate the
+aggregated model -> ``clientN_aggregated_metrics.csv`` -> plots -> save again.  (The reference does all of it
+strictly one after the other, client1.py:383-403; ``--no-overlap-rounds`` restores that order.)  File names, CSV schema, plot names and the resume-from-``clientN_model.pth`` behaviour match the
 reference; with ``rounds > 1`` later rounds add a ``_roundK`` suffix (the reference is single-round).  Degraded paths
 are kept: if aggregation fails the client still plots its local results (client1.py:405-410).
 """
 from __future__ import annotations
 
 import os
+import time
 from typing import Dict, Optional, Tuple
 
 import torch
@@ -22,7 +25,7 @@ from ..data.tokenizer import WordPieceTokenizer
 from ..report.log import EventLog
 from ..report.metrics import EvalResult, save_metrics
 from ..report.plots import plot_evaluation
-from ..train.trainer import evaluate_model, make_backend, train_model
+from ..train.trainer import evaluate_model, make_backend, stage_first_epoch, train_model
 from .transport import Transport
 
 
@@ -89,28 +92,51 @@ def run_client(cfg: FedConfig, transport: Optional[Transport] = None, backend=No
         log.say(f"resumed full training state from {state_path}: {first_round} round(s) already done")
 
     results: Dict[str, EvalResult] = {}
+    prestaged = None
     for rnd in range(first_round, cfg.rounds):
         sfx = "" if rnd == 0 else f"_round{rnd + 1}"
-        train_model(backend, train, cfg.local_epochs, seed=cfg.resolved_seed() + 1000 * rnd, log=log, name=name)
-        sd = backend.state_dict()  # (collective inside a data-parallel client group)
-        local = None
+        train_model(backend, train, cfg.local_epochs, seed=cfg.resolved_seed() + 1000 * rnd, log=log, name=name,
+                    prestaged=prestaged)
+        prestaged = None
+        sd = backend.state_dict()  # (collective inside a data-parallel client group); a snapshot, not a view
+        local = val_local = None
         if reporter:
             print(f"{name} evaluating local model on validation set...")
             val_local = evaluate_model(backend, val, log, name, want_probs=False)
             print(f"{name} evaluating local model on test set...")
             local = evaluate_model(backend, test, log, name, want_probs=cfg.extra_curves)
+            results[f"local{sfx}"] = local
+
+        def write_local_files() -> None:
+            if not reporter:
+                return
             save_metrics(local, out(f"client{cid}_local_metrics{sfx}.csv"))
             if cfg.save_val_metrics:
                 save_metrics(val_local, out(f"client{cid}_local_val_metrics{sfx}.csv"))
             torch.save(sd, model_path)
-            results[f"local{sfx}"] = local
-        del sd
 
         aggregated: Optional[EvalResult] = None
         ok = False
-        if transport is not None:
-            with log.phase("federated aggregation", transport=transport.name, round=rnd + 1):
-                ok = transport.aggregate(backend)
+        if transport is not None and cfg.overlap_rounds:
+            with log.phase("federated aggregation", transport=transport.name, round=rnd + 1, overlapped=True) as ex:
+                t0 = time.perf_counter()
+                pending = transport.aggregate_async(backend)   # NVSwitch: the kernel is now running on a side stream
+                ex["launched_after_s"] = time.perf_counter() - t0
+                # ---- work that does not depend on the aggregated model, done while the GPUs average ----
+                write_local_files()
+                if rnd + 1 < cfg.rounds and hasattr(backend, "stage_epoch"):
+                    prestaged = stage_first_epoch(backend, train, cfg.resolved_seed() + 1000 * (rnd + 1))
+                ex["overlapped_host_s"] = time.perf_counter() - t0
+                ok = pending.wait()
+                ex["total_s"] = time.perf_counter() - t0
+                if getattr(transport, "last_round_ms", None) is not None:
+                    ex["device_round_ms"] = transport.last_round_ms
+        else:
+            write_local_files()
+            if transport is not None:
+                with log.phase("federated aggregation", transport=transport.name, round=rnd + 1):
+                    ok = transport.aggregate(backend)
+        del sd
         if ok and not reporter:
             backend.state_dict()  # keep the collective call pattern of the reporter
         if ok and reporter:

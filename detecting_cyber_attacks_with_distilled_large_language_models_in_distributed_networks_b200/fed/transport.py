@@ -68,10 +68,12 @@ class Pending:
 
 
 def _aggregate_async_default(self, backend) -> Pending:
-    return Pending(self.aggregate(backend))
+    # transports without a device-side round have nothing to overlap: the round runs inside wait(), i.e. after the
+    # caller has written the local model's files (the round replaces the parameters those files describe)
+    return Pending(None, lambda: self.aggregate(backend))
 
 
-Transport.aggregate_async = _aggregate_async_default  # transports without a device-side round run it synchronously
+Transport.aggregate_async = _aggregate_async_default
 
 AUTO = -1  # NvSwitchTransport mode: NVLS when the group has a multicast mapping and >= 4 clients, else two-shot
 

@@ -18,7 +18,7 @@ from typing import List, Optional
 import torch
 import torch.nn as nn
 
-from ..data.pack import PackedSplit, iterate_batches
+from ..data.pack import PackedSplit, StagedEpoch, iterate_batches, stage_shuffled_epoch
 from ..models.arena import ModelDims
 from ..ops import native as nv
 from ..report.log import EventLog
@@ -49,10 +49,23 @@ class TorchBackend:
     def _mask(ids: torch.Tensor, lens: torch.Tensor) -> torch.Tensor:
         return (torch.arange(ids.shape[1], device=ids.device)[None, :] < lens[:, None]).long()
 
-    def train_epoch(self, split: PackedSplit, generator: Optional[torch.Generator]) -> float:
+    def stage_epoch(self, split: PackedSplit, generator: Optional[torch.Generator]) -> StagedEpoch:
+        return stage_shuffled_epoch(split, self.B, generator)
+
+    def _staged_batches(self, st: StagedEpoch):
+        B, S = self.B, self.S
+        for rec in st.steps:
+            yield rec[: B * S].view(B, S), rec[B * S: B * S + B], rec[B * S + B:]
+        if st.tail is not None:
+            yield st.tail
+
+    def train_epoch(self, split: PackedSplit, generator: Optional[torch.Generator],
+                    staged: Optional[StagedEpoch] = None) -> float:
         self.model.train()
         total, nb = 0.0, 0
-        for ids, lens, labels in iterate_batches(split, self.B, shuffle=True, generator=generator):
+        batches = (self._staged_batches(staged) if staged is not None
+                   else iterate_batches(split, self.B, shuffle=True, generator=generator))
+        for ids, lens, labels in batches:
             ids, lens, labels = ids.to(self.device), lens.to(self.device), labels.to(self.device)
             self.opt.zero_grad()
             loss = self.crit(self.model(ids.long(), self._mask(ids, lens)), labels.long())
@@ -107,34 +120,27 @@ class B200Backend:
     def load_state_dict(self, sd) -> None:
         self.engine.load_state_dict(sd)
 
-    def train_epoch(self, split: PackedSplit, generator: Optional[torch.Generator]) -> float:
+    def stage_epoch(self, split: PackedSplit, generator: Optional[torch.Generator]) -> StagedEpoch:
+        """Shuffles and gathers one epoch of ``split`` into per-step input records (device-resident).  Separate from
+        ``train_epoch`` so that the next round's first epoch can be staged while a federated aggregation is in
+        flight."""
+        rank, world = (self.dp.rank, self.dp.world) if self.dp is not None else (0, 1)
+        return stage_shuffled_epoch(split, self.B, generator, rank, world)
+
+    def train_epoch(self, split: PackedSplit, generator: Optional[torch.Generator],
+                    staged: Optional[StagedEpoch] = None) -> float:
+        """One pass over ``split``.  Per step: ONE device copy of the staged input record into the engine's static
+        input buffer, then the captured graph — the same work per step as ``bench.py``'s loop.  A data-parallel
+        client keeps the ragged end of the epoch (an equal smaller last step on every GPU)."""
         eng = self.engine
         eng.loss_accum.zero_()
-        if self.dp is not None:
-            return self._train_epoch_dp(split, generator)
-        for ids, lens, labels in iterate_batches(split, self.B, shuffle=True, generator=generator):
-            if ids.shape[0] == self.B:
-                eng.set_batch(ids, lens, labels)
-                eng.train_step()
-            else:  # ragged tail batch: pad by repeating rows is wrong for the mean loss; run a smaller eager step
-                self._tail_step(ids, lens, labels)
-        loss, _ = eng.read_loss()
-        return loss
-
-    def _train_epoch_dp(self, split: PackedSplit, generator: Optional[torch.Generator]) -> float:
-        """Data-parallel client: the G GPUs draw the SAME permutation (same seed) and GPU r takes every G-th batch
-        slot, so a global step consumes G*B distinct samples.  All GPUs must run the same number of steps (the step
-        contains cross-GPU barriers), so the ragged tail of the epoch is dropped."""
-        eng, dp = self.engine, self.dp
-        n = len(split)
-        dev = split.input_ids.device
-        perm = torch.randperm(n, generator=generator).to(dev)
-        per_step = self.B * dp.world
-        steps = n // per_step
-        for i in range(steps):
-            ix = perm[i * per_step + dp.rank * self.B: i * per_step + (dp.rank + 1) * self.B]
-            eng.set_batch(split.input_ids[ix], split.lens[ix], split.labels[ix])
+        if staged is None:
+            staged = self.stage_epoch(split, generator)
+        for i in range(staged.steps.shape[0]):
+            eng.d_in.copy_(staged.steps[i])
             eng.train_step()
+        if staged.tail is not None:  # DataLoader drop_last=False in the reference: a smaller eager step
+            self._tail_step(*staged.tail)
         loss, _ = eng.read_loss()
         return loss
 
@@ -149,7 +155,7 @@ class B200Backend:
         if b not in cache:
             main = self.engine
             e = B200Engine(self.dims, b, self.S, main.device, lr=main.lr, betas=main.betas, eps=main.eps,
-                           flat_params=main.arena.flat, bf16_params=main.arena.bf16, init_seed=None)
+                           flat_params=main.arena.flat, bf16_params=main.arena.bf16, init_seed=None, dp=self.dp)
             e.arena.grad, e.arena.exp_avg, e.arena.exp_avg_sq = main.arena.grad, main.arena.exp_avg, main.arena.exp_avg_sq
             e.rng, e.loss_accum = main.rng, main.loss_accum
             e.touched_rows = main.touched_rows  # part of the optimizer state (which vocabulary rows have moments)
@@ -191,17 +197,31 @@ def make_backend(prefer: str = "auto", **kw):
     return B200Backend(**kw)
 
 
-def train_model(backend, train_split: PackedSplit, num_epochs: int = 3, seed: int = 0,
-                log: Optional[EventLog] = None, name: str = "Client 1") -> List[float]:
-    """Reference ``train_model``: ``num_epochs`` passes, prints ``Average Loss`` per epoch; returns those losses."""
-    log = log or EventLog(name.upper(), quiet=True)
+def stage_first_epoch(backend, train_split: PackedSplit, seed: int):
+    """Staging of a round's first epoch ahead of time (while the previous round's aggregation runs): returns what
+    ``train_model(..., prestaged=...)`` expects.  Draws from the same seeded generator ``train_model`` would create,
+    so the batches are identical to an un-staged run."""
     gen = torch.Generator(device="cpu").manual_seed(seed)
+    split = train_split.to(backend.device)
+    return gen, backend.stage_epoch(split, gen)
+
+
+def train_model(backend, train_split: PackedSplit, num_epochs: int = 3, seed: int = 0,
+                log: Optional[EventLog] = None, name: str = "Client 1", prestaged=None) -> List[float]:
+    """Reference ``train_model``: ``num_epochs`` passes, prints ``Average Loss`` per epoch; returns those losses.
+    ``prestaged`` = ``stage_first_epoch(backend, train_split, seed)`` made earlier."""
+    log = log or EventLog(name.upper(), quiet=True)
+    if prestaged is not None:
+        gen, first = prestaged
+    else:
+        gen, first = torch.Generator(device="cpu").manual_seed(seed), None
     split = train_split.to(backend.device)
     losses = []
     with log.phase("model training", epochs=num_epochs, samples=len(split)):
         for ep in range(num_epochs):
             t0 = time.perf_counter()
-            loss = backend.train_epoch(split, gen)
+            loss = (backend.train_epoch(split, gen, staged=first) if (ep == 0 and first is not None)
+                    else backend.train_epoch(split, gen))
             dt = time.perf_counter() - t0
             losses.append(loss)
             print(f"{name} Epoch [{ep + 1}/{num_epochs}], Average Loss: {loss:.4f}", flush=True)

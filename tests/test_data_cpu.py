@@ -99,3 +99,36 @@ def test_pack_and_iterate():
     a = [b[2].tolist() for b in pack.iterate_batches(ps, 16, shuffle=True, generator=g1)]
     b = [b[2].tolist() for b in pack.iterate_batches(ps, 16, shuffle=True, generator=g2)]
     assert a == b  # seeded shuffling is reproducible (the reference's is not: SURVEY Q12)
+
+
+def test_staged_epoch_matches_iterate_batches_and_dp_slices():
+    """The once-per-epoch gather feeds the same batches in the same order as the per-step gather; a data-parallel
+    client's GPUs share one permutation, take disjoint slices and keep the ragged end as an equal smaller step."""
+    import torch
+
+    from detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200.data.pack import (
+        PackedSplit, iterate_batches, stage_shuffled_epoch)
+
+    n, S, B = 70, 8, 16
+    split = PackedSplit(torch.arange(n * S, dtype=torch.int32).view(n, S), torch.arange(n, dtype=torch.int32) % S + 1,
+                        torch.arange(n, dtype=torch.int32) % 2)
+    want = list(iterate_batches(split, B, shuffle=True, generator=torch.Generator().manual_seed(5)))
+    st = stage_shuffled_epoch(split, B, torch.Generator().manual_seed(5))
+    assert len(st) == len(want) == 5 and st.steps.shape == (4, B * S + 2 * B)
+    for i in range(4):
+        rec = st.steps[i]
+        assert torch.equal(rec[: B * S].view(B, S), want[i][0])
+        assert torch.equal(rec[B * S: B * S + B], want[i][1]) and torch.equal(rec[B * S + B:], want[i][2])
+    assert all(torch.equal(a, b) for a, b in zip(st.tail, want[4]))
+    # two GPUs of one client: 70 = 2 full global steps of 32 + 6 left -> a last step of 3 samples each
+    parts = [stage_shuffled_epoch(split, B, torch.Generator().manual_seed(5), rank=r, world=2) for r in range(2)]
+    perm = torch.randperm(n, generator=torch.Generator().manual_seed(5))
+    seen = []
+    for r, p in enumerate(parts):
+        assert p.steps.shape[0] == 2 and p.tail[0].shape[0] == 3
+        for i in range(2):
+            ids = p.steps[i][: B * S].view(B, S)
+            assert torch.equal(ids, split.input_ids[perm[i * 32 + r * B: i * 32 + (r + 1) * B]])
+            seen += (ids[:, 0] // S).tolist()
+        seen += (p.tail[0][:, 0] // S).tolist()
+    assert len(set(seen)) == len(seen) == 70
