@@ -83,9 +83,14 @@ def make_model_dir(path: str) -> str:
     return path
 
 
-def run(args, rank: int, world: int, local_rank: int):
+def run(args, rank: int, world: int, local_rank: int, amp: bool = False):
+    """``amp=False`` (the driver's reference arm): the stock reference, nothing changed.  ``amp=True`` is the secondary,
+    precision-matched arm of ``baseline/torch_amp_arm.py``: same model, data and ``train_model``, with the forward pass
+    run under ``torch.autocast(bfloat16)`` and TF32 allowed for what stays in fp32."""
+    impl = "reference-bf16-autocast" if amp else "reference"
+
     def unavailable(why: str):
-        return {"impl": "reference", "unavailable": why}  # bench.py prints it on rank 0 and exits 0
+        return {"impl": impl, "unavailable": why}  # bench.py prints it on rank 0 and exits 0
 
     if find_reference() is None:
         return unavailable("baseline/_ref/client1.py not found (run baseline/install_reference.sh)")
@@ -132,6 +137,18 @@ def run(args, rank: int, world: int, local_rank: int):
                 if nw > 0 else None)
         timed = DataLoader(ref.CICIDS2017Dataset(texts[nw:], labels[nw:], tokenizer), batch_size=B, shuffle=True)
         model = ref.DDoSClassifier(model_dir).to(device)                      # client1.py:374
+        if amp:
+            # bf16 tensor-core matmuls with fp32 master weights / Adam (the mixed precision this repository's engine
+            # uses): the reference's own forward under autocast; its train_model (loss, backward, Adam) is unchanged
+            torch.backends.cuda.matmul.allow_tf32 = True
+            torch.backends.cudnn.allow_tf32 = True
+            stock_forward = model.forward
+
+            def autocast_forward(*a, **k):
+                with torch.autocast(device_type=device.type, dtype=torch.bfloat16):
+                    return stock_forward(*a, **k).float()
+
+            model.forward = autocast_forward
         opt = torch.optim.Adam(model.parameters(), lr=2e-5)                   # client1.py:380
         crit = nn.CrossEntropyLoss()
 
@@ -171,13 +188,15 @@ def run(args, rank: int, world: int, local_rank: int):
         out = {
             "metric": "train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": value / (40.6 * world), "dtype": "fp32",
+            "scaling": "weak", "vs_baseline": value / (40.6 * world), "dtype": "bf16-autocast" if amp else "fp32",
             "data": "synthetic CICIDS-shaped flow sentences (reference features_to_text + HF tokenizer, synthetic "
                     "vocab), random-init weights",
-            "impl": "reference",
+            "impl": impl,
             "config": {"model": "reference DDoSClassifier (HF DistilBertModel + Linear(768,2))", "global_batch": B * world,
                        "per_client_batch": B, "seq_len": 128, "parallelism": f"fed{world} (independent clients)",
-                       "path": "client1.train_model, stock DataLoader/tokenizer/Adam, fp32 (no TF32/AMP)"},
+                       "path": ("client1.train_model, stock DataLoader/tokenizer/Adam, forward under "
+                                "torch.autocast(bfloat16), TF32 allowed" if amp else
+                                "client1.train_model, stock DataLoader/tokenizer/Adam, fp32 (no TF32/AMP)")},
             "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": B * 128 * 8 * 2 + B * 8,
                     "d2h_bytes_per_step": 8,
                     "note": "the reference's loop is end to end by construction (tokenise + H2D + 2x loss.item())"},

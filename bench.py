@@ -44,7 +44,9 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--impl", choices=["ours", "reference", "reference-amp"], default="ours")
+    ap.add_argument("--no-amp-arm", action="store_true",
+                    help="ours, 1 GPU: skip the in-process precision-matched reference arm (vs_reference_bf16_autocast)")
     ap.add_argument("--batch", type=int, default=16)
     ap.add_argument("--seq", type=int, default=128)
     ap.add_argument("--pool", type=int, default=8, help="distinct synthetic batches cycled through")
@@ -278,8 +280,32 @@ def main() -> None:
         import reference_arm
 
         out = reference_arm.run(args, rank, world, local_rank)
+    elif args.impl == "reference-amp":
+        sys.path.insert(0, os.path.join(ROOT, "baseline"))
+        import torch_amp_arm
+
+        out = torch_amp_arm.run(args, rank, world, local_rank)
     else:
         out = run_ours(args, rank, world, local_rank)
+        if world == 1 and not args.no_amp_arm and os.environ.get("DCAD_BENCH_AMP_ARM", "1") != "0":
+            # secondary arm, AFTER our own timed regions: the reference's model + train_model under bf16 autocast
+            try:
+                sys.path.insert(0, os.path.join(ROOT, "baseline"))
+                import torch_amp_arm
+
+                amp_args = argparse.Namespace(**vars(args))
+                amp_args.steps, amp_args.warmup = min(args.steps, 50), min(max(args.warmup, 3), 5)
+                amp = torch_amp_arm.run(amp_args, rank, world, local_rank)
+                if "value" in amp:
+                    out["reference_bf16_autocast"] = {"value": amp["value"], "unit": "samples/s",
+                                                      "ms_per_step": amp["ms_per_step"], "steps": amp_args.steps,
+                                                      "path": amp["config"]["path"]}
+                    out["vs_reference_bf16_autocast"] = out["value"] / amp["value"]
+                    out["e2e"]["vs_reference_bf16_autocast"] = out["e2e"]["value"] / amp["value"]
+                else:
+                    out["reference_bf16_autocast"] = {"unavailable": amp.get("unavailable")}
+            except Exception as e:  # noqa: BLE001
+                out["reference_bf16_autocast"] = {"unavailable": repr(e)[:200]}
     sys.stdout.flush()
     if rank == 0 and out is not None:
         print(json.dumps(out), file=json_out, flush=True)
