@@ -161,7 +161,10 @@ def run_ours(args, rank: int, world: int, local_rank: int) -> dict:
     out = {
         "metric": "train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": value / (PUBLISHED_SAMPLES_PER_S_PER_CLIENT * world), "dtype": "bf16",
+        "scaling": "weak", "vs_baseline": value / (PUBLISHED_SAMPLES_PER_S_PER_CLIENT * world),
+        # the same number under an honest name: BASELINE.md's only published throughput is 40.6 samples/s per client on
+        # an unspecified Windows PC; the ratio that means something is the driver's own-arm vs reference-arm one
+        "vs_published_unspecified_hw": value / (PUBLISHED_SAMPLES_PER_S_PER_CLIENT * world), "dtype": "bf16",
         "data": "synthetic CICIDS-shaped token batches (seq 128, ~84 real tokens + padding), random-init weights",
         "impl": "ours",
         "config": {"model": "DDoSClassifier (DistilBERT-base 6L/768d/12h + Linear(768,2)), 66.36M params",
@@ -225,8 +228,33 @@ def run_ours(args, rank: int, world: int, local_rank: int) -> dict:
             return max_over_ranks(e0.elapsed_time(e1) / iters)
 
         two_shot_ms = time_round(p2p.TWO_SHOT)
-        nvls_ms = time_round(p2p.NVLS) if getattr(group, "has_nvls", False) else None
-        fed_ms = min(two_shot_ms, nvls_ms) if nvls_ms is not None else two_shot_ms
+        has_nvls = getattr(group, "has_nvls", False)
+        nvls_ms = time_round(p2p.NVLS) if has_nvls else None   # every rank multicasts the bf16 copy of its shard
+
+        def time_round_local_cast():
+            for _ in range(3):
+                group.fedavg(p2p.NVLS, local_cast=True)
+            barrier()
+            e0.record()
+            for _ in range(iters):
+                group.fedavg(p2p.NVLS, local_cast=True)
+            e1.record()
+            torch.cuda.synchronize(dev)
+            return max_over_ranks(e0.elapsed_time(e1) / iters)
+
+        nvls_lc_ms = None
+        if has_nvls:
+            try:  # fp32 arena through the switch, bf16 copy cast locally by every GPU afterwards
+                nvls_lc_ms = time_round_local_cast()
+            except Exception as e:  # noqa: BLE001
+                out["fedavg_nvls_local_cast_error"] = repr(e)[:200]
+        cands = {"two_shot": two_shot_ms}
+        if nvls_ms is not None:
+            cands["nvls"] = nvls_ms
+        if nvls_lc_ms is not None:
+            cands["nvls_local_cast"] = nvls_lc_ms
+        best = min(cands, key=cands.get)
+        fed_ms = cands[best]
         err = group.error_flag()
         # NCCL all-reduce baseline on a scratch copy of the arena (same bytes), incl. the scale and the bf16 cast
         scratch = eng.arena.flat.clone()
@@ -240,30 +268,95 @@ def run_ours(args, rank: int, world: int, local_rank: int) -> dict:
         e1.record()
         torch.cuda.synchronize(dev)
         nccl_ms = max_over_ranks(e0.elapsed_time(e1) / iters)
+        del scratch, scratch_m
         bytes_arena = layout.total * 4
         bytes_mirror = layout.gemm_end * 2
-        use_nvls = nvls_ms is not None and nvls_ms <= two_shot_ms
         # bytes arriving at each GPU over NVLink.  two-shot: (N-1)/N of the arena pulled from peers + the peers' pushed
-        # shards with their bf16 copies.  NVLS: the switch-reduced own shard + the other ranks' multicast stores.
-        ingress_two_shot = (world - 1) / world * (2 * bytes_arena + bytes_mirror)
-        ingress_nvls = bytes_arena / world + (world - 1) / world * (bytes_arena + bytes_mirror)
-        ingress = ingress_nvls if use_nvls else ingress_two_shot
+        # shards with their bf16 copies.  NVLS: the switch-reduced own shard + the other ranks' multicast stores
+        # (without the bf16 copies when every GPU casts its own).
+        ingress = {
+            "two_shot": (world - 1) / world * (2 * bytes_arena + bytes_mirror),
+            "nvls": bytes_arena / world + (world - 1) / world * (bytes_arena + bytes_mirror),
+            "nvls_local_cast": bytes_arena / world + (world - 1) / world * bytes_arena,
+        }[best]
+        kernel_names = {"two_shot": "fedavg_p2p two-shot", "nvls": "fedavg_nvls (multimem.ld_reduce + multimem.st)",
+                        "nvls_local_cast": "fedavg_nvls (multimem.ld_reduce + multimem.st, fp32 arena) + local bf16 cast"}
         out["fedavg"] = {
             "round_latency_ms": fed_ms,
-            "kernel": ("fedavg_nvls (multimem.ld_reduce + multimem.st)" if use_nvls else "fedavg_p2p two-shot")
-                      + ", in place, fp32 arena 265.5 MB + fused bf16 mirror 85 MB",
-            "two_shot_ms": two_shot_ms, "nvls_ms": nvls_ms,
-            "nccl_allreduce_baseline_ms": nccl_ms, "handshake_error_flag": err,
+            "kernel": kernel_names[best] + ", in place, fp32 arena 265.5 MB + bf16 mirror 85 MB",
+            "two_shot_ms": two_shot_ms, "nvls_ms": nvls_ms, "nvls_local_cast_ms": nvls_lc_ms,
+            "nccl_allreduce_baseline_ms": nccl_ms, "vs_nccl_baseline": nccl_ms / fed_ms, "handshake_error_flag": err,
             "nvlink_ingress_bytes_per_gpu": ingress,
             "achieved_ingress_GBps": ingress / (fed_ms * 1e-3) / 1e9,
             "roofline_ms_at_770GBps_per_direction": ingress / 770e9 * 1e3,
-            "fraction_of_link_roofline": (ingress / 770e9 * 1e3) / fed_ms,
+            "fraction_of_link_roofline": (ingress / 770e9 * 1e3) / fed_ms,          # measured peer-copy bandwidth
+            "roofline_ms_at_900GBps_nominal": ingress / 900e9 * 1e3,
+            "fraction_of_link_roofline_900GBps_nominal": (ingress / 900e9 * 1e3) / fed_ms,
             "vs_published_socket_round": PUBLISHED_FEDAVG_ROUND_MS / fed_ms,
         }
+
+        # ---- a federated ROUND = K local steps + one FedAvg launch (the inter-GPU bytes inside the timed region) ----
+        try:
+            best_mode = {"two_shot": dict(mode=p2p.TWO_SHOT), "nvls": dict(mode=p2p.NVLS),
+                         "nvls_local_cast": dict(mode=p2p.NVLS, local_cast=True)}[best]
+            rounds_rec = {}
+            for K, R in ((1, 30), (8, 15), (847, 1)):   # 847 = the published epoch length (client1_terminal_output.txt:7)
+                def one_round(K=K):
+                    for i in range(K):
+                        eng.set_batch(*pool_d[i % args.pool])
+                        eng.train_step()
+                    group.fedavg(**best_mode)
+                one_round(min(K, 3))
+                barrier()
+                e0.record()
+                for _ in range(R):
+                    one_round()
+                e1.record()
+                torch.cuda.synchronize(dev)
+                ms_r = max_over_ranks(e0.elapsed_time(e1)) / R
+                rounds_rec[f"K{K}"] = {"local_steps": K, "rounds_timed": R, "ms_per_round": ms_r,
+                                       "samples_per_s": world * B * K / (ms_r / 1e3),
+                                       "efficiency_vs_no_aggregation": (K * ms / args.steps) / ms_r}
+            out["federated_round"] = {"what": "K graph-replayed local steps + one in-place FedAvg launch per round, "
+                                              "device-timed, max over ranks; value = whole-job samples/s",
+                                      "fedavg_kernel": kernel_names[best], **rounds_rec,
+                                      "handshake_error_flag": group.error_flag()}
+        except Exception as e:  # noqa: BLE001
+            out["federated_round"] = {"error": repr(e)[:300]}
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     return out
+
+
+def dp_child_record(args, rank: int, world: int, local_rank: int):
+    """The data-parallel configuration fed(N/G) x dpG (G = 2 at N = 2, else 4) measured in CHILD processes -- one per
+    rank, its own rendezvous port -- after this process has finished and printed nothing yet: a fault in that path
+    cannot cost the headline line.  Returns the child's record (rank 0) or None."""
+    import subprocess
+
+    G = 2 if world == 2 else 4
+    if world % G:
+        return None
+    env = dict(os.environ, DCAD_BENCH_CHILD="1", MASTER_PORT=str(int(os.environ.get("MASTER_PORT", "29500")) + 313))
+    # a rendezvous of their own: rank 0's child hosts a fresh TCPStore on the new port (the launcher's agent store
+    # still holds the keys of this process's own, already destroyed, process group)
+    env["TORCHELASTIC_USE_AGENT_STORE"] = "False"
+    cmd = [sys.executable, os.path.abspath(__file__), "--gpus", str(world), "--dp", str(G), "--steps", str(args.steps),
+           "--warmup", str(args.warmup), "--batch", str(args.batch), "--seq", str(args.seq)]
+    try:
+        r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=420)
+    except subprocess.TimeoutExpired:
+        return {"error": "timed out after 420 s"}
+    if rank != 0:
+        return None
+    for line in reversed(r.stdout.strip().splitlines()):
+        if line.startswith("{"):
+            try:
+                return json.loads(line)
+            except ValueError:
+                continue
+    return {"error": f"child exit {r.returncode}: {r.stderr[-300:]}"}
 
 
 def main() -> None:
@@ -287,7 +380,21 @@ def main() -> None:
         out = torch_amp_arm.run(args, rank, world, local_rank)
     else:
         out = run_ours(args, rank, world, local_rank)
-        if world == 1 and not args.no_amp_arm and os.environ.get("DCAD_BENCH_AMP_ARM", "1") != "0":
+        child = os.environ.get("DCAD_BENCH_CHILD") == "1"
+        if world > 1 and args.dp <= 1 and not child and os.environ.get("DCAD_BENCH_DP", "1") != "0":
+            rec = dp_child_record(args, rank, world, local_rank)
+            if rank == 0 and out is not None and rec is not None:
+                if "value" in rec:
+                    out["dp"] = {"parallelism": rec["config"]["parallelism"], "value": rec["value"], "unit": "samples/s",
+                                 "ms_per_step": rec["ms_per_step"], "global_batch": rec["config"]["global_batch"],
+                                 "dp_efficiency": rec["value"] / out["value"],
+                                 "efficiency_note": "samples/s of N GPUs as clients of G GPUs each / samples/s of N "
+                                                    "independent one-GPU clients (same per-GPU batch)",
+                                 "e2e_value": rec.get("e2e", {}).get("value"), "fedavg": rec.get("fedavg"),
+                                 "handshake_error_flag": rec.get("dp_handshake_error_flag")}
+                else:
+                    out["dp"] = rec
+        if world == 1 and not child and not args.no_amp_arm and os.environ.get("DCAD_BENCH_AMP_ARM", "1") != "0":
             # secondary arm, AFTER our own timed regions: the reference's model + train_model under bf16 autocast
             try:
                 sys.path.insert(0, os.path.join(ROOT, "baseline"))
