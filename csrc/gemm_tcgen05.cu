@@ -92,7 +92,7 @@ template <int BN, int CG = 1, int EPI = 0>
 struct GemmCfg {
     static constexpr int NSUB = BN > 256 ? 2 : 1;   // MMAs (accumulators) per k-step
     static constexpr int SUBN = BN / NSUB;          // UMMA N
-    static constexpr bool ALIAS = BN > 256;
+    static constexpr bool ALIAS = BN > 256 || EPI == 2;  // EPI 2: per-warp epilogue, staging always in the ring (deeper ring)
     static constexpr int ACC_STAGES = BN > 256 ? 1 : 2;
     static constexpr int NBUF = ALIAS ? 2 : 1;      // EPI 1: staging boxes per epilogue warp
     static constexpr int STAGING_TOTAL = EPI == 0 ? NUM_STAGING * STAGING_BYTES : EPI_WARPS * NBUF * BOX_BYTES;
@@ -108,7 +108,7 @@ struct GemmCfg {
     static constexpr int ACC_STRIDE = pow2_ceil(BN);  // TMEM columns per accumulator stage
     static constexpr int TMEM_COLS = ACC_STAGES * ACC_STRIDE;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + (ALIAS ? 0 : STAGING_TOTAL) + 1024;
-    static_assert(EPI == 1 || BN <= 256, "the 384-wide tile needs the per-warp epilogue");
+    static_assert(EPI >= 1 || BN <= 256, "the 384-wide tile needs the per-warp epilogue");
     static_assert(TMEM_COLS <= 512, "accumulators exceed the 512 TMEM columns");
     static_assert(!ALIAS || STAGES * STAGE_BYTES >= STAGING_TOTAL, "staging does not fit in the ring");
 };
@@ -802,13 +802,13 @@ static int g_gemm_epi = -1;
 static int gemm_epi_mode() {
     if (g_gemm_epi < 0) {
         const char* e = getenv("DCAD_GEMM_EPI");
-        g_gemm_epi = (e && e[0] == '1') ? 1 : 0;
+        g_gemm_epi = (e && e[0] == '1') ? 1 : ((e && e[0] == '2') ? 2 : 0);
     }
     return g_gemm_epi;
 }
 extern "C" int dcad_gemm_set_epilogue(int mode) {
     const int prev = gemm_epi_mode();
-    if (mode == 0 || mode == 1) g_gemm_epi = mode;
+    if (mode >= 0 && mode <= 2) g_gemm_epi = mode;
     return prev;
 }
 
@@ -859,7 +859,7 @@ static int build_problem(GemmParams& p, CUtensorMap& tmA, CUtensorMap& tmB, CUte
     else                    rc = make_tensor_map_2d(&tmB, B, K, N, ldb, BK, 64, 2);   // B stored [K][ldb]
     if (rc) return rc;
     const uint64_t d_rows = ws_row_stride > 0 ? static_cast<uint64_t>(ws_row_stride) * split_k : static_cast<uint64_t>(M);
-    const int d_box_rows = epi_mode == 1 ? BOX_ROWS : BM;  // per-warp boxes or whole-tile slabs
+    const int d_box_rows = epi_mode >= 1 ? BOX_ROWS : BM;  // per-warp boxes or whole-tile slabs
     rc = out_fp32 ? make_tensor_map_2d(&tmD, D, d_rows, N, ldd, d_box_rows, 32, 4)
                   : make_tensor_map_2d(&tmD, D, d_rows, N, ldd, d_box_rows, 64, 2);
     if (rc) return rc;
@@ -897,6 +897,7 @@ static int gemm_dispatch(const void* A, const void* B, void* D, int M, int N, in
 #define DCAD_GEMM_CASE_CG(BN_, AM_, BM_, CG_)                                             \
     if (cg == CG_ && bn == BN_ && a_major == AM_ && b_major == BM_) {                     \
         if (em == 1) return launch_gemm<BN_, AM_, BM_, CG_, 1, 1>(g, max_ctas, s);        \
+        if (em == 2) return launch_gemm<BN_, AM_, BM_, CG_, 1, 2>(g, max_ctas, s);        \
         return launch_gemm<BN_, AM_, BM_, CG_, 1, 0>(g, max_ctas, s);                     \
     }
 #define DCAD_GEMM_CASE(BN_, AM_, BM_) DCAD_GEMM_CASE_CG(BN_, AM_, BM_, 1)
@@ -954,7 +955,7 @@ extern "C" int dcad_gemm_bf16_group(int n, const void* const* A, const void* con
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
 #define DCAD_GROUP_CASE(BN_, AM_, BM_)                                                              \
     if (bn == BN_ && a_major == AM_ && b_major == BM_) {                                            \
-        if (em == 1) return launch_gemm<BN_, AM_, BM_, 1, DCAD_GEMM_GROUP_MAX, 1>(g, max_ctas, s);  \
+        if (em >= 1) return launch_gemm<BN_, AM_, BM_, 1, DCAD_GEMM_GROUP_MAX, 1>(g, max_ctas, s);  \
         return launch_gemm<BN_, AM_, BM_, 1, DCAD_GEMM_GROUP_MAX, 0>(g, max_ctas, s);               \
     }
     DCAD_GROUP_CASE(128, 1, 1)

@@ -1,0 +1,154 @@
+"""GPU tests at the REAL size (DistilBERT-base: 768 / 6 layers / 12 heads, batch 16, seq 128) against Hugging Face's
+``DistilBertModel`` in fp32 — the model the reference trains (client1.py:53-65) — plus a kernel-level check of the
+attention backward with dropout on.  Collected after the other GPU tests (file name)."""
+from __future__ import annotations
+
+import importlib
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+PKG = "detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200"
+
+
+def _hf_classifier(sd, dims):
+    """HF DistilBertModel (fp32, eager attention, all dropouts 0) + Linear head carrying the engine's weights."""
+    from transformers import DistilBertConfig, DistilBertModel
+
+    cfg = DistilBertConfig(vocab_size=dims.vocab_size, max_position_embeddings=dims.max_position, dim=dims.dim,
+                           n_layers=dims.n_layers, n_heads=dims.n_heads, hidden_dim=dims.hidden_dim, dropout=0.0,
+                           attention_dropout=0.0)
+    try:
+        enc = DistilBertModel(cfg, attn_implementation="eager")
+    except TypeError:
+        enc = DistilBertModel(cfg)
+    enc.load_state_dict({k[len("distilbert."):]: v for k, v in sd.items() if k.startswith("distilbert.")})
+    head = torch.nn.Linear(dims.dim, dims.n_classes)
+    head.load_state_dict({"weight": sd["classifier.weight"], "bias": sd["classifier.bias"]})
+    return enc.cuda().train(), head.cuda().train()
+
+
+def fullsize_parity_report(seed: int = 0):
+    """(logit errors, per-tensor gradient errors) of the engine against HF fp32 on one full-size batch."""
+    eng_mod = importlib.import_module(f"{PKG}.models.engine")
+    arena_mod = importlib.import_module(f"{PKG}.models.arena")
+    nv = importlib.import_module(f"{PKG}.ops.native")
+    synth = importlib.import_module(f"{PKG}.data.synth")
+    import dataclasses
+
+    dims = dataclasses.replace(arena_mod.ModelDims(), dropout=0.0, attention_dropout=0.0, head_dropout=0.0)
+    B, S = 16, 128
+    eng = eng_mod.B200Engine(dims, batch=B, seq=S, init_seed=seed)
+    ids, lens, labels = synth.synth_token_batch(B, S, dims.vocab_size, seed=seed)
+    ids, lens, labels = ids.cuda(), lens.cuda(), labels.cuda()
+    eng.set_batch(ids, lens, labels)
+    sd = eng.state_dict()
+    enc, head = _hf_classifier(sd, dims)
+    mask = (torch.arange(S, device="cuda")[None, :] < lens[:, None]).long()
+    torch.backends.cuda.matmul.allow_tf32 = False
+    logits_ref = head(enc(input_ids=ids.long(), attention_mask=mask)[0][:, 0])
+    loss_ref = F.cross_entropy(logits_ref, labels.long())
+    loss_ref.backward()
+    # engine: forward + head + backward (no optimizer step), every kernel hand-written
+    h, stride = eng._forward(B, train=True)
+    nv.cls_head_train(h, stride, eng.cw, eng.cb, eng.labels, B, eng.loss_accum, eng.logits, eng.d_cw, eng.d_cb,
+                      eng.dcls, cols=dims.dim)
+    eng._backward()
+    torch.cuda.synchronize()
+    ref_grads = {"distilbert." + k: p.grad for k, p in enc.named_parameters()}
+    ref_grads["classifier.weight"], ref_grads["classifier.bias"] = head.weight.grad, head.bias.grad
+    rows = []
+    for k, _ in eng.arena.layout.keys:
+        g, e = eng.arena.view(k, eng.arena.grad), ref_grads[k]
+        nz = e[e != 0]
+        rms = nz.pow(2).mean().sqrt().item() if nz.numel() else 0.0     # (embedding rows of unused tokens are 0)
+        rows.append((k, ((g - e).norm() / e.norm().clamp_min(1e-30)).item(), e.norm().item(),
+                     ((g - e).abs().max().item() / max(rms, 1e-30)), (g - e).norm().item()))
+    return {"loss": (float(eng.loss_accum[0].item()), float(loss_ref.item())),
+            "logits": (eng.logits.clone(), logits_ref.detach()), "grads": rows}
+
+
+def test_full_size_logits_and_all_gradients_match_hf_fp32():
+    """bf16 tensor-core compute with fp32 accumulation against HF in strict fp32: the loss and the logits agree to bf16
+    precision and EVERY one of the 102 gradient tensors agrees in relative norm; tensors whose true gradient is
+    (numerically) zero -- k_lin.bias: softmax is invariant to a per-query shift -- are held to the scale of their kind."""
+    rep = fullsize_parity_report()
+    loss, loss_ref = rep["loss"]
+    assert abs(loss - loss_ref) < 5e-3 * max(1.0, abs(loss_ref)), (loss, loss_ref)
+    out, exp = rep["logits"]
+    assert torch.allclose(out, exp, atol=2e-2, rtol=2e-2), (out - exp).abs().max().item()
+    import statistics
+
+    kind = {b: statistics.median(r[2] for r in rep["grads"] if r[0].endswith(".bias") == b) for b in (True, False)}
+    bad = []
+    for k, rel, norm, max_over_rms, err_norm in rep["grads"]:
+        # norm-wise: 2 % of the tensor's own gradient, plus 0.1 % of the typical gradient norm of its kind (the true
+        # k_lin.bias gradient is ~1e-9: only the second term can hold it); measured: <= 0.91 % on every tensor
+        ok_norm = err_norm <= 2e-2 * norm + 1e-3 * kind[k.endswith(".bias")]
+        # element-wise: no single element is off by more than the rms of the tensor's non-zero elements
+        ok_elem = norm < 1e-3 * kind[k.endswith(".bias")] or max_over_rms <= 1.0
+        if not (ok_norm and ok_elem):
+            bad.append((k, round(rel, 4), round(max_over_rms, 3)))
+    assert not bad, bad
+
+
+def _rng_state(seed=1234, step=0):
+    return torch.tensor([seed, step], dtype=torch.int64, device="cuda")
+
+
+def test_attention_backward_with_dropout_matches_autograd():
+    """attn_bwd regenerates the dropout mask of attn_fwd from (seed, step, stream, element).  The mask the kernels use
+    is recovered from two forwards whose V selects keys (V = [I; 0] and [0; I]), then autograd differentiates
+    softmax -> mask / (1 - p) -> @V with exactly that mask."""
+    nv = importlib.import_module(f"{PKG}.ops.native")
+    torch.manual_seed(17)
+    B, S, H, D, p = 2, 128, 12, 64, 0.1
+    lens = torch.tensor([S, 77], device="cuda", dtype=torch.int32)
+    qkv = torch.randn(B * S, 3 * H * D, device="cuda").bfloat16()
+    rng = _rng_state()
+    lse2 = torch.empty(B * H * 128, device="cuda")
+
+    def fwd(x, pd):
+        ctx = torch.empty(B * S, H * D, device="cuda", dtype=torch.bfloat16)
+        nv.attn_fwd(x, ctx, lse2, lens, B, S, H, p_drop=pd, rng=rng, stream_id=5)
+        return ctx
+
+    # recover P_dropped[b, h, q, key] column block by column block
+    probe = qkv.clone().view(B, S, 3, H, D)
+    eye = torch.eye(D, device="cuda", dtype=torch.bfloat16)
+    pdrop = torch.zeros(B, H, S, S, device="cuda")
+    pfull = torch.zeros(B, H, S, S, device="cuda")
+    for half in range(2):
+        probe[:, :, 2] = 0
+        probe[:, half * D:(half + 1) * D, 2] = eye[None, :, None, :]          # V[key, h, :] = e_(key - 64*half)
+        x = probe.view(B * S, 3 * H * D)
+        pdrop[..., half * D:(half + 1) * D] = fwd(x, p).float().view(B, S, H, D).permute(0, 2, 1, 3)
+        pfull[..., half * D:(half + 1) * D] = fwd(x, 0.0).float().view(B, S, H, D).permute(0, 2, 1, 3)
+    keep = (pdrop != 0) | (pfull == 0)
+    valid_k = (torch.arange(S, device="cuda")[None, :] < lens[:, None])
+    frac = 1.0 - keep[:, :, :, :][valid_k[:, None, None, :].expand_as(keep)].float().mean().item()
+    assert 0.08 < frac < 0.12, frac                                            # ~10 % of the real keys are dropped
+    # the kept probabilities are scaled by exactly 1 / (1 - p)
+    both = (pdrop != 0) & (pfull > 1e-3)
+    assert torch.allclose(pdrop[both], pfull[both] / (1 - p), rtol=3e-2, atol=1e-3)
+
+    ctx = fwd(qkv, p)
+    valid_q = valid_k.reshape(B * S, 1)
+    dctx = (torch.randn(B * S, H * D, device="cuda") * valid_q).bfloat16()
+    dqkv = torch.empty_like(qkv)
+    nv.attn_bwd(qkv, ctx, dctx, lse2, dqkv, lens, B, S, H, p_drop=p, rng=rng, stream_id=5)
+
+    q32 = qkv.float().requires_grad_(True)
+    q, k, v = q32.view(B, S, 3, H, D).permute(2, 0, 3, 1, 4)
+    s = (q @ k.transpose(-1, -2)) * 0.125
+    s = s.masked_fill(~valid_k[:, None, None, :], float("-inf"))
+    pd = torch.softmax(s, -1) * keep.float() / (1 - p)
+    ref = (pd @ v).permute(0, 2, 1, 3).reshape(B * S, H * D)
+    assert ((ctx.float() - ref) * valid_q).norm() / (ref * valid_q).norm() < 2e-2
+    ref.backward(dctx.float())
+    err = (dqkv.float() - q32.grad).norm() / q32.grad.norm()
+    assert err < 3e-2, err.item()
+    assert torch.allclose(dqkv.float(), q32.grad, rtol=0.1, atol=0.05 * q32.grad.pow(2).mean().sqrt().item() * 4)

@@ -19,9 +19,10 @@ def nv():
     return native
 
 
-@pytest.fixture()
-def warp_epilogue(nv):
-    prev = nv.set_gemm_epilogue(1)
+@pytest.fixture(params=[1, 2])
+def warp_epilogue(nv, request):
+    """1 = per-warp boxes beside the operand ring, 2 = per-warp boxes inside the ring (one more operand stage)"""
+    prev = nv.set_gemm_epilogue(request.param)
     yield
     nv.set_gemm_epilogue(prev)
 
@@ -61,8 +62,10 @@ def test_warp_epilogue_equals_block_epilogue_bitwise(nv):
     bias = torch.randn(N, device="cuda")
     aux = torch.randn(M, N, device="cuda").bfloat16()
     wt = w.t().contiguous()
+    dy = torch.randn(640, 768, device="cuda").bfloat16()
+    x = torch.randn(640, 512, device="cuda").bfloat16()
     res = {}
-    for mode in (0, 1):
+    for mode in (0, 1, 2):
         prev = nv.set_gemm_epilogue(mode)
         try:
             out, pre = (torch.empty(M, N, device="cuda", dtype=torch.bfloat16) for _ in range(2))
@@ -72,8 +75,6 @@ def test_warp_epilogue_equals_block_epilogue_bitwise(nv):
             nv.gemm_bf16(a, wt, dg, b_major=nv.MAJOR_MN, aux=aux, epi=nv.EPI_DGELU, block_n=192, colsum=cs)
             pair = torch.empty_like(out)
             nv.gemm_bf16(a, w, pair, bias=bias, epi=nv.EPI_BIAS, block_n=256 | nv.TILE_PAIR)
-            dy = torch.randn(640, 768, device="cuda").bfloat16()
-            x = torch.randn(640, 512, device="cuda").bfloat16()
             dw = torch.zeros(768, 512, device="cuda")
             nv.gemm_bf16(dy, x, dw, a_major=nv.MAJOR_MN, b_major=nv.MAJOR_MN, block_n=256, split_k=1)
             ws = torch.empty(nv.gemm_splitk_workspace_bytes(M, N, 3) // 4, device="cuda")
@@ -86,8 +87,9 @@ def test_warp_epilogue_equals_block_epilogue_bitwise(nv):
         finally:
             nv.set_gemm_epilogue(prev)
     names = ("gelu", "pre", "dgelu", "pair", "wgrad", "splitk", "group0", "group1")
-    for n, x0, x1 in zip(names, res[0], res[1]):
-        assert torch.equal(x0, x1), n
+    for mode in (1, 2):
+        for n, x0, x1 in zip(names, res[0], res[mode]):
+            assert torch.equal(x0, x1), (mode, n)
     assert _close(res[1][0], F.gelu(a.float() @ w.float().t() + bias), 1e-2)
 
 
@@ -119,5 +121,8 @@ def test_wide_tile_384(nv, b_major):
             x = aux.float().requires_grad_(True)
             F.gelu(x).backward(torch.ones_like(x))
             assert _close(out, ref * x.grad, 1e-2)
-            colsum = out.float().sum(0)
-            assert torch.allclose(cs - 2.0, colsum, rtol=1e-3, atol=1e-3 * colsum.abs().max().item() + 1e-3)
+            # the kernel sums the fp32 values before they are rounded to bf16: compare with the fp32 reference, within
+            # the rounding noise of M bf16 inputs per column
+            want = (ref * x.grad).sum(0)
+            noise = 2.0 ** -8 * (ref * x.grad).pow(2).mean().sqrt().item() * M ** 0.5
+            assert torch.allclose(cs - 2.0, want, rtol=1e-2, atol=4 * noise + 1e-3)

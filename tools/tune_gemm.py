@@ -69,7 +69,25 @@ def main():
         A = a if am == 0 else a.t()
         B = b if bm == 0 else b.t()
         cub = time_graph(lambda: torch.matmul(A, B.t()))
-        row = {"name": name, "M": M, "N": N, "K": K, "cublas_us": cub, "bn": {}}
+        # the same WORK through the library: cuBLAS GEMM + the elementwise kernels its epilogue-less call needs for
+        # what our epilogue fuses (bias, GELU with the pre-activation kept, dGELU) -- the like-for-like bar
+        if epi == 1:
+            fair = time_graph(lambda: torch.addmm(bias.bfloat16(), A, B.t()))
+        elif epi == 2:
+            bb = bias.bfloat16()
+
+            def lib_gelu():
+                pre = torch.addmm(bb, A, B.t())
+                return pre, torch.nn.functional.gelu(pre)
+            fair = time_graph(lib_gelu)
+        elif epi == 3:
+            ax = aux.float().requires_grad_(True)
+            torch.nn.functional.gelu(ax).backward(torch.ones_like(ax))
+            dg = ax.grad.bfloat16()   # (the derivative itself is precomputed: only the multiply is charged)
+            fair = time_graph(lambda: torch.matmul(A, B.t()) * dg)
+        else:
+            fair = cub
+        row = {"name": name, "M": M, "N": N, "K": K, "cublas_us": cub, "cublas_plus_epilogue_kernels_us": fair, "bn": {}}
         P = nv.TILE_PAIR  # "p" prefix below = 256 x bn tile on a CTA pair (cta_group::2)
         lab = lambda bn: ("p" if bn & P else "") + str(bn & ~P)  # noqa: E731
         cands = [(bn, 1) for bn in (64, 128, 192, 256) if N % bn == 0]
@@ -108,14 +126,16 @@ def main():
         row["best_us"] = ok[row["best_bn"]] if ok else None
         row["tflops_best"] = 2.0 * M * N * K / (row["best_us"] * 1e-6) / 1e12 if ok else None
         res.append(row)
-        print(f"{name:11s} {M:5d}x{N:5d}x{K:5d} cublas {cub:7.1f}us | " +
+        print(f"{name:11s} {M:5d}x{N:5d}x{K:5d} cublas {cub:7.1f}us (+epilogue kernels {fair:5.1f}) | " +
               " ".join(f"{bn}:{(v if v else -1):6.1f}" for bn, v in row["bn"].items()) +
               f" | best {row['best_bn']} {row['best_us']:.1f}us {row['tflops_best']:.0f}TF", flush=True)
     tot = sum(r["best_us"] for r in res) * 6
     totc = sum(r["cublas_us"] for r in res) * 6
-    print(f"sum over 6 layers: ours(best) {tot:.0f} us, cuBLAS (no epilogues) {totc:.0f} us")
+    totf = sum(r["cublas_plus_epilogue_kernels_us"] for r in res) * 6
+    print(f"sum over 6 layers: ours(best) {tot:.0f} us, cuBLAS (no epilogues) {totc:.0f} us, "
+          f"cuBLAS + epilogue kernels {totf:.0f} us")
     os.makedirs(ROOT / "gpurun_out", exist_ok=True)
-    name = (f"tune_gemm_T{T}" if T != 2048 else "tune_gemm") + ("_epi1" if epi_mode else "") + ".json"
+    name = (f"tune_gemm_T{T}" if T != 2048 else "tune_gemm") + (f"_epi{epi_mode}" if epi_mode else "") + ".json"
     (ROOT / "gpurun_out" / name).write_text(json.dumps(res, indent=1))
 
 
