@@ -76,6 +76,11 @@ def test_multiprocess_ipc_fedavg_and_bench():
     r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-3000:])
     assert "FEDAVG_IPC_OK" in r.stdout
+    # round-2 paths: a peer that never launches leaves every arena untouched, the next round recovers, subset rounds
+    # agreed through the store, the asynchronous transport handle, bf16 exchange arenas
+    for marker in ("ABSENT_PEER_LEAVES_ARENAS_UNTOUCHED_OK", "ROUND_AFTER_FAILURE_OK", "QUORUM_SUBSET_AND_ASYNC_OK",
+                   "BF16_EXCHANGE_OK"):
+        assert marker in r.stdout, (marker, r.stdout[-2000:])
 
 
 def test_intra_client_data_parallel_matches_single_gpu():

@@ -76,10 +76,124 @@ def main():
                 print(f"SYMM_{name.upper()}_OK", flush=True)
         dist.barrier()
         sg.close()
+    extra_checks(rank, world, dev, mine, allv, base, elems, mirror)
     if rank == 0:
         print("FEDAVG_IPC_OK", flush=True)
-    dist.destroy_process_group()
 
 
-if __name__ == "__main__":
-    main()
+def extra_checks(rank, world, dev, mine, allv, base, elems, mirror):
+    """Round-2 paths: NVLS with the locally cast mirror, a participant that never shows up (nothing may be written,
+    the error word is reported once), rounds over a subset of the clients agreed through the store, the asynchronous
+    transport handle, and the bf16 exchange."""
+    import time
+    from datetime import timedelta
+
+    from detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200.fed import rounds, transport
+
+    def say(msg):
+        if rank == 0:
+            print(msg, flush=True)
+
+    # ---- 1. NVLS, every GPU casting its own bf16 copy ----
+    try:
+        sg = p2p.SymmPeerGroup(rank, world, elems, mirror)
+    except Exception:  # noqa: BLE001
+        sg = None
+    if sg is not None and sg.has_nvls:
+        sg.arena_tensor().copy_(mine)
+        sg.mirror_tensor().zero_()
+        torch.cuda.synchronize()
+        dist.barrier()
+        sg.fedavg(p2p.NVLS, local_cast=True)
+        torch.cuda.synchronize()
+        assert sg.error_flag() == 0
+        got = sg.arena_tensor().cpu()
+        assert torch.allclose(got, base, rtol=1e-6, atol=1e-6)
+        assert torch.equal(sg.mirror_tensor().cpu(), got[:mirror].bfloat16()), "mirror is not the cast of the local arena"
+        say("NVLS_LOCAL_CAST_OK")
+    if sg is not None:
+        dist.barrier()
+        sg.close()
+
+    grp = p2p.PeerGroup(rank, world, elems, mirror)
+    arena = grp.arena_tensor()
+    # ---- 2. a client that never launches: the others time out, write NOTHING, report the failure once ----
+    arena.copy_(mine)
+    torch.cuda.synchronize()
+    dist.barrier()
+    absent = world - 1
+    t0 = time.time()
+    if rank != absent:
+        grp.fedavg(p2p.TWO_SHOT, epoch=1)          # expects every rank; rank `absent` never comes
+        torch.cuda.synchronize()
+        assert grp.error_flag() == 1, "a missing peer must raise the error word"
+        assert grp.error_flag() == 0, "the error word is cleared once it has been reported"
+    dist.barrier()
+    torch.cuda.synchronize()
+    assert torch.equal(arena, mine), f"rank {rank}: a timed-out round modified the parameters"
+    say(f"ABSENT_PEER_LEAVES_ARENAS_UNTOUCHED_OK ({time.time() - t0:.1f} s)")
+    # ... and the next round works again (explicit epochs keep the ranks in step although one skipped a launch)
+    dist.barrier()
+    grp.fedavg(p2p.TWO_SHOT, epoch=2)
+    torch.cuda.synchronize()
+    assert grp.error_flag() == 0 and torch.equal(arena.cpu(), base)
+    say("ROUND_AFTER_FAILURE_OK")
+
+    # ---- 3. quorum through the store + the asynchronous transport (its epochs count rounds from 1: fresh pads) ----
+    from torch.distributed import distributed_c10d as c10d
+
+    dist.barrier()
+    grp.close()
+    grp = p2p.PeerGroup(rank, world, elems, mirror)
+    arena = grp.arena_tensor()
+
+    store = dist.PrefixStore("mp_check", c10d._get_default_store())
+    coord = rounds.RoundCoordinator(store, rank, world, deadline_s=20.0, min_clients=1)
+
+    class Plan:  # the last client sits round 0 out (what utils.faults "drop=N@0" does)
+        def before_upload(self, client_id, rnd):
+            return not (client_id == world - 1 and rnd == 0 and world > 1)
+
+    tr = transport.NvSwitchTransport(grp, transport.AUTO, coordinator=coord, faults=Plan(), client_id=rank)
+    arena.copy_(mine)
+    torch.cuda.synchronize()
+    dist.barrier()
+    t0 = time.time()
+    pend = tr.aggregate_async(None)      # returns with the kernel in flight
+    ok = pend.wait()
+    torch.cuda.synchronize()
+    members = list(range(world - 1)) if world > 1 else [0]
+    sub = allv[members[0]].cpu().clone()
+    for m in members[1:]:
+        sub += allv[m].cpu()
+    sub /= len(members)
+    if rank in members:
+        assert ok and torch.equal(arena.cpu(), sub), f"rank {rank}: subset round mismatch"
+    else:
+        assert not ok and torch.equal(arena, mine), "the client that sat out must keep its local model"
+    assert time.time() - t0 < 15.0, "an announced absence must not cost the deadline"
+    dist.barrier()
+    arena.copy_(mine)
+    torch.cuda.synchronize()
+    dist.barrier()
+    assert tr.aggregate(None) and torch.equal(arena.cpu(), base)      # round 1: everybody again
+    say("QUORUM_SUBSET_AND_ASYNC_OK")
+    dist.barrier()
+    grp.close()
+
+    # ---- 4. bf16 exchange arenas (half the NVLink bytes) ----
+    xg = p2p.PeerGroup(rank, world, elems, 0, arena_dtype=torch.bfloat16)
+    xg.arena_tensor().copy_(mine.bfloat16())
+    torch.cuda.synchronize()
+    dist.barrier()
+    xg.fedavg(p2p.TWO_SHOT, with_mirror=False)
+    torch.cuda.synchronize()
+    assert xg.error_flag() == 0
+    exp16 = allv[0].bfloat16().float().cpu()
+    for a in allv[1:]:
+        exp16 += a.bfloat16().float().cpu()
+    exp16 = (exp16 / world).bfloat16()
+    assert torch.equal(xg.arena_tensor().cpu(), exp16), "bf16 exchange: fp32 accumulation, one rounding of the mean"
+    say("BF16_EXCHANGE_OK")
+    dist.barrier()
+    xg.close()
