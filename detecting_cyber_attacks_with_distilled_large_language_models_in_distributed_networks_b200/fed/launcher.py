@@ -146,13 +146,23 @@ class _StoreTransport(Transport):
         rnd, self.round_idx = self.round_idx, self.round_idx + 1
         take_part = not (self.faults and not self.faults.before_upload(self.client_id, rnd))
         store = self.coord.store
+        chunk = 4 << 20  # the TCP store refuses values above 8 MiB
         if take_part:
             buf = io.BytesIO()
             torch.save({k: v.cpu() for k, v in backend.state_dict().items()}, buf)
-            store.set(f"sd/r{rnd}/{self.rank}", buf.getvalue())
+            raw = buf.getvalue()
+            n = (len(raw) + chunk - 1) // chunk
+            for i in range(n):
+                store.set(f"sd/r{rnd}/{self.rank}/{i}", raw[i * chunk: (i + 1) * chunk])
+            store.set(f"sd/r{rnd}/{self.rank}/n", str(n).encode())
         members = self.coord.agree(rnd, take_part=take_part)
         if members is None:
             return False
-        sds = [torch.load(io.BytesIO(store.get(f"sd/r{rnd}/{m}")), weights_only=True) for m in members]
+
+        def fetch(m: int):
+            n = int(store.get(f"sd/r{rnd}/{m}/n").decode())
+            return torch.load(io.BytesIO(b"".join(store.get(f"sd/r{rnd}/{m}/{i}") for i in range(n))), weights_only=True)
+
+        sds = [fetch(m) for m in members]
         backend.load_state_dict(fedavg_state_dicts_cpu(sds))
         return True
