@@ -19,6 +19,12 @@ namespace dcad {
 
 int make_tensor_map_bf16_3d(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t ld1,
                             uint64_t ld2, uint32_t b0, uint32_t b1);
+// attention_generic.cu: CUDA-core fallback for 128 < S <= 512
+int attn_generic_fwd(const void* qkv, void* ctx, float* lse2, const int32_t* lens, int B, int S, int H, float p_drop,
+                     const uint64_t* rng, uint32_t stream_id, cudaStream_t stream);
+int attn_generic_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse2, void* dqkv,
+                     const int32_t* lens, int B, int S, int H, float p_drop, const uint64_t* rng, uint32_t stream_id,
+                     cudaStream_t stream);
 
 constexpr int AT_S = 128;        // tile rows (max sequence length)
 constexpr int AT_D = 64;         // head dim
@@ -451,12 +457,15 @@ static inline uint32_t drop_thresh_attn(float p) {
 
 using namespace dcad;
 
-// qkv: [B*S, 3*H*64] bf16; ctx: [B*S, H*64] bf16; lse2: [B*H*128] fp32 (log2-domain logsumexp, for backward)
+// qkv: [B*S, 3*H*64] bf16; ctx: [B*S, H*64] bf16; lse2: [B*H*max(S,128)] fp32 (log2-domain logsumexp, for backward).
+// S <= 128: the tcgen05 kernels of this file; 128 < S <= 512: the CUDA-core fallback of attention_generic.cu.
 extern "C" int dcad_attn_fwd(const void* qkv, void* ctx, float* lse2, const int32_t* lens, int B, int S, int H,
                              float p_drop, const uint64_t* rng, uint32_t stream_id, void* stream) {
     if (B <= 0) return 0;
-    if (S <= 0 || S > AT_S || H <= 0) return DCAD_ERR_BAD_SHAPE;
+    if (S <= 0 || S > 512 || H <= 0) return DCAD_ERR_BAD_SHAPE;
     if (p_drop > 0.f && rng == nullptr) return DCAD_ERR_BAD_ARGUMENT;
+    if (S > AT_S)
+        return attn_generic_fwd(qkv, ctx, lse2, lens, B, S, H, p_drop, rng, stream_id, reinterpret_cast<cudaStream_t>(stream));
     const int HD = H * AT_D;
     CUtensorMap tm;
     int rc = make_tensor_map_bf16_3d(&tm, qkv, 3 * HD, S, B, 3 * HD, static_cast<uint64_t>(S) * 3 * HD, AT_D, AT_S);
@@ -475,8 +484,14 @@ extern "C" int dcad_attn_bwd(const void* qkv, const void* ctx, const void* dctx,
                              const int32_t* lens, int B, int S, int H, float p_drop, const uint64_t* rng,
                              uint32_t stream_id, float* dbias, void* stream) {
     if (B <= 0) return 0;
-    if (S <= 0 || S > AT_S || H <= 0) return DCAD_ERR_BAD_SHAPE;
+    if (S <= 0 || S > 512 || H <= 0) return DCAD_ERR_BAD_SHAPE;
     if (p_drop > 0.f && rng == nullptr) return DCAD_ERR_BAD_ARGUMENT;
+    if (S > AT_S) {
+        int rc = attn_generic_bwd(qkv, ctx, dctx, lse2, dqkv, lens, B, S, H, p_drop, rng, stream_id,
+                                  reinterpret_cast<cudaStream_t>(stream));
+        if (rc || dbias == nullptr) return rc;
+        return dcad_colsum_bf16(dqkv, dbias, B * S, 3 * H * AT_D, 3 * H * AT_D, stream);  // fused-bias contract: += colsum
+    }
     const int HD = H * AT_D;
     CUtensorMap tq, td;
     int rc = make_tensor_map_bf16_3d(&tq, qkv, 3 * HD, S, B, 3 * HD, static_cast<uint64_t>(S) * 3 * HD, AT_D, AT_S);

@@ -5,8 +5,11 @@
 // (transformers modeling_distilbert.py:257,261), the FFN dropout (:227) and the Embeddings module (:96-122) that the
 // reference reaches through client1.py:61; backward replaces their autograd (client1.py:109).
 //
-// One warp owns one row (cols = NV*256, 8 bf16 per 16-byte access), statistics by warp shuffles.  The backward
-// reconstructs x_hat from the saved LN *output* (x_hat = (y - beta) / gamma) so only rstd [rows] is kept.
+// One warp owns one row (cols = NV*256, 8 bf16 per 16-byte access), statistics by warp shuffles.  The backward needs
+// x_hat: the forward can save it (bf16, `xhat_out`; its rounding error is 2^-9 |x_hat| whatever gamma and beta are),
+// or the backward rebuilds it from the saved LN *output*, x_hat = (y - beta) / gamma, which costs no extra tensor but
+// amplifies the bf16 rounding of y by |beta| / |gamma| -- fine for gamma ~ 1 (random init), poor for channels of a
+// pretrained encoder whose gamma is small.  The training engine saves x_hat.
 #include "common.cuh"
 #include "../include/dcad_b200.h"
 
@@ -66,8 +69,8 @@ template <int NV>
 __global__ void __launch_bounds__(LN_WARPS * 32)
 add_ln_fwd_kernel(const __nv_bfloat16* __restrict__ a, const PartialIn a_part, const __nv_bfloat16* __restrict__ res,
                   const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ out,
-                  float* __restrict__ rstd_out, int rows, float eps, uint32_t thresh, float keep_scale,
-                  const uint64_t* __restrict__ rng, uint32_t stream_id) {
+                  float* __restrict__ rstd_out, __nv_bfloat16* __restrict__ xhat_out, int rows, float eps,
+                  uint32_t thresh, float keep_scale, const uint64_t* __restrict__ rng, uint32_t stream_id) {
     pdl_trigger();
     pdl_wait();
     constexpr int COLS = NV * 256;
@@ -106,12 +109,13 @@ add_ln_fwd_kernel(const __nv_bfloat16* __restrict__ a, const PartialIn a_part, c
 #pragma unroll
     for (int v = 0; v < NV; ++v) {
         const int col = (v * 32 + lane) * 8;
-        float g[8], b[8], y[8];
+        float g[8], b[8], y[8], xh[8];
         load8f(gamma + col, g);
         load8f(beta + col, b);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) y[j] = (x[v][j] - mean) * rstd * g[j] + b[j];
+        for (int j = 0; j < 8; ++j) { xh[j] = (x[v][j] - mean) * rstd; y[j] = xh[j] * g[j] + b[j]; }
         store8(out + static_cast<size_t>(row) * COLS + col, y);
+        if (xhat_out) store8(xhat_out + static_cast<size_t>(row) * COLS + col, xh);
     }
     if (lane == 0 && rstd_out) rstd_out[row] = rstd;
 }
@@ -156,10 +160,11 @@ add_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy1, const PartialIn dy1_par
             }
             load8(y + off, yy);
             load8f(gamma + col, gm);
-            load8f(beta + col, bt);
+            if (beta) load8f(beta + col, bt);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-                xh[v][j] = (yy[j] - bt[j]) / safe_gamma(gm[j]);
+                // beta == nullptr: `y` holds the x_hat the forward saved; else x_hat is rebuilt from the LN output
+                xh[v][j] = beta ? (yy[j] - bt[j]) / safe_gamma(gm[j]) : yy[j];
                 g[v][j] = d[v][j] * gm[j];
                 c1 += g[v][j];
                 c2 += g[v][j] * xh[v][j];
@@ -407,7 +412,7 @@ using namespace dcad;
 
 static int add_ln_fwd_run(const void* a, PartialIn a_part, const void* res, const float* gamma, const float* beta,
                           void* out, float* rstd, int rows, int cols, float eps, float p_drop, const uint64_t* rng,
-                          uint32_t stream_id, void* stream) {
+                          uint32_t stream_id, void* stream, void* xhat_out = nullptr) {
     if (rows <= 0) return 0;
     if (cols % 256 || cols > 1024) return DCAD_ERR_BAD_SHAPE;
     if (p_drop > 0.f && rng == nullptr) return DCAD_ERR_BAD_ARGUMENT;
@@ -418,7 +423,7 @@ static int add_ln_fwd_run(const void* a, PartialIn a_part, const void* res, cons
     DCAD_NV_DISPATCH(cols, return (int)launch_pdl(
         add_ln_fwd_kernel<NV>, dim3(grid), dim3(LN_WARPS * 32), 0, s, reinterpret_cast<const __nv_bfloat16*>(a),
         a_part, reinterpret_cast<const __nv_bfloat16*>(res), gamma, beta, reinterpret_cast<__nv_bfloat16*>(out), rstd,
-        rows, eps, th, ks, rng, stream_id));
+        reinterpret_cast<__nv_bfloat16*>(xhat_out), rows, eps, th, ks, rng, stream_id));
     return 0;
 }
 
@@ -427,6 +432,26 @@ extern "C" int dcad_add_ln_fwd(const void* a, const void* res, const float* gamm
                                uint32_t stream_id, void* stream) {
     return add_ln_fwd_run(a, PartialIn{nullptr, nullptr, 0, 0}, res, gamma, beta, out, rstd, rows, cols, eps, p_drop,
                           rng, stream_id, stream);
+}
+
+// Same as dcad_add_ln_fwd, and also stores x_hat = (x - mean) * rstd (bf16, same shape as out) for a backward that does
+// not want to rebuild it from the output (dcad_add_ln_bwd with beta == NULL and y = that x_hat).
+extern "C" int dcad_add_ln_fwd_x(const void* a, const void* res, const float* gamma, const float* beta, void* out,
+                                 float* rstd, void* xhat_out, int rows, int cols, float eps, float p_drop,
+                                 const uint64_t* rng, uint32_t stream_id, void* stream) {
+    return add_ln_fwd_run(a, PartialIn{nullptr, nullptr, 0, 0}, res, gamma, beta, out, rstd, rows, cols, eps, p_drop,
+                          rng, stream_id, stream, xhat_out);
+}
+
+extern "C" int dcad_add_ln_fwd_partials_x(const float* a_partials, int splits, int64_t slice_elems,
+                                          const float* a_bias, const void* res, const float* gamma, const float* beta,
+                                          void* out, float* rstd, void* xhat_out, int rows, int cols, float eps,
+                                          float p_drop, const uint64_t* rng, uint32_t stream_id, void* stream) {
+    if (a_partials == nullptr || splits < 1 || (slice_elems & 3) ||
+        (reinterpret_cast<uintptr_t>(a_partials) & 15u))
+        return DCAD_ERR_BAD_ARGUMENT;
+    return add_ln_fwd_run(nullptr, PartialIn{a_partials, a_bias, slice_elems, splits}, res, gamma, beta, out, rstd,
+                          rows, cols, eps, p_drop, rng, stream_id, stream, xhat_out);
 }
 
 extern "C" int dcad_add_ln_fwd_partials(const float* a_partials, int splits, int64_t slice_elems, const float* a_bias,

@@ -101,8 +101,10 @@ class B200Engine:
         if not torch.cuda.is_available():
             raise nv.NativeError("B200Engine needs a CUDA device; use models.distilbert.DDoSClassifier on CPU")
         nv.lib()  # fail loudly if the native library is missing
-        if seq > 128:
-            raise ValueError("the fused attention kernel covers seq <= 128 (the reference truncates to 128)")
+        if seq > dims.max_position or seq > 512:
+            raise ValueError(f"seq {seq} exceeds the position table ({dims.max_position}) / the attention kernels (512)")
+        # seq <= 128 (the reference's max_len, client1.py:27): the tcgen05 whole-sequence attention kernels;
+        # 128 < seq <= 512: the same entry points fall back to the CUDA-core kernels of csrc/attention_generic.cu
         if dims.head_dim != 64 or dims.dim % 256 != 0:
             raise ValueError("kernels are specialised for head_dim 64 and dim in {256,512,768,1024}")
         self.dims, self.B, self.S = dims, batch, seq
@@ -164,9 +166,16 @@ class B200Engine:
         self.sa = [torch.empty(T, D, **bf) for _ in range(L)]
         self.pre = [torch.empty(T, Fh, **bf) for _ in range(L)]
         self.hmid = [torch.empty(T, Fh, **bf) for _ in range(L)]
+        # LayerNorm backward needs x_hat.  Saved by the forward in bf16 (3 MB per LayerNorm and step of extra HBM writes)
+        # rather than rebuilt from the bf16 output as (y - beta) / gamma: that amplifies y's rounding by |beta| / |gamma|
+        # and a pretrained DistilBERT -- what the reference fine-tunes, client1.py:55 -- has channels with small gamma
+        # (DCAD_SAVE_XHAT=0 restores the rebuild)
+        self.save_xhat = os.environ.get("DCAD_SAVE_XHAT", "1") != "0"
+        self.xh1 = [torch.empty(T, D, **bf) if self.save_xhat else None for _ in range(L)]
+        self.xh2 = [torch.empty(T, D, **bf) if self.save_xhat else None for _ in range(L)]
         self.rstd1 = [torch.empty(T, **f32) for _ in range(L)]
         self.rstd2 = [torch.empty(T, **f32) for _ in range(L)]
-        self.lse2 = [torch.empty(batch * H * 128, **f32) for _ in range(L)]
+        self.lse2 = [torch.empty(batch * H * max(seq, 128), **f32) for _ in range(L)]
         self.emb_mean = torch.empty(T, **f32)
         self.emb_rstd = torch.empty(T, **f32)
         # transient forward / backward buffers
@@ -185,6 +194,8 @@ class B200Engine:
         self.c_pre, self.c_hmid, self.c_gwide = (torch.empty(batch, Fh, **bf) for _ in range(3))
         self.c_ga, self.c_gb, self.c_gc, self.c_gd, self.c_ge = (torch.empty(batch, D, **bf) for _ in range(5))
         self.c_rstd1, self.c_rstd2 = torch.empty(batch, **f32), torch.empty(batch, **f32)
+        self.c_xh1, self.c_xh2 = ((torch.empty(batch, D, **bf), torch.empty(batch, D, **bf)) if self.save_xhat
+                                  else (None, None))
         self.logits = torch.empty(batch, dims.n_classes, **f32)
         # scratch for the split-K GEMMs (fp32 partial tiles), sized for the larger of the two users
         sk = max(self.plan.lin2_fwd[1], self.plan.lin1_dgrad[1], self.plan.qkv_dgrad[1], 2)
@@ -317,6 +328,15 @@ class B200Engine:
             return None
         return self.lens[:rows_b]
 
+    @staticmethod
+    def _xh(buf, rows: int, train: bool):
+        """where a LayerNorm forward keeps x_hat for the backward (training steps only)"""
+        return buf[:rows] if (train and buf is not None) else None
+
+    def _ln_saved(self, y, xhat, beta):
+        """(tensor, beta) operands of add_ln_bwd: the saved x_hat (beta = None) or the LayerNorm output to rebuild from"""
+        return (xhat, None) if (self.save_xhat and xhat is not None) else (y, beta)
+
     def _k(self, fn, *args, **kw):
         if self._count(1, fn.__name__):
             return fn(*args, **kw)
@@ -343,13 +363,15 @@ class B200Engine:
             if self.prune_last_layer and l == d.n_layers - 1:
                 return self._forward_tail_pruned(l, rows_b, train, p_h, rng, fuse_head), d.dim
             self._gemm(ctx, self.p["wo"][l], tmp, bias=self.p["bo"][l], epi=nv.EPI_BIAS, block_n=pl.out_fwd)
-            self._k(nv.add_ln_fwd, tmp, x, self.p["g1"][l], self.p["b1"][l], sa, self.rstd1[l][:T], eps=d.ln_eps)
+            self._k(nv.add_ln_fwd, tmp, x, self.p["g1"][l], self.p["b1"][l], sa, self.rstd1[l][:T], eps=d.ln_eps,
+                    xhat_out=self._xh(self.xh1[l], T, train))
             self._gemm(sa, self.p["w1"][l], hmid, bias=self.p["bb1"][l], aux_out=pre if train else None,
                        epi=nv.EPI_BIAS_GELU, block_n=pl.lin1_fwd, row_lens=self._row_lens(rows_b))
             ffn = self._gemm_then(hmid, self.p["w2"][l], T, d.dim, pl.lin2_fwd, tmp, pl.fuse_ln_partials >= 2,
                                   bias=self.p["bb2"][l])
             self._k(nv.add_ln_fwd, ffn, sa, self.p["g2"][l], self.p["b2"][l], self.x[l + 1][:T], self.rstd2[l][:T],
-                    eps=d.ln_eps, p_drop=p_h, rng=rng, stream_id=_layer_stream(l, 1))
+                    eps=d.ln_eps, p_drop=p_h, rng=rng, stream_id=_layer_stream(l, 1),
+                    xhat_out=self._xh(self.xh2[l], T, train))
         return self.x[d.n_layers][:T], S * d.dim
 
     def _forward_tail_pruned(self, l: int, rows_b: int, train: bool, p_h: float, rng, fuse_head: bool = False):
@@ -363,7 +385,8 @@ class B200Engine:
         self._k(nv.gather_rows_bf16, self.ctx[l], ctxc, Bc, d.dim, S)
         self._k(nv.gather_rows_bf16, self.x[l], xc, Bc, d.dim, S)
         self._gemm(ctxc, P["wo"][l], tmpc, bias=P["bo"][l], epi=nv.EPI_BIAS, block_n=pl.tail_bn)
-        self._k(nv.add_ln_fwd, tmpc, xc, P["g1"][l], P["b1"][l], sac, self.c_rstd1[:Bc], eps=d.ln_eps)
+        self._k(nv.add_ln_fwd, tmpc, xc, P["g1"][l], P["b1"][l], sac, self.c_rstd1[:Bc], eps=d.ln_eps,
+                xhat_out=self._xh(self.c_xh1, Bc, train))
         self._gemm(sac, P["w1"][l], hmidc, bias=P["bb1"][l], aux_out=prec if train else None, epi=nv.EPI_BIAS_GELU,
                    block_n=pl.tail_bn)
         ffn = self._gemm_then(hmidc, P["w2"][l], Bc, d.dim, pl.tail_long_k, tmpc, pl.fuse_ln_partials >= 1, bias=P["bb2"][l])
@@ -372,7 +395,7 @@ class B200Engine:
         if fuse_head:
             return ffn
         self._k(nv.add_ln_fwd, ffn, sac, P["g2"][l], P["b2"][l], outc, self.c_rstd2[:Bc], eps=d.ln_eps, p_drop=p_h,
-                rng=rng, stream_id=_layer_stream(l, 1))
+                rng=rng, stream_id=_layer_stream(l, 1), xhat_out=self._xh(self.c_xh2, Bc, train))
         return outc
 
     def _tail_head(self, ffn) -> None:
@@ -471,7 +494,8 @@ class B200Engine:
                 # output_layer_norm(dropout(ffn_out) + sa)
                 dz2 = G.c
                 da2 = G.d if d.dropout > 0 else dz2  # without dropout the two gradients coincide
-                self._k(nv.add_ln_bwd, dy1, dy2, self.x[l + 1], P["g2"][l], P["b2"][l], self.rstd2[l], dz2,
+                y2, beta2 = self._ln_saved(self.x[l + 1], self.xh2[l], P["b2"][l])
+                self._k(nv.add_ln_bwd, dy1, dy2, y2, P["g2"][l], beta2, self.rstd2[l], dz2,
                         da2 if d.dropout > 0 else None, P["d_g2"][l], P["d_b2"][l], P["d_bb2"][l], p_drop=d.dropout,
                         rng=self.rng, stream_id=_layer_stream(l, 1))
                 # lin2: dW2 = da2^T hmid (side) ; dpre = (da2 W2) * gelu'(pre)
@@ -488,7 +512,8 @@ class B200Engine:
                                       b_major=MN)
                 # sa_layer_norm(attn_out + x): dz1 is the gradient wrt both attn_out and the residual x
                 dz1 = G.a
-                self._k(nv.add_ln_bwd, dsa, dz2, sa, P["g1"][l], P["b1"][l], self.rstd1[l], dz1, None, P["d_g1"][l],
+                y1, beta1 = self._ln_saved(sa, self.xh1[l], P["b1"][l])
+                self._k(nv.add_ln_bwd, dsa, dz2, y1, P["g1"][l], beta1, self.rstd1[l], dz1, None, P["d_g1"][l],
                         P["d_b1"][l], P["d_bo"][l])
                 # out_lin: dWo = dz1^T ctx (side) ; dctx = dz1 Wo
                 if not pl.group_wgrad:
@@ -530,14 +555,16 @@ class B200Engine:
         G = self.gset[l % 2]
         dz2, da2 = self.c_gc, (self.c_gd if d.dropout > 0 else self.c_gc)
         if not head_fused:  # otherwise _tail_head already produced dz2 / da2 and the LayerNorm parameter gradients
-            self._k(nv.add_ln_bwd, self.dcls, None, self.c_out, P["g2"][l], P["b2"][l], self.c_rstd2, dz2,
+            y2, beta2 = self._ln_saved(self.c_out, self.c_xh2, P["b2"][l])
+            self._k(nv.add_ln_bwd, self.dcls, None, y2, P["g2"][l], beta2, self.c_rstd2, dz2,
                     da2 if d.dropout > 0 else None, P["d_g2"][l], P["d_b2"][l], P["d_bb2"][l], p_drop=d.dropout,
                     rng=self.rng, stream_id=_layer_stream(l, 1))
         self._gemm(da2, P["w2"][l], self.c_gwide, b_major=MN, aux=self.c_pre, epi=nv.EPI_DGELU, block_n=pl.tail_bn,
                    colsum=P["d_bb1"][l] if pl.fuse_colsum else None)
         dsa = self._gemm_then(self.c_gwide, P["w1"][l], B, D, pl.tail_long_k, self.c_gb, pl.fuse_ln_partials >= 1, b_major=MN)
         dz1 = self.c_ga
-        self._k(nv.add_ln_bwd, dsa, dz2, self.c_sa, P["g1"][l], P["b1"][l], self.c_rstd1, dz1, None, P["d_g1"][l],
+        y1, beta1 = self._ln_saved(self.c_sa, self.c_xh1, P["b1"][l])
+        self._k(nv.add_ln_bwd, dsa, dz2, y1, P["g1"][l], beta1, self.c_rstd1, dz1, None, P["d_g1"][l],
                 P["d_b1"][l], P["d_bo"][l])
         dctx_c = self.c_ge
         self._gemm(dz1, P["wo"][l], dctx_c, b_major=MN, block_n=pl.tail_bn)

@@ -108,6 +108,8 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("dcad_gemm_splitk_workspace_bytes", [I, I, I], ctypes.c_size_t)
     sig("dcad_gemm_bf16_splitk", [P, P, P, I, I, I, I, I, I, I, I, P, P, P, I, I, I, I, I, P, ctypes.c_size_t, P])
     sig("dcad_add_ln_fwd", [P, P, P, P, P, P, I, I, F, F, P, U32, P])
+    sig("dcad_add_ln_fwd_x", [P, P, P, P, P, P, P, I, I, F, F, P, U32, P])
+    sig("dcad_add_ln_fwd_partials_x", [P, I, L64, P, P, P, P, P, P, P, I, I, F, F, P, U32, P])
     sig("dcad_add_ln_fwd_partials", [P, I, L64, P, P, P, P, P, P, I, I, F, F, P, U32, P])
     sig("dcad_add_ln_bwd_partials", [P, I, L64, P, P, P, P, P, P, P, P, P, P, I, I, F, P, U32, P])
     sig("dcad_gemm_bf16_splitk_partials", [P, P, I, I, I, I, I, I, I, I, I, I, P, ctypes.c_size_t, P, P, P])
@@ -283,7 +285,21 @@ def gemm_bf16_splitk_partials(a: torch.Tensor, b: torch.Tensor, M: int, N: int, 
     return Partials(workspace, splits.value, slice_elems.value, M, N, bias)
 
 
-def add_ln_fwd(a, res, gamma, beta, out, rstd, *, eps=1e-12, p_drop=0.0, rng=None, stream_id=0, stream=None):
+def add_ln_fwd(a, res, gamma, beta, out, rstd, *, eps=1e-12, p_drop=0.0, rng=None, stream_id=0, stream=None,
+               xhat_out=None):
+    """``xhat_out`` (bf16, like ``out``): also keep x_hat for ``add_ln_bwd(..., y=xhat, beta=None)``."""
+    if xhat_out is not None:
+        if isinstance(a, Partials):
+            rows, cols = a.shape
+            check(lib().dcad_add_ln_fwd_partials_x(a.workspace.data_ptr(), a.splits, a.slice_elems, ptr(a.bias),
+                                                   ptr(res), ptr(gamma), ptr(beta), ptr(out), ptr(rstd), ptr(xhat_out),
+                                                   rows, cols, eps, p_drop, ptr(rng), stream_id, stream_ptr(stream)),
+                  "dcad_add_ln_fwd_partials_x")
+            return out
+        rows, cols = a.shape
+        check(lib().dcad_add_ln_fwd_x(ptr(a), ptr(res), ptr(gamma), ptr(beta), ptr(out), ptr(rstd), ptr(xhat_out), rows,
+                                      cols, eps, p_drop, ptr(rng), stream_id, stream_ptr(stream)), "dcad_add_ln_fwd_x")
+        return out
     if isinstance(a, Partials):
         rows, cols = a.shape
         check(lib().dcad_add_ln_fwd_partials(a.workspace.data_ptr(), a.splits, a.slice_elems, ptr(a.bias), ptr(res),
@@ -298,6 +314,8 @@ def add_ln_fwd(a, res, gamma, beta, out, rstd, *, eps=1e-12, p_drop=0.0, rng=Non
 
 def add_ln_bwd(dy1, dy2, y, gamma, beta, rstd, dz, da, dgamma, dbeta, dbias, *, p_drop=0.0, rng=None, stream_id=0,
                stream=None):
+    """``beta=None``: ``y`` is the x_hat saved by ``add_ln_fwd(..., xhat_out=...)``; else x_hat is rebuilt from the
+    LayerNorm output ``y``."""
     rows, cols = y.shape
     if isinstance(dy1, Partials):
         check(lib().dcad_add_ln_bwd_partials(dy1.workspace.data_ptr(), dy1.splits, dy1.slice_elems, ptr(dy2), ptr(y),

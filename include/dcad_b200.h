@@ -133,6 +133,18 @@ void dcad_gemm_set_timing_buffer(void* dev_ptr);
 int dcad_add_ln_fwd(const void* a, const void* res, const float* gamma, const float* beta, void* out, float* rstd,
                     int rows, int cols, float eps, float p_drop, const uint64_t* rng, uint32_t stream_id,
                     void* stream);
+/* dcad_add_ln_fwd that also stores x_hat = (x - mean) * rstd (bf16 [rows, cols]) for the backward: pass it to
+ * dcad_add_ln_bwd as `y` with beta == NULL.  HF keeps the LayerNorm input for autograd (client1.py:109 through
+ * modeling_distilbert.py:257,261); rebuilding x_hat from the bf16 output instead amplifies its rounding by
+ * |beta| / |gamma|, which pretrained encoders with small gamma channels do not tolerate. */
+int dcad_add_ln_fwd_x(const void* a, const void* res, const float* gamma, const float* beta, void* out, float* rstd,
+                      void* xhat_out, int rows, int cols, float eps, float p_drop, const uint64_t* rng,
+                      uint32_t stream_id, void* stream);
+int dcad_add_ln_fwd_partials_x(const float* a_partials, int splits, int64_t slice_elems, const float* a_bias,
+                               const void* res, const float* gamma, const float* beta, void* out, float* rstd,
+                               void* xhat_out, int rows, int cols, float eps, float p_drop, const uint64_t* rng,
+                               uint32_t stream_id, void* stream);
+
 /* backward of dcad_add_ln_fwd.  dy = dy1 (+ dy2 when non-NULL).  dz = grad wrt res (and wrt the pre-dropout sum);
  * da = grad wrt a (only written when p_drop > 0, otherwise it equals dz).  dgamma/dbeta/dbias (dbias may be NULL;
  * it is colsum(da), the bias gradient of the Linear that produced a) are ACCUMULATED into zero-initialised buffers. */

@@ -152,3 +152,148 @@ def test_attention_backward_with_dropout_matches_autograd():
     err = (dqkv.float() - q32.grad).norm() / q32.grad.norm()
     assert err < 3e-2, err.item()
     assert torch.allclose(dqkv.float(), q32.grad, rtol=0.1, atol=0.05 * q32.grad.pow(2).mean().sqrt().item() * 4)
+
+
+def test_layernorm_backward_with_small_gamma_uses_saved_xhat():
+    """Pretrained encoders have LayerNorm channels with small gamma and |beta| ~ 1.  Rebuilding x_hat from the bf16
+    output, (y - beta) / gamma, then amplifies y's rounding by |beta| / |gamma|; with the x_hat the forward saves
+    (what the training engine does) the backward stays at bf16 accuracy for every channel."""
+    nv = importlib.import_module(f"{PKG}.ops.native")
+    torch.manual_seed(3)
+    rows, cols = 512, 768
+    a = torch.randn(rows, cols, device="cuda").bfloat16()
+    res = torch.randn(rows, cols, device="cuda").bfloat16()
+    gamma = torch.exp(torch.empty(cols, device="cuda").uniform_(-6.9, 0.4))      # 1e-3 .. 1.5, log-uniform
+    beta = torch.randn(cols, device="cuda")
+    dy = torch.randn(rows, cols, device="cuda").bfloat16()
+    x = (a.float() + res.float()).requires_grad_(True)
+    g32, b32 = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    F.layer_norm(x, (cols,), g32, b32, 1e-12).backward(dy.float())
+
+    def run(save):
+        y = torch.empty_like(a)
+        xh = torch.empty_like(a) if save else None
+        rstd = torch.empty(rows, device="cuda")
+        nv.add_ln_fwd(a, res, gamma, beta, y, rstd, xhat_out=xh)
+        dz = torch.empty_like(a)
+        dgamma, dbeta, dbias = (torch.zeros(cols, device="cuda") for _ in range(3))
+        nv.add_ln_bwd(dy, None, xh if save else y, gamma, None if save else beta, rstd, dz, None, dgamma, dbeta, dbias)
+        torch.cuda.synchronize()
+        return dz.float(), dgamma, dbeta
+
+    dz, dgamma, dbeta = run(save=True)
+    assert (dz - x.grad).norm() / x.grad.norm() < 1e-2
+    assert torch.allclose(dbeta, b32.grad, rtol=1e-3, atol=1e-2)
+    # d gamma_c = sum_rows dy * x_hat: accurate for EVERY channel, the tiny-gamma ones included
+    scale = g32.grad.abs().mean().item()
+    assert torch.allclose(dgamma, g32.grad, rtol=2e-2, atol=2e-2 * scale), (dgamma - g32.grad).abs().max().item()
+    # the rebuild is visibly worse on the small-gamma channels (documented limitation of the cheaper path)
+    _, dgamma_rebuilt, _ = run(save=False)
+    small = gamma < 0.02
+    err_saved = (dgamma - g32.grad)[small].abs().max().item()
+    err_rebuilt = (dgamma_rebuilt - g32.grad)[small].abs().max().item()
+    assert err_rebuilt > 5 * err_saved, (err_saved, err_rebuilt)
+
+
+def _attn_ref_generic(qkv, lens, B, S, H, keep=None, p=0.0):
+    D = 64
+    q, k, v = qkv.view(B, S, 3, H, D).permute(2, 0, 3, 1, 4)
+    s = (q @ k.transpose(-1, -2)) * 0.125
+    valid = torch.arange(S, device=qkv.device)[None, :] < lens[:, None].long()
+    s = s.masked_fill(~valid[:, None, None, :], float("-inf"))
+    pr = torch.softmax(s, -1)
+    if keep is not None:
+        pr = pr * keep / (1 - p)
+    return (pr @ v).permute(0, 2, 1, 3).reshape(B * S, H * D), valid
+
+
+@pytest.mark.parametrize("S", [136, 256, 512])
+def test_long_sequence_attention_fallback(S):
+    """128 < S <= 512 (the reference's max_len is a parameter, client1.py:27, and DistilBERT has 512 positions): the
+    attention entry points fall back to the CUDA-core kernels; forward and backward against PyTorch autograd."""
+    nv = importlib.import_module(f"{PKG}.ops.native")
+    torch.manual_seed(S)
+    B, H = 2, 4
+    lens = torch.tensor([S, S // 2 + 3], device="cuda", dtype=torch.int32)
+    qkv = torch.randn(B * S, 3 * H * 64, device="cuda").bfloat16()
+    ctx = torch.full((B * S, H * 64), float("nan"), device="cuda", dtype=torch.bfloat16)
+    lse2 = torch.empty(B * H * S, device="cuda")
+    nv.attn_fwd(qkv, ctx, lse2, lens, B, S, H)
+    q32 = qkv.float().requires_grad_(True)
+    ref, valid = _attn_ref_generic(q32, lens, B, S, H)
+    vq = valid.reshape(B * S, 1)
+    assert bool(torch.isfinite(ctx.float()).all())
+    assert torch.all(ctx.float()[~vq.expand_as(ctx)] == 0)                        # padded query rows are zeros
+    assert ((ctx.float() - ref) * vq).norm() / (ref * vq).norm() < 1e-2
+    dctx = (torch.randn(B * S, H * 64, device="cuda") * vq).bfloat16()
+    ref.backward(dctx.float())
+    dqkv = torch.full_like(qkv, float("nan"))
+    dbias = torch.full((3 * H * 64,), 0.5, device="cuda")
+    nv.attn_bwd(qkv, ctx, dctx, lse2, dqkv, lens, B, S, H, dbias=dbias)
+    assert bool(torch.isfinite(dqkv.float()).all())
+    assert (dqkv.float() - q32.grad).norm() / q32.grad.norm() < 2e-2
+    assert torch.allclose(dbias - 0.5, dqkv.float().sum(0), rtol=1e-2, atol=0.05)
+    g = dqkv.view(B, S, 3, H * 64)
+    assert torch.all(g[1, S // 2 + 3:] == 0)                                      # nothing flows into padding
+
+
+def test_long_sequence_attention_fallback_dropout_and_engine():
+    """Dropout in the fallback: the backward kernels regenerate the forward's mask (recovered here with V = one-hot
+    probes); and the engine trains at seq 256 end to end."""
+    nv = importlib.import_module(f"{PKG}.ops.native")
+    torch.manual_seed(5)
+    B, S, H, D, p = 1, 192, 2, 64, 0.1
+    lens = torch.tensor([S], device="cuda", dtype=torch.int32)
+    qkv = torch.randn(B * S, 3 * H * D, device="cuda").bfloat16()
+    rng = _rng_state()
+    lse2 = torch.empty(B * H * S, device="cuda")
+
+    def fwd(x, pd):
+        ctx = torch.empty(B * S, H * D, device="cuda", dtype=torch.bfloat16)
+        nv.attn_fwd(x, ctx, lse2, lens, B, S, H, p_drop=pd, rng=rng, stream_id=7)
+        return ctx
+
+    probe = qkv.clone().view(B, S, 3, H, D)
+    eye = torch.eye(D, device="cuda", dtype=torch.bfloat16)
+    pdrop = torch.zeros(B, H, S, S, device="cuda")
+    for blk in range(S // D):
+        probe[:, :, 2] = 0
+        probe[:, blk * D:(blk + 1) * D, 2] = eye[None, :, None, :]
+        pdrop[..., blk * D:(blk + 1) * D] = fwd(probe.view(B * S, 3 * H * D), p).float().view(B, S, H, D).permute(0, 2, 1, 3)
+    keep = (pdrop != 0).float()
+    assert 0.08 < 1.0 - keep.mean().item() < 0.12
+    ctx = fwd(qkv, p)
+    q32 = qkv.float().requires_grad_(True)
+    ref, _ = _attn_ref_generic(q32, lens, B, S, H, keep=keep, p=p)
+    assert (ctx.float() - ref).norm() / ref.norm() < 1e-2
+    dctx = torch.randn(B * S, H * D, device="cuda").bfloat16()
+    ref.backward(dctx.float())
+    dqkv = torch.empty_like(qkv)
+    nv.attn_bwd(qkv, ctx, dctx, lse2, dqkv, lens, B, S, H, p_drop=p, rng=rng, stream_id=7)
+    assert (dqkv.float() - q32.grad).norm() / q32.grad.norm() < 2e-2
+
+    # engine at seq 256: loss goes down on a learnable rule, eval logits match the PyTorch module
+    eng_mod = importlib.import_module(f"{PKG}.models.engine")
+    arena_mod = importlib.import_module(f"{PKG}.models.arena")
+    db = importlib.import_module(f"{PKG}.models.distilbert")
+    dims = arena_mod.ModelDims(vocab_size=1000, max_position=512, dim=256, n_layers=2, n_heads=4, hidden_dim=512,
+                               dropout=0.0, attention_dropout=0.0, head_dropout=0.0)
+    Bq, Sq = 4, 256
+    eng = eng_mod.B200Engine(dims, batch=Bq, seq=Sq, init_seed=3, lr=1e-3)
+    g = torch.Generator().manual_seed(1)
+    ids = torch.randint(0, 1000, (Bq, Sq), generator=g).cuda()
+    lens_e = torch.tensor([256, 200, 131, 77]).cuda()
+    labels = (ids[:, 1] % 2)
+    mask = (torch.arange(Sq, device="cuda")[None, :] < lens_e[:, None]).long()
+    eng.set_batch(ids.int(), lens_e.int(), labels.int())
+    ref_m = db.DDoSClassifier(dims).cuda().eval()
+    ref_m.load_state_dict(eng.state_dict())
+    with torch.no_grad():
+        exp = ref_m(ids, mask)
+    assert torch.allclose(eng.logits_eval(), exp, atol=3e-2, rtol=3e-2)
+    losses = []
+    for it in range(30):
+        eng.train_step()
+        if it % 10 == 9:
+            losses.append(eng.read_loss()[0])
+    assert losses[-1] < losses[0], losses
