@@ -207,6 +207,15 @@ class B200Engine:
         # others (their g, m and v are exactly zero, so the update is the identity) -- flow sentences use a small
         # part of the 30522-row table, which is more than a third of all parameters
         self.touched_rows = torch.zeros(dims.vocab_size, device=dev, dtype=torch.uint8)
+        # data-parallel client: the flags live in peer-mapped memory (the owner of a row reads every GPU's flag) and the
+        # word-embedding table is reduced / updated / re-distributed row-sparsely (DCAD_DP_SPARSE_EMB=0: dense)
+        self.dp_sparse_emb = dp is not None and os.environ.get("DCAD_DP_SPARSE_EMB", "1") != "0"
+        if self.dp_sparse_emb:
+            self.touched_rows = dp.flags_tensor()
+            self.touched_rows.zero_()
+        # ... and each block's GEMM weights are updated under the backward pass, behind a per-block barrier
+        self.dp_early_adam = (dp is not None and os.environ.get("DCAD_DP_EARLY_ADAM", "1") != "0"
+                              and dims.n_layers <= 6)
         self._step_ticket = torch.zeros(1, device=dev, dtype=torch.int32)
         self.loss_accum = torch.zeros(2, **f32)                       # {sum of batch-mean losses, #batches}
         self.eval_loss_accum = torch.zeros(2, **f32)
@@ -467,7 +476,7 @@ class B200Engine:
         ``_optimizer`` only has the embeddings / biases / LayerNorm / classifier region left."""
         d, S, B, pl = self.dims, self.S, self.B, self.plan
         in_step = early_adam  # called from the training step (as opposed to a bare backward in tests / tools)
-        early_adam = early_adam and self._side is not None and self.dp is None
+        early_adam = early_adam and self._side is not None and (self.dp is None or self.dp_early_adam)
         self._adam_early_done = early_adam
         H, D = d.n_heads, d.dim
         MN = nv.MAJOR_MN
@@ -537,7 +546,10 @@ class B200Engine:
                 lay = self.arena.layout
                 lo = lay.qkv_weight_offset(l)
                 hi = lay.qkv_weight_offset(l + 1) if l + 1 < d.n_layers else lay.gemm_end
-                self._fork(lambda: self._adam_range(lo, hi))
+                if self.dp is None:
+                    self._fork(lambda: self._adam_range(lo, hi))
+                else:
+                    self._fork(lambda: self._adam_block_dp(l, lo, hi))
             side_done[l] = self._side_mark()
             dy1, dy2 = dxq, dz1  # gradient wrt x_l = via QKV projection + via the residual
         self._k(nv.embed_ln_bwd, dy1, dy2, self.ids, self.word, self.pos, self.eg, self.emb_mean, self.emb_rstd,
@@ -619,26 +631,61 @@ class B200Engine:
         # epilogues) -> sharded Adam with the parameter all-gather fused in -> barrier ----
         dp = self.dp
         G, r = dp.world, dp.rank
-        self._k(nv.xgpu_barrier, dp.pad_ptrs, r, self.rng, 0)          # every peer's backward (and its pushes) is done
-        lo, hi = dp.r2_range(r)
-        if hi > lo:  # biases / LayerNorm / embeddings / classifier: sum the G locally-accumulated copies of my range
+        scale = 1.0 / G
+        adam = (self.lr, self.betas[0], self.betas[1], self.eps, scale, self.rng)
+        # barrier phases 0..5 belong to the per-block updates of _adam_block_dp; the two of the step's end are 6 and 7
+        self._k(nv.xgpu_barrier, dp.pad_ptrs, r, self.rng, 6)          # every peer's backward (and its pushes) is done
+        if not getattr(self, "_adam_early_done", False):
+            glo, ghi = dp.gemm_range(r)
+            if ghi > glo:
+                self._k(nv.adam_step_dp, a.flat, a.grad, a.exp_avg, a.exp_avg_sq, glo, ghi, 0, lay.gemm_end, 0, 0, *adam,
+                        None, dp.mirror_ptrs, r)
+        self._adam_early_done = False
+
+        def dense_range(lo: int, hi: int) -> None:
+            """biases / LayerNorm / classifier / position table: sum the G locally accumulated copies of [lo, hi),
+            Adam, push the fp32 values into every peer's arena"""
+            if hi <= lo:
+                return
             self._k(nv.fedavg_local, [p + lo * 4 for p in dp.grad_ptrs], dp.grad_ptrs[r] + lo * 4, hi - lo,
                     weights=[1.0] * G)
-        glo, ghi = dp.gemm_range(r)
-        scale = 1.0 / G
-        if ghi > glo:
-            self._k(nv.adam_step_dp, a.flat, a.grad, a.exp_avg, a.exp_avg_sq, glo, ghi, 0, lay.gemm_end, 0, 0, self.lr,
-                    self.betas[0], self.betas[1], self.eps, scale, self.rng, None, dp.mirror_ptrs, r)
-        if hi > lo:
-            self._k(nv.adam_step_dp, a.flat, a.grad, a.exp_avg, a.exp_avg_sq, lo, hi, 0, 0, lo, hi, self.lr,
-                    self.betas[0], self.betas[1], self.eps, scale, self.rng, dp.param_ptrs, None, r)
-        self._k(nv.xgpu_barrier, dp.pad_ptrs, r, self.rng, 1)          # all pushed parameters have landed everywhere
-        # the part of the locally accumulated gradients that other GPUs own has been consumed by them: clear it
-        if lo > lay.gemm_end:
-            a.grad[lay.gemm_end: lo].zero_()
-        if hi < lay.total:
-            a.grad[hi: lay.total].zero_()
+            self._k(nv.adam_step_dp, a.flat, a.grad, a.exp_avg, a.exp_avg_sq, lo, hi, 0, 0, lo, hi, *adam,
+                    dp.param_ptrs, None, r)
+
+        if self.dp_sparse_emb:
+            w0 = lay.offsets[_WORD_EMB]
+            w1 = w0 + lay.numel(_WORD_EMB)
+            # the small dense pieces around the word table: first piece on rank 0, second on the last rank
+            if r == 0:
+                dense_range(lay.gemm_end, w0)
+            if r == G - 1:
+                dense_range(w1, lay.total)
+            # the word table, row-sparse: only rows some GPU has ever touched are reduced, updated and re-distributed
+            row_lo, row_hi = dp.word_rows(r)
+            first = dp.self_first
+            self._k(nv.adam_step_dp_rows, a.exp_avg[w0:w1], a.exp_avg_sq[w0:w1], a.grad[w0:w1],
+                    first([p + w0 * 4 for p in dp.param_ptrs]), first([p + w0 * 4 for p in dp.grad_ptrs]),
+                    first(dp.flag_ptrs), row_lo, row_hi, self.dims.dim, *adam)
+        else:
+            lo, hi = dp.r2_range(r)
+            dense_range(lo, hi)
+        self._k(nv.xgpu_barrier, dp.pad_ptrs, r, self.rng, 7)          # all pushed parameters have landed everywhere
+        # the locally accumulated gradients outside the GEMM region have been consumed by their owners: clear them
+        a.grad[lay.gemm_end: lay.total].zero_()
         self._k(nv.step_advance, self.rng)
+
+    def _adam_block_dp(self, l: int, lo: int, hi: int) -> None:
+        """Data-parallel client, side stream: once EVERY GPU of the group has reduce-added its weight gradients of
+        block ``l`` into the owners' arenas (one cross-GPU barrier; nothing reads this block's weights again in this
+        step), the owner updates its share of the block and stores the new bf16 weights into every peer's mirror --
+        the optimizer and the parameter all-gather of block l run under the backward pass of blocks l-1 .. 0."""
+        dp, a = self.dp, self.arena
+        self._k(nv.xgpu_barrier, dp.pad_ptrs, dp.rank, self.rng, self.dims.n_layers - 1 - l)
+        glo, ghi = dp.gemm_range(dp.rank)
+        b0, b1 = max(lo, glo), min(hi, ghi)
+        if b1 > b0:
+            self._k(nv.adam_step_dp, a.flat, a.grad, a.exp_avg, a.exp_avg_sq, b0, b1, 0, a.layout.gemm_end, 0, 0, self.lr,
+                    self.betas[0], self.betas[1], self.eps, 1.0 / dp.world, self.rng, None, dp.mirror_ptrs, dp.rank)
 
     # ------------------------------------------------------------------------------------------------ public API
     def _train_step_kernels(self) -> None:

@@ -124,6 +124,7 @@ def _declare(L: ctypes.CDLL) -> None:
     sig("dcad_adam_step_rows", [P, P, P, P, P, L64, L64, L64, L64, L64, F, F, F, F, P, P, L64, L64, I, P, P])
     sig("dcad_step_advance", [P, P])
     sig("dcad_adam_step_dp", [P, P, P, P, L64, L64, L64, L64, L64, L64, F, F, F, F, F, P, P, P, I, I, P])
+    sig("dcad_adam_step_dp_rows", [P, P, P, P, P, P, I, I, I, I, F, F, F, F, F, P, P])
     sig("dcad_xgpu_barrier", [P, I, I, P, U32, P])
     sig("dcad_attn_fwd", [P, P, P, P, I, I, I, F, P, U32, P])
     sig("dcad_attn_bwd", [P, P, P, P, P, P, I, I, I, F, P, U32, P, P])
@@ -415,6 +416,14 @@ def adam_step_dp(p, g, m, v, begin, end, bf16_begin, bf16_end, push32_begin, pus
     check(lib().dcad_adam_step_dp(ptr(p), ptr(g), ptr(m), ptr(v), begin, end, bf16_begin, bf16_end, push32_begin,
                                   push32_end, lr, beta1, beta2, eps, grad_scale, ptr(state), _ptr_array(peer_p_ptrs),
                                   _ptr_array(peer_bf16_ptrs), n, self_index, stream_ptr(stream)), "dcad_adam_step_dp")
+
+
+def adam_step_dp_rows(m, v, g_own, p_ptrs, g_ptrs, flag_ptrs, row_lo, row_hi, row_len, lr, beta1, beta2, eps, grad_scale,
+                      state, stream=None):
+    """Row-sparse sharded Adam of the word-embedding table (``dcad_adam_step_dp_rows``); ``p_ptrs[0]`` is this rank's."""
+    check(lib().dcad_adam_step_dp_rows(ptr(m), ptr(v), ptr(g_own), _ptr_array(p_ptrs), _ptr_array(g_ptrs),
+                                       _ptr_array(flag_ptrs), len(p_ptrs), row_lo, row_hi, row_len, lr, beta1, beta2,
+                                       eps, grad_scale, ptr(state), stream_ptr(stream)), "dcad_adam_step_dp_rows")
 
 
 def xgpu_barrier(pad_ptrs, rank, state, phase, stream=None):

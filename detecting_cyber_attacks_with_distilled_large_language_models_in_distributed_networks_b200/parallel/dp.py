@@ -53,21 +53,27 @@ class DPGroup:
         self.grad_buf = nv.RawDeviceBuffer(nv.p2p_alloc(n * 4), n * 4)
         self.mirror_buf = nv.RawDeviceBuffer(nv.p2p_alloc(layout.gemm_end * 2), layout.gemm_end * 2)
         self.pad_buf = nv.RawDeviceBuffer(nv.p2p_alloc(PAD_BYTES), PAD_BYTES)
+        # which vocabulary rows this GPU has touched (embed_ln_bwd writes it); peers read it in the row-sparse optimizer
+        vocab_bytes = (layout.dims.vocab_size + 255) // 256 * 256
+        self.flags_buf = nv.RawDeviceBuffer(nv.p2p_alloc(vocab_bytes), vocab_bytes)
         mine = {k: nv.p2p_ipc_get(b.ptr) for k, b in (("param", self.param_buf), ("grad", self.grad_buf),
-                                                      ("mirror", self.mirror_buf), ("pad", self.pad_buf))}
+                                                      ("mirror", self.mirror_buf), ("pad", self.pad_buf),
+                                                      ("flags", self.flags_buf))}
         gathered: List[Optional[dict]] = [None] * world
         dist.all_gather_object(gathered, mine, group=dist_group)
         self._opened: List[nv.RawDeviceBuffer] = []
         self.all_param_ptrs, self.all_grad_ptrs, self.all_mirror_ptrs, self.all_pad_ptrs = [], [], [], []
+        self.all_flag_ptrs: List[int] = []
         for r, h in enumerate(gathered):
             for name, lst, own in (("param", self.all_param_ptrs, self.param_buf),
                                    ("grad", self.all_grad_ptrs, self.grad_buf),
                                    ("mirror", self.all_mirror_ptrs, self.mirror_buf),
-                                   ("pad", self.all_pad_ptrs, self.pad_buf)):
+                                   ("pad", self.all_pad_ptrs, self.pad_buf),
+                                   ("flags", self.all_flag_ptrs, self.flags_buf)):
                 if r == rank:
                     lst.append(own.ptr)
-                elif name == "grad" and r not in self.members:
-                    lst.append(0)  # gradients are only ever exchanged inside a client group
+                elif name in ("grad", "flags") and r not in self.members:
+                    lst.append(0)  # gradients (and row flags) are only ever exchanged inside a client group
                 else:
                     p = nv.p2p_ipc_open(h[name])
                     self._opened.append(nv.RawDeviceBuffer(p, 0, owner=False, ipc=True))
@@ -75,6 +81,7 @@ class DPGroup:
         pick = lambda lst: [lst[g] for g in self.members]  # noqa: E731
         self.param_ptrs, self.grad_ptrs = pick(self.all_param_ptrs), pick(self.all_grad_ptrs)
         self.mirror_ptrs, self.pad_ptrs = pick(self.all_mirror_ptrs), pick(self.all_pad_ptrs)
+        self.flag_ptrs = pick(self.all_flag_ptrs)
         self._peer_grad_bufs = [nv.RawDeviceBuffer(p, n * 4, owner=False) for p in self.grad_ptrs]
         self.gemm_bounds, self.r2_bounds = self._partition()
         self._fed_epoch = 0
@@ -166,6 +173,19 @@ class DPGroup:
     def pad_tensor(self) -> torch.Tensor:
         return self.pad_buf.view(torch.int32, numel=64)
 
+    def flags_tensor(self) -> torch.Tensor:
+        """uint8 [vocab]: rows of the word-embedding table this GPU has touched (peer-readable)."""
+        return self.flags_buf.view(torch.uint8, numel=self.layout.dims.vocab_size)
+
+    def word_rows(self, r: int) -> Tuple[int, int]:
+        """Vocabulary rows whose optimizer state rank ``r`` owns (row-sparse embedding update)."""
+        V = self.layout.dims.vocab_size
+        return V * r // self.world, V * (r + 1) // self.world
+
+    def self_first(self, lst: List[int]) -> List[int]:
+        """``lst`` (one entry per member) rotated so that this rank's entry comes first."""
+        return lst[self.rank:] + lst[: self.rank]
+
     def owner_grad_view(self, offset: int, shape: Tuple[int, ...]) -> torch.Tensor:
         """View of the gradient of the GEMM weight at ``offset`` inside its OWNER's gradient arena (peer memory when
         the owner is another GPU): the destination of the wgrad TMA reduce-add."""
@@ -213,5 +233,5 @@ class DPGroup:
         for b in self._opened:
             b.free()
         self._opened = []
-        for b in (self.param_buf, self.grad_buf, self.mirror_buf, self.pad_buf):
+        for b in (self.param_buf, self.grad_buf, self.mirror_buf, self.pad_buf, self.flags_buf):
             b.free()

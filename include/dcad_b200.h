@@ -227,12 +227,23 @@ int dcad_adam_step_dp(float* p, float* g, float* m, float* v, int64_t begin, int
                       int64_t bf16_end, int64_t push32_begin, int64_t push32_end, float lr, float beta1, float beta2,
                       float eps, float grad_scale, const uint64_t* state, const void* const* peer_p,
                       const void* const* peer_bf16, int n_peers, int self, void* stream);
+/* Row-sparse form of the above for the word-embedding table (no counterpart in the reference): rows [row_lo, row_hi)
+ * belong to this rank; a row is processed only if some GPU's flags[k][row] is set (it has ever received a gradient:
+ * otherwise g = m = v = 0 everywhere and Adam is the identity).  For such a row the n locally accumulated gradient
+ * rows are summed through the peer mappings, Adam is applied with this rank's moments, and the new row is stored into
+ * all n parameter arenas.  p_ptrs / g_ptrs: HOST arrays of n pointers to the word table inside each GPU's parameter /
+ * gradient arena (p_ptrs[0] = this rank's own); flag_ptrs: each GPU's touched-row bytes. */
+int dcad_adam_step_dp_rows(float* m, float* v, float* g_own, void* const* p_ptrs, const void* const* g_ptrs,
+                           const void* const* flag_ptrs, int n, int row_lo, int row_hi, int row_len, float lr,
+                           float beta1, float beta2, float eps, float grad_scale, const uint64_t* state, void* stream);
 /* One-block barrier across the GPUs of a group through their signal pads (words [48,64)); the epoch is
  * state[1] * 8 + phase + 1, read on the device, so the launch can be replayed from a CUDA graph.  n <= 8. */
 int dcad_xgpu_barrier(const void* const* pads, int rank, int n, const uint64_t* state, uint32_t phase, void* stream);
 
-/* ---- fused attention, seq <= 128, head_dim 64 (HF modeling_distilbert.py:126-151 + attention dropout) ----
- * qkv [B*S, 3*H*64] bf16 (Q | K | V), ctx [B*S, H*64] bf16, lse2 [B*H*128] fp32, lens [B] valid key counts or NULL. */
+/* ---- fused attention, head_dim 64 (HF modeling_distilbert.py:126-151 + attention dropout) ----
+ * qkv [B*S, 3*H*64] bf16 (Q | K | V), ctx [B*S, H*64] bf16, lse2 [B*H*max(S,128)] fp32, lens [B] valid key counts or
+ * NULL.  S <= 128 (the reference's max_len, client1.py:27): tcgen05 whole-sequence kernels; 128 < S <= 512: CUDA-core
+ * fallback kernels (csrc/attention_generic.cu). */
 int dcad_attn_fwd(const void* qkv, void* ctx, float* lse2, const int32_t* lens, int B, int S, int H, float p_drop,
                   const uint64_t* rng, uint32_t stream_id, void* stream);
 /* dbias (may be NULL): [3*H*64] fp32, += column sums of dqkv = gradient of the fused QKV bias (atomics). */

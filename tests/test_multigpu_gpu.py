@@ -79,7 +79,7 @@ def test_multiprocess_ipc_fedavg_and_bench():
     # round-2 paths: a peer that never launches leaves every arena untouched, the next round recovers, subset rounds
     # agreed through the store, the asynchronous transport handle, bf16 exchange arenas
     for marker in ("ABSENT_PEER_LEAVES_ARENAS_UNTOUCHED_OK", "ROUND_AFTER_FAILURE_OK", "QUORUM_SUBSET_AND_ASYNC_OK",
-                   "BF16_EXCHANGE_OK"):
+                   "SKEWED_LAUNCHES_OK", "BF16_EXCHANGE_OK"):
         assert marker in r.stdout, (marker, r.stdout[-2000:])
 
 

@@ -79,6 +79,8 @@ def main():
     extra_checks(rank, world, dev, mine, allv, base, elems, mirror)
     if rank == 0:
         print("FEDAVG_IPC_OK", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
 
 
 def extra_checks(rank, world, dev, mine, allv, base, elems, mirror):
@@ -181,6 +183,32 @@ def extra_checks(rank, world, dev, mine, allv, base, elems, mirror):
     dist.barrier()
     grp.close()
 
+    # ---- 3b. the signal-pad protocol under skew: no host barrier between rounds, every rank delays its launch by a
+    # random amount and refills its arena right after its own kernel; the start handshake must hold a fast rank back
+    # until the slow ranks' arenas are final, the end handshake must keep a fast rank from refilling an arena a slow
+    # rank is still reading ----
+    import random
+
+    grp = p2p.PeerGroup(rank, world, elems, mirror)
+    arena = grp.arena_tensor()
+    rnd_gen = random.Random(1000 + rank)
+    gens = [torch.Generator(device=dev).manual_seed(7000 + r) for r in range(world)]
+    for it in range(8):
+        vals = [torch.randn(elems, device=dev, generator=gens[r]) for r in range(world)]  # every rank knows all inputs
+        arena.copy_(vals[rank])
+        time.sleep(rnd_gen.random() * 0.05)
+        grp.fedavg(p2p.TWO_SHOT if it % 2 == 0 else p2p.TWO_SHOT, epoch=it + 1)
+        exp = vals[0].cpu().clone()
+        for v in vals[1:]:
+            exp += v.cpu()
+        exp /= world
+        torch.cuda.synchronize()
+        assert grp.error_flag() == 0, f"rank {rank} round {it}: handshake timed out"
+        assert torch.equal(arena.cpu(), exp), f"rank {rank} round {it}: skewed launch broke the round"
+    say("SKEWED_LAUNCHES_OK")
+    dist.barrier()
+    grp.close()
+
     # ---- 4. bf16 exchange arenas (half the NVLink bytes) ----
     xg = p2p.PeerGroup(rank, world, elems, 0, arena_dtype=torch.bfloat16)
     xg.arena_tensor().copy_(mine.bfloat16())
@@ -197,3 +225,7 @@ def extra_checks(rank, world, dev, mine, allv, base, elems, mirror):
     say("BF16_EXCHANGE_OK")
     dist.barrier()
     xg.close()
+
+
+if __name__ == "__main__":
+    main()

@@ -63,7 +63,9 @@ def run_reference(work: str) -> None:
     t0 = time.time()
     procs = {}
     logs = {}
-    for role, script, gpu in (("server", "server.py", ""), ("client1", "client1.py", "0"),
+    # the reference pickles its CUDA tensors as they are (client1.py:232,284) and the server unpickles them onto the same
+    # device index: the server process needs a visible GPU too
+    for role, script, gpu in (("server", "server.py", "0" if n_gpu else ""), ("client1", "client1.py", "0"),
                               ("client2", "client2.py", "1" if n_gpu > 1 else "0")):
         env = dict(env0, CUDA_VISIBLE_DEVICES=gpu)
         logs[role] = open(os.path.join(cwd, f"{role}_stdout.txt"), "w")
@@ -71,7 +73,14 @@ def run_reference(work: str) -> None:
                                        stdout=logs[role], stderr=subprocess.STDOUT)
         if role == "server":
             time.sleep(2.0)
-    rc = {r: p.wait(timeout=3600) for r, p in procs.items()}
+    rc = {}
+    deadline = time.time() + float(os.environ.get("QUALITY_REF_TIMEOUT", "900"))
+    for r, p in procs.items():
+        try:
+            rc[r] = p.wait(timeout=max(1.0, deadline - time.time()))
+        except subprocess.TimeoutExpired:   # e.g. clients polling a server that died: do not burn GPU time on retries
+            p.kill()
+            rc[r] = "killed at the harness deadline"
     for f in logs.values():
         f.close()
     json.dump({"returncodes": rc, "wall_s": time.time() - t0, "gpus": n_gpu}, open(os.path.join(cwd, "run.json"), "w"))
