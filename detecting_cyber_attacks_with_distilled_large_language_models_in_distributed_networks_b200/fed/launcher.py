@@ -93,7 +93,10 @@ def launch(cfg: FedConfig) -> None:
                 group = p2p.PeerGroup(rank, world, layout.total, layout.gemm_end, with_out_buffer=one)
             backend_kwargs.update(flat_params=group.arena_tensor(), bf16_params=group.mirror_tensor())
             mode = {"nvswitch": p2p.TWO_SHOT, "nvswitch-oneshot": p2p.ONE_SHOT, "nvls": p2p.NVLS, "auto": AUTO}[cfg.transport]
-            transport = NvSwitchTransport(group, mode, coordinator=coord, faults=plan, client_id=ccfg.client_id)
+            from ..report.log import EventLog
+
+            transport = NvSwitchTransport(group, mode, coordinator=coord, faults=plan, client_id=ccfg.client_id,
+                                          log=EventLog(f"CLIENT {ccfg.client_id}", cfg.event_log, quiet=True))
     elif world > 1 and use_cuda and cfg.transport == "nccl":
         transport = NcclTransport()
     elif world > 1:
