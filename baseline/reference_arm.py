@@ -136,6 +136,9 @@ def run(args, rank: int, world: int, local_rank: int, amp: bool = False):
         warm = (DataLoader(ref.CICIDS2017Dataset(texts[:nw], labels[:nw], tokenizer), batch_size=B, shuffle=True)
                 if nw > 0 else None)
         timed = DataLoader(ref.CICIDS2017Dataset(texts[nw:], labels[nw:], tokenizer), batch_size=B, shuffle=True)
+        sample = [int(tokenizer(t, add_special_tokens=True, truncation=True, max_length=128,
+                                return_tensors="pt")["input_ids"].shape[1]) for t in texts[:256]]
+        token_lens = {"mean": sum(sample) / len(sample), "min": min(sample), "max": max(sample), "samples": len(sample)}
         model = ref.DDoSClassifier(model_dir).to(device)                      # client1.py:374
         if amp:
             # bf16 tensor-core matmuls with fp32 master weights / Adam (the mixed precision this repository's engine
@@ -194,6 +197,7 @@ def run(args, rank: int, world: int, local_rank: int, amp: bool = False):
             "impl": impl,
             "config": {"model": "reference DDoSClassifier (HF DistilBertModel + Linear(768,2))", "global_batch": B * world,
                        "per_client_batch": B, "seq_len": 128, "parallelism": f"fed{world} (independent clients)",
+                       "token_lens": token_lens,
                        "path": ("client1.train_model, stock DataLoader/tokenizer/Adam, forward under "
                                 "torch.autocast(bfloat16), TF32 allowed" if amp else
                                 "client1.train_model, stock DataLoader/tokenizer/Adam, fp32 (no TF32/AMP)")},

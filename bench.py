@@ -109,6 +109,8 @@ def run_ours(args, rank: int, world: int, local_rank: int) -> dict:
         ids, lens, labels = synth.synth_token_batch(B, S, dims.vocab_size, seed=1000 * rank + i)
         pool_h.append((ids.pin_memory(), lens.pin_memory(), labels.pin_memory()))
         pool_d.append((ids.to(dev), lens.to(dev), labels.to(dev)))
+    all_lens = torch.cat([h[1] for h in pool_h]).tolist()
+    lens_hist = {f"{lo}-{lo + 15}": sum(1 for v in all_lens if lo <= v < lo + 16) for lo in range(0, S, 16)}
     eng.set_batch(*pool_d[0])
     if not args.no_graph:
         eng.capture()
@@ -165,7 +167,9 @@ def run_ours(args, rank: int, world: int, local_rank: int) -> dict:
         # the same number under an honest name: BASELINE.md's only published throughput is 40.6 samples/s per client on
         # an unspecified Windows PC; the ratio that means something is the driver's own-arm vs reference-arm one
         "vs_published_unspecified_hw": value / (PUBLISHED_SAMPLES_PER_S_PER_CLIENT * world), "dtype": "bf16",
-        "data": "synthetic CICIDS-shaped token batches (seq 128, ~84 real tokens + padding), random-init weights",
+        "data": "synthetic CICIDS-shaped token batches (seq 128, ~84 real tokens + padding, ids drawn Zipf(1.3) from "
+                "2,232 distinct vocabulary entries = the measured statistics of tokenised flow sentences), "
+                "random-init weights",
         "impl": "ours",
         "config": {"model": "DDoSClassifier (DistilBERT-base 6L/768d/12h + Linear(768,2)), 66.36M params",
                    "global_batch": B * world, "per_client_batch": B, "seq_len": S,
@@ -177,6 +181,10 @@ def run_ours(args, rank: int, world: int, local_rank: int) -> dict:
                    "l2": "no explicit flush: each step streams ~1.4 GB (fp32 params/grads/moments 1.06 GB + bf16 "
                          "weights + saved activations) >> 126 MB L2",
                    "cuda_graph": not args.no_graph,
+                   # valid tokens per sample of the synthetic batches (padded to seq_len; every kernel processes the
+                   # padded rows, attention and the embedding backward skip them): mean ~84 like the tokenised flow
+                   # sentences the reference arm feeds (its JSON line reports `token_lens` of its own batches)
+                   "lens_mean": sum(all_lens) / max(len(all_lens), 1), "lens_histogram": lens_hist,
                    "baseline_note": "vs_baseline divides by 40.6 samples/s per client (BASELINE.md, unspecified "
                                     "hardware) x number of clients"},
         "e2e": {"value": e2e_value, "unit": "samples/s", "ms_per_step": ms_e2e / args.steps,

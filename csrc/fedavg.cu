@@ -287,13 +287,14 @@ fedavg_nvls_kernel(const FedArgs a, float* mc_arena, __nv_bfloat16* mc_mirror, i
     const float inv_n = 1.0f / static_cast<float>(n);
     const float nf = static_cast<float>(n);
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
-    for (int64_t v0 = lo + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; v0 < hi; v0 += stride * 4) {
-        float4 acc[4];
+    constexpr int NU = 8;  // 8 x 16 B switch-reduced loads in flight per thread (an NVLS round trip is several us)
+    for (int64_t v0 = lo + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; v0 < hi; v0 += stride * NU) {
+        float4 acc[NU];
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
+        for (int u = 0; u < NU; ++u)
             if (v0 + u * stride < hi) acc[u] = multimem_ld_reduce_add_f32x4(mc_arena + (v0 + u * stride) * 4);
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
+        for (int u = 0; u < NU; ++u) {
             const int64_t vec = v0 + u * stride;
             if (vec >= hi) continue;
             float4 r = acc[u];

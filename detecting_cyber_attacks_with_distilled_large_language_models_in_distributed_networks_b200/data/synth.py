@@ -93,14 +93,33 @@ def write_synthetic_csv(path: str, n_rows: int = 22575, ddos_fraction: float = 0
     return path
 
 
-def synth_token_batch(batch: int, seq: int, vocab_size: int, seed: int = 0, mean_len: int = 84):
-    """Token-level synthetic batch shaped like tokenised flow sentences (~84 real tokens of 128):
-    returns (input_ids [B,S] int32 with [CLS]=101 ... [SEP]=102 and [PAD]=0, lens [B] int32, labels [B] int32)."""
+# Measured on 22,575 synthetic flow sentences tokenised with the synthetic vocabulary (tools: data/tokenizer.py):
+# 83.1 tokens per sentence (78..88), 2,232 DISTINCT token ids in total, the 100 most frequent carrying 86 % of all
+# tokens -- flow records are ten numbers in a fixed sentence frame.  The HF tokenizer of the reference arm gives
+# 84.3 (82..86) on the same sentences.
+FLOW_DISTINCT_TOKENS = 2232
+FLOW_ZIPF_EXPONENT = 1.3      # sum_{k<=100} k^-1.3 / sum_{k<=2232} k^-1.3 = 0.86
+
+
+def synth_token_batch(batch: int, seq: int, vocab_size: int, seed: int = 0, mean_len: int = 84, len_std: float = 2.0,
+                      distinct: int = FLOW_DISTINCT_TOKENS):
+    """Token-level synthetic batch shaped like tokenised flow sentences: ~84 real tokens of ``seq`` (std 2), ids drawn
+    from a fixed subset of ``distinct`` vocabulary entries with a Zipf(1.3) rank-frequency law (see the measurements
+    above), [CLS]=101 first, [SEP]=102 last, [PAD]=0 after.  Returns (input_ids [B,S] int32, lens [B] int32, labels
+    [B] int32).  ``distinct <= 0`` draws ids uniformly from the whole vocabulary (the round-1 behaviour: every step
+    touches ~1,300 new embedding rows, which no tokenised flow data does)."""
     import torch
 
     g = torch.Generator().manual_seed(seed)
-    lens = torch.clamp((torch.randn(batch, generator=g) * 6 + mean_len).round().long(), 8, seq)
-    ids = torch.randint(1000, max(vocab_size, 1001), (batch, seq), generator=g)
+    lens = torch.clamp((torch.randn(batch, generator=g) * len_std + mean_len).round().long(), 8, seq)
+    lo = min(1000, max(vocab_size - 1, 1))
+    if distinct and distinct > 0 and vocab_size - lo > 1:
+        n = min(distinct, vocab_size - lo)
+        used = lo + torch.randperm(vocab_size - lo, generator=torch.Generator().manual_seed(20250805))[:n]
+        w = torch.arange(1, n + 1, dtype=torch.float64) ** -FLOW_ZIPF_EXPONENT
+        ids = used[torch.multinomial(w, batch * seq, replacement=True, generator=g)].view(batch, seq)
+    else:
+        ids = torch.randint(lo, max(vocab_size, lo + 1), (batch, seq), generator=g)
     pos = torch.arange(seq)[None, :]
     ids[:, 0] = 101
     ids[pos == (lens[:, None] - 1)] = 102

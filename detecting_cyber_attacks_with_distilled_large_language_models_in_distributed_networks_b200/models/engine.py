@@ -216,6 +216,11 @@ class B200Engine:
         # ... and each block's GEMM weights are updated under the backward pass, behind a per-block barrier
         self.dp_early_adam = (dp is not None and os.environ.get("DCAD_DP_EARLY_ADAM", "1") != "0"
                               and dims.n_layers <= 6)
+        # ... on a stream of its own: the barrier of block l waits for the SLOWEST GPU's weight gradients and the owner's
+        # Adam follows it; on the weight-gradient stream both would sit in front of the next block's wgrad GEMM of
+        # every GPU (measured on 4 GPUs: 30-125 us of barrier wait per block, 1.82 ms per step)
+        self._opt_stream = (torch.cuda.Stream(device=dev, priority=int(os.environ.get("DCAD_SIDE_PRIO", "0")))
+                            if (self.dp_early_adam and overlap_wgrad) else None)
         self._step_ticket = torch.zeros(1, device=dev, dtype=torch.int32)
         self.loss_accum = torch.zeros(2, **f32)                       # {sum of batch-mean losses, #batches}
         self.eval_loss_accum = torch.zeros(2, **f32)
@@ -437,6 +442,23 @@ class B200Engine:
             if prev is not None:
                 nv.set_pdl(prev)
 
+    def _fork_opt(self, fn) -> None:
+        """Data-parallel client: enqueue ``fn()`` (per-block barrier + sharded Adam) on the optimizer stream, ordered
+        after everything issued on the weight-gradient stream so far."""
+        if self._opt_stream is None or self._side is None:
+            self._fork(fn)
+            return
+        ev = torch.cuda.Event()
+        ev.record(self._side)
+        self._opt_stream.wait_event(ev)
+        prev = nv.set_pdl(False)
+        try:
+            with torch.cuda.stream(self._opt_stream):
+                fn()
+        finally:
+            nv.set_pdl(prev)
+        self._opt_pending = True
+
     def _side_mark(self):
         if self._side is None:
             return None
@@ -549,7 +571,7 @@ class B200Engine:
                 if self.dp is None:
                     self._fork(lambda: self._adam_range(lo, hi))
                 else:
-                    self._fork(lambda: self._adam_block_dp(l, lo, hi))
+                    self._fork_opt(lambda: self._adam_block_dp(l, lo, hi))
             side_done[l] = self._side_mark()
             dy1, dy2 = dxq, dz1  # gradient wrt x_l = via QKV projection + via the residual
         self._k(nv.embed_ln_bwd, dy1, dy2, self.ids, self.word, self.pos, self.eg, self.emb_mean, self.emb_rstd,
@@ -557,6 +579,11 @@ class B200Engine:
                 stream_id=_STREAM_EMBED, touched=self.touched_rows)
         for ev in side_done.values():  # every weight gradient is complete before the optimizer reads it
             self._join(ev)
+        if getattr(self, "_opt_pending", False):  # ... and so are the per-block updates of a data-parallel client
+            ev = torch.cuda.Event()
+            ev.record(self._opt_stream)
+            self._join(ev)
+            self._opt_pending = False
 
     def _backward_tail_pruned(self, l: int, head_fused: bool = False):
         """Backward of the pruned tail (LN2, FFN, LN1, out_lin of the last block) on the B CLS rows.  Returns
