@@ -12,7 +12,7 @@ from test_x_fullsize_gpu import fullsize_parity_report  # noqa: E402
 rep = fullsize_parity_report()
 out, exp = rep["logits"]
 res = {"loss": rep["loss"], "logits_max_abs_err": (out - exp).abs().max().item(),
-       "grads": [{"key": k, "rel_norm_err": r, "ref_norm": n, "max_err_over_rms": m} for k, r, n, m, _e in rep["grads"]]}
+       "grads": [{"key": k, "rel_norm_err": r, "ref_norm": n, "max_err_over_rms": m, "max_err_over_max": _mm} for k, r, n, m, _e, _mm in rep["grads"]]}
 worst = sorted(res["grads"], key=lambda g: -g["rel_norm_err"])[:12]
 print("loss (engine, hf):", rep["loss"], " logits max |err|:", res["logits_max_abs_err"])
 for g in worst:
