@@ -162,26 +162,40 @@ adam_dp_rows_kernel(float* __restrict__ m, float* __restrict__ v, float* __restr
         uint32_t f = (lane < peers.n) ? peers.flags[lane][row] : 0u;
         if (__ballot_sync(0xffffffffu, f != 0u) == 0u) continue;
         const size_t base = static_cast<size_t>(row) * row_len;
-        for (int c = lane * 4; c < row_len; c += 128) {
-            float4 gg = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (int k = 0; k < peers.n; ++k) {
-                const float4 t = *reinterpret_cast<const float4*>(peers.g[k] + base + c);
-                gg.x += t.x; gg.y += t.y; gg.z += t.z; gg.w += t.w;
+        // two 16-byte chunks per lane and pass; all peer loads of a pass are issued before any arithmetic (an NVLink
+        // round trip is ~2 us: the row costs a few round trips, not n_peers x chunks of them)
+        for (int c0 = lane * 4; c0 < row_len; c0 += 256) {
+            float4 t[2][8];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int c = c0 + h * 128;
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    if (k < peers.n && c < row_len) t[h][k] = *reinterpret_cast<const float4*>(peers.g[k] + base + c);
             }
-            gg.x *= grad_scale; gg.y *= grad_scale; gg.z *= grad_scale; gg.w *= grad_scale;
-            float4 pp = *reinterpret_cast<const float4*>(peers.p[0] + base + c);  // every replica holds the same value
-            float4 mm = *reinterpret_cast<const float4*>(m + base + c);
-            float4 vv = *reinterpret_cast<const float4*>(v + base + c);
-#define DCAD_ADAM_ONE(x_)                                                     \
-            mm.x_ = beta1 * mm.x_ + omb1 * gg.x_;                             \
-            vv.x_ = beta2 * vv.x_ + omb2 * gg.x_ * gg.x_;                     \
-            pp.x_ -= step_size * (mm.x_ / (sqrtf(vv.x_) * inv_sqrt_bc2 + eps));
-            DCAD_ADAM_ONE(x) DCAD_ADAM_ONE(y) DCAD_ADAM_ONE(z) DCAD_ADAM_ONE(w)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int c = c0 + h * 128;
+                if (c >= row_len) continue;
+                float4 gg = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    if (k < peers.n) { gg.x += t[h][k].x; gg.y += t[h][k].y; gg.z += t[h][k].z; gg.w += t[h][k].w; }
+                gg.x *= grad_scale; gg.y *= grad_scale; gg.z *= grad_scale; gg.w *= grad_scale;
+                float4 pp = *reinterpret_cast<const float4*>(peers.p[0] + base + c);  // every replica holds the same value
+                float4 mm = *reinterpret_cast<const float4*>(m + base + c);
+                float4 vv = *reinterpret_cast<const float4*>(v + base + c);
+#define DCAD_ADAM_ONE(x_)                                                         \
+                mm.x_ = beta1 * mm.x_ + omb1 * gg.x_;                             \
+                vv.x_ = beta2 * vv.x_ + omb2 * gg.x_ * gg.x_;                     \
+                pp.x_ -= step_size * (mm.x_ / (sqrtf(vv.x_) * inv_sqrt_bc2 + eps));
+                DCAD_ADAM_ONE(x) DCAD_ADAM_ONE(y) DCAD_ADAM_ONE(z) DCAD_ADAM_ONE(w)
 #undef DCAD_ADAM_ONE
-            *reinterpret_cast<float4*>(m + base + c) = mm;
-            *reinterpret_cast<float4*>(v + base + c) = vv;
-            *reinterpret_cast<float4*>(g_own + base + c) = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (int k = 0; k < peers.n; ++k) *reinterpret_cast<float4*>(peers.p[k] + base + c) = pp;
+                *reinterpret_cast<float4*>(m + base + c) = mm;
+                *reinterpret_cast<float4*>(v + base + c) = vv;
+                *reinterpret_cast<float4*>(g_own + base + c) = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int k = 0; k < peers.n; ++k) *reinterpret_cast<float4*>(peers.p[k] + base + c) = pp;
+            }
         }
     }
 }
@@ -307,7 +321,7 @@ extern "C" int dcad_adam_step_dp_rows(float* m, float* v, float* g_own, void* co
     peers.n = n;
     const int rows = row_hi - row_lo;
     int blocks = (rows + 7) / 8;  // 8 warps (rows) per block
-    if (blocks > 148 * 4) blocks = 148 * 4;
+    if (blocks > 148 * 8) blocks = 148 * 8;
     adam_dp_rows_kernel<<<blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(m, v, g_own, peers, row_lo, row_hi,
                                                                                       row_len, lr, beta1, beta2, eps,
                                                                                       grad_scale, state);

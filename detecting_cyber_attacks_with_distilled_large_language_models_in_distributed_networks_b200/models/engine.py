@@ -663,8 +663,7 @@ class B200Engine:
         # barrier phases 0..5 belong to the per-block updates of _adam_block_dp; the two of the step's end are 6 and 7
         self._k(nv.xgpu_barrier, dp.pad_ptrs, r, self.rng, 6)          # every peer's backward (and its pushes) is done
         if not getattr(self, "_adam_early_done", False):
-            glo, ghi = dp.gemm_range(r)
-            if ghi > glo:
+            for glo, ghi in dp.gemm_ranges(r):
                 self._k(nv.adam_step_dp, a.flat, a.grad, a.exp_avg, a.exp_avg_sq, glo, ghi, 0, lay.gemm_end, 0, 0, *adam,
                         None, dp.mirror_ptrs, r)
         self._adam_early_done = False
@@ -708,11 +707,12 @@ class B200Engine:
         the optimizer and the parameter all-gather of block l run under the backward pass of blocks l-1 .. 0."""
         dp, a = self.dp, self.arena
         self._k(nv.xgpu_barrier, dp.pad_ptrs, dp.rank, self.rng, self.dims.n_layers - 1 - l)
-        glo, ghi = dp.gemm_range(dp.rank)
-        b0, b1 = max(lo, glo), min(hi, ghi)
-        if b1 > b0:
-            self._k(nv.adam_step_dp, a.flat, a.grad, a.exp_avg, a.exp_avg_sq, b0, b1, 0, a.layout.gemm_end, 0, 0, self.lr,
-                    self.betas[0], self.betas[1], self.eps, 1.0 / dp.world, self.rng, None, dp.mirror_ptrs, dp.rank)
+        for glo, ghi in dp.gemm_ranges(dp.rank):
+            b0, b1 = max(lo, glo), min(hi, ghi)
+            if b1 > b0:
+                self._k(nv.adam_step_dp, a.flat, a.grad, a.exp_avg, a.exp_avg_sq, b0, b1, 0, a.layout.gemm_end, 0, 0,
+                        self.lr, self.betas[0], self.betas[1], self.eps, 1.0 / dp.world, self.rng, None, dp.mirror_ptrs,
+                        dp.rank)
 
     # ------------------------------------------------------------------------------------------------ public API
     def _train_step_kernels(self) -> None:

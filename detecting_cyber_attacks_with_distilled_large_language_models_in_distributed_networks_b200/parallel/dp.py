@@ -130,33 +130,39 @@ class DPGroup:
         return units
 
     def _partition(self):
+        """Ownership of the GEMM weights and of the fp32 remainder of the arena.
+
+        A weight-gradient GEMM reduce-adds its whole output into ONE arena, so GEMM tensors are owned whole.  The four
+        tensors of a transformer block go to four different ranks (largest first: lin1, lin2, fused qkv, out_lin), the
+        same slots in every block — for groups of 8 the blocks alternate between two sets of four ranks.  Each block's
+        optimizer work is then spread over the group instead of falling to the one or two ranks that would own the
+        block in a contiguous split: with per-block early Adam (models/engine.py) the update of the LAST block of the
+        backward pass is the exposed one, and it shrinks from a whole block to its largest tensor (a third of it)."""
         lay, G = self.layout, self.world
-        units = self._gemm_units()
-        total = lay.gemm_end
-        bounds = [0]
-        acc = 0
-        for off, n in units:  # contiguous, tensor-aligned ranges of roughly equal size
-            acc += n
-            while len(bounds) < G and acc >= total * len(bounds) / G:
-                bounds.append(off + n)
-        while len(bounds) < G:
-            bounds.append(total)
-        bounds.append(total)
-        bounds = bounds[: G + 1]
-        bounds[-1] = total
+        units = self._gemm_units()                       # per layer, arena order: qkv, out_lin, lin1, lin2
+        slot_of = {0: 2, 1: 3, 2: 0, 3: 1}
+        owned: List[List[Tuple[int, int]]] = [[] for _ in range(G)]
+        self._unit_owner: List[Tuple[int, int, int]] = []
+        for i, (off, n) in enumerate(units):
+            layer, j = divmod(i, 4)
+            r = (slot_of[j] + 4 * layer) % G
+            owned[r].append((off, off + n))
+            self._unit_owner.append((off, off + n, r))
+        self.gemm_owned = owned
         r2 = lay.total - lay.gemm_end
         r2b = [lay.gemm_end + (r2 * r // G) // 4 * 4 for r in range(G)] + [lay.total]
-        return bounds, r2b
+        return None, r2b
 
-    def gemm_range(self, r: int) -> Tuple[int, int]:
-        return self.gemm_bounds[r], self.gemm_bounds[r + 1]
+    def gemm_ranges(self, r: int) -> List[Tuple[int, int]]:
+        """Arena element ranges [lo, hi) of the GEMM weights rank ``r`` owns (whole tensors, arena order)."""
+        return self.gemm_owned[r]
 
     def r2_range(self, r: int) -> Tuple[int, int]:
         return self.r2_bounds[r], self.r2_bounds[r + 1]
 
     def gemm_owner(self, offset: int) -> int:
-        for r in range(self.world):
-            if self.gemm_bounds[r] <= offset < self.gemm_bounds[r + 1]:
+        for lo, hi, r in self._unit_owner:
+            if lo <= offset < hi:
                 return r
         raise ValueError(offset)
 
@@ -201,8 +207,7 @@ class DPGroup:
         each rank holds a complete fp32 ``state_dict`` (checkpoints, inter-client FedAvg)."""
         import torch.distributed as dist
 
-        lo, hi = self.gemm_range(self.rank)
-        if hi > lo:
+        for lo, hi in self.gemm_ranges(self.rank):
             for k in range(self.world):
                 if k != self.rank:
                     nv.fedavg_local([self.param_ptrs[self.rank] + lo * 4], self.param_ptrs[k] + lo * 4, hi - lo,

@@ -38,7 +38,8 @@ def main():
     G = int(os.environ.get("DP_GROUP", world))
     grp = DPGroup.build(rank, world, G, lay) if G != world else DPGroup(rank, world, lay)
     client = rank // G
-    assert grp.gemm_bounds[0] == 0 and grp.gemm_bounds[-1] == lay.gemm_end and grp.r2_bounds[-1] == lay.total
+    assert sum(hi - lo for r in range(grp.world) for lo, hi in grp.gemm_ranges(r)) == lay.gemm_end
+    assert grp.r2_bounds[-1] == lay.total
     eng = B200Engine(dims, batch=Bl, seq=S, device=local, init_seed=11, lr=1e-3, dp=grp)
     ids, lens, labels = batch(Bl * G, S, dims.vocab_size, seed=5 + client)
     sl = slice(grp.rank * Bl, (grp.rank + 1) * Bl)
@@ -78,7 +79,7 @@ def main():
     loss_ref, _ = ref.read_loss()
     ok = frac_bad < 0.02 and cos > 0.98 and same_mirror and same_r2
     print(f"rank {rank}: frac_bad={frac_bad:.4f} cos={cos:.4f} same_mirror={same_mirror} same_r2={same_r2} "
-          f"loss_dp(local)={loss_dp:.4f} loss_ref={loss_ref:.4f} bounds={grp.gemm_bounds}", flush=True)
+          f"loss_dp(local)={loss_dp:.4f} loss_ref={loss_ref:.4f} owned={[len(grp.gemm_ranges(r)) for r in range(grp.world)]}", flush=True)
     assert ok
 
     if world // G > 1:
