@@ -287,7 +287,7 @@ fedavg_nvls_kernel(const FedArgs a, float* mc_arena, __nv_bfloat16* mc_mirror, i
     const float inv_n = 1.0f / static_cast<float>(n);
     const float nf = static_cast<float>(n);
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
-    constexpr int NU = 8;  // 8 x 16 B switch-reduced loads in flight per thread (an NVLS round trip is several us)
+    constexpr int NU = 4;  // 16-byte switch-reduced loads in flight per thread (8 measured no faster: 0.690 vs 0.659 ms at 8 GPUs)
     for (int64_t v0 = lo + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; v0 < hi; v0 += stride * NU) {
         float4 acc[NU];
 #pragma unroll
