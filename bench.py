@@ -53,6 +53,8 @@ def parse_args():
     ap.add_argument("--no-fedavg", action="store_true")
     ap.add_argument("--dp", type=int, default=1, help="GPUs per federated client (intra-client data parallelism)")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-trim-padding", action="store_true",
+                    help="compute all seq_len columns even when the longest sample of the data is shorter")
     return ap.parse_args()
 
 
@@ -99,14 +101,23 @@ def run_ours(args, rank: int, world: int, local_rank: int) -> dict:
             group = p2p.PeerGroup(rank, world, layout.total, layout.gemm_end)
         flat, bf16 = group.arena_tensor(), group.mirror_tensor()
     client_id = rank // max(args.dp, 1)
-    eng = eng_mod.B200Engine(dims, batch=B, seq=S, device=local_rank, init_seed=client_id, seed=1234 + rank,
+    # synthetic CICIDS-shaped token batches [B, S]: a device-resident pool (device-timed metric) and a pinned host pool
+    # (end-to-end metric).  Columns that are padding in EVERY sample are not computed (exact: a padded position is
+    # masked as a key, never read as an output and has zero gradient; data/pack.py::executed_seq_len): the step runs
+    # at the longest sample's length rounded up to 32.
+    pack = importlib.import_module(f"{PKG}.data.pack")
+    raw = [synth.synth_token_batch(B, S, dims.vocab_size, seed=1000 * rank + i) for i in range(args.pool)]
+    longest = max(int(r[1].max()) for r in raw)
+    if world > 1:
+        t = torch.tensor([longest], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        longest = int(t.item())
+    S_exec = S if args.no_trim_padding else pack.executed_seq_len(S, longest)
+    eng = eng_mod.B200Engine(dims, batch=B, seq=S_exec, device=local_rank, init_seed=client_id, seed=1234 + rank,
                              flat_params=flat, bf16_params=bf16, dp=dpg)
-
-    # synthetic CICIDS-shaped token batches: a device-resident pool (device-timed metric) and a pinned host pool
-    # (end-to-end metric)
     pool_d, pool_h = [], []
-    for i in range(args.pool):
-        ids, lens, labels = synth.synth_token_batch(B, S, dims.vocab_size, seed=1000 * rank + i)
+    for ids, lens, labels in raw:
+        ids = ids[:, :S_exec].contiguous()
         pool_h.append((ids.pin_memory(), lens.pin_memory(), labels.pin_memory()))
         pool_d.append((ids.to(dev), lens.to(dev), labels.to(dev)))
     all_lens = torch.cat([h[1] for h in pool_h]).tolist()
@@ -172,7 +183,11 @@ def run_ours(args, rank: int, world: int, local_rank: int) -> dict:
                 "random-init weights",
         "impl": "ours",
         "config": {"model": "DDoSClassifier (DistilBERT-base 6L/768d/12h + Linear(768,2)), 66.36M params",
-                   "global_batch": B * world, "per_client_batch": B, "seq_len": S,
+                   "global_batch": B * world, "per_client_batch": B, "seq_len": S, "seq_len_executed": S_exec,
+                   "padding": (f"inputs are [batch, {S}] token ids padded like the reference's (max_length=128); the "
+                               f"longest sample has {longest} tokens, so the {S - S_exec} trailing columns that are "
+                               f"padding in every sample are not computed (exact: padded positions influence nothing)"
+                               if S_exec < S else "every padded position is computed"),
                    "parallelism": (f"fed{world} (one federated client per GPU, FedAvg over NVSwitch peer memory)"
                                    if args.dp <= 1 else
                                    f"fed{world // args.dp} x dp{args.dp} (each client spans {args.dp} GPUs: wgrad "

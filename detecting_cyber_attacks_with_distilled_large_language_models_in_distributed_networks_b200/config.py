@@ -28,6 +28,8 @@ class FedConfig:
     local_epochs: int = 3
     batch_size: int = 16
     max_len: int = 128
+    trim_padding: bool = True          # run at the longest tokenised sample's length (rounded up to 32) instead of
+                                       # computing columns that are padding in every sample (exact; data/pack.py)
     lr: float = 2e-5
     backend: str = "auto"              # auto | b200 | torch
     seed: Optional[int] = None         # default: 41 + client_id (reference: 42 / 43)

@@ -45,6 +45,27 @@ class PackedSplit:
     def num_batches(self, batch_size: int) -> int:
         return (len(self) + batch_size - 1) // batch_size
 
+    def max_len(self) -> int:
+        return int(self.lens.max().item()) if len(self) else 0
+
+    def trim(self, seq: int) -> "PackedSplit":
+        """Drops the trailing columns past ``seq`` (every sample must be at most ``seq`` tokens long)."""
+        if seq >= self.seq_len:
+            return self
+        if self.max_len() > seq:
+            raise ValueError(f"cannot trim to {seq}: a sample has {self.max_len()} tokens")
+        return PackedSplit(self.input_ids[:, :seq].contiguous(), self.lens, self.labels)
+
+
+def executed_seq_len(max_len: int, longest: int, multiple: int = 32) -> int:
+    """Sequence length the step actually runs at: the longest tokenised sample rounded up to ``multiple``, at most
+    ``max_len``.  The reference pads every sample to ``max_length=128`` (client1.py:38-45) and computes every padded
+    position; a padded position influences nothing (masked as a key, never read as an output, zero gradient), so
+    columns that are padding in EVERY sample can be dropped without changing a single result -- flow sentences are
+    78-88 tokens, i.e. 96 columns instead of 128: a quarter fewer token rows in every GEMM / LayerNorm / attention."""
+    longest = max(int(longest), 1)
+    return min(int(max_len), (longest + multiple - 1) // multiple * multiple)
+
 
 def pack_texts(tokenizer, texts: Sequence[str], labels: Sequence[int], max_len: int = 128) -> PackedSplit:
     ids, lens = tokenizer.encode_batch(texts, max_len)

@@ -19,7 +19,7 @@ import torch
 
 from ..config import FedConfig
 from ..data import cicids, synth
-from ..data.pack import PackedSplit, pack_texts
+from ..data.pack import PackedSplit, executed_seq_len, pack_texts
 from ..data.split import split_indices
 from ..data.tokenizer import WordPieceTokenizer
 from ..report.log import EventLog
@@ -69,8 +69,16 @@ def run_client(cfg: FedConfig, transport: Optional[Transport] = None, backend=No
     dims = cfg.model_dims()
     if tok.vocab_size > dims.vocab_size:
         raise ValueError(f"tokenizer vocabulary ({tok.vocab_size}) exceeds the model's ({dims.vocab_size})")
+    seq = cfg.max_len
+    if cfg.trim_padding:
+        # columns that are padding in every sample of every split are dropped (exact: see data/pack.py)
+        seq = executed_seq_len(cfg.max_len, max(train.max_len(), val.max_len(), test.max_len()))
+        if seq < cfg.max_len:
+            log.say(f"longest sample has {max(train.max_len(), val.max_len(), test.max_len())} tokens: running at "
+                    f"sequence length {seq} instead of the padded {cfg.max_len}")
+            train, val, test = train.trim(seq), val.trim(seq), test.trim(seq)
     if backend is None:
-        kw = dict(dims=dims, batch=cfg.batch_size, seq=cfg.max_len, lr=cfg.lr, seed=cfg.resolved_seed())
+        kw = dict(dims=dims, batch=cfg.batch_size, seq=seq, lr=cfg.lr, seed=cfg.resolved_seed())
         kw.update(backend_kwargs or {})
         backend = make_backend(cfg.backend, **kw)
     if cfg.pretrained and not os.path.exists(model_path):

@@ -92,6 +92,27 @@ class GemmPlan:
     fuse_ln_partials: int = field(default_factory=lambda: int(os.environ.get("DCAD_FUSE_LN", "2")))
 
 
+def plan_for(tokens: int) -> GemmPlan:
+    """Tile plan for ``tokens`` = batch * executed sequence length rows.  The defaults of ``GemmPlan`` were tuned at
+    2048 rows (16 x 128); at 1536 rows (16 x 96: flow sentences with the all-padding columns dropped) there are 12
+    row-blocks, so 256-wide tiles make the N = 3072 GEMMs exactly one wave (144 tiles) and a 4-way split of the
+    K-long N = 768 GEMMs gives 144 units (`profiles/gemm_round2/tune_gemm_T1536.json`).  ``DCAD_PLAN`` overrides single
+    fields, e.g. ``DCAD_PLAN="qkv_fwd=192,lin2_fwd=256/4"``."""
+    pl = GemmPlan()
+    if tokens <= 1536:
+        pl.qkv_fwd = 192      # 12 x 12 = 144 tiles (in-step A/B at 1536 rows: 1.2747 vs 1.2828 ms with 256-wide tiles)
+        pl.lin1_fwd = int(os.environ.get("DCAD_LIN1_FWD_BN", "256"))
+        pl.lin2_dgrad = int(os.environ.get("DCAD_LIN2_DGRAD_BN", "256"))
+        pl.lin2_dgrad_ctas = int(os.environ.get("DCAD_LIN2_DGRAD_CTAS", "0"))
+    for item in filter(None, os.environ.get("DCAD_PLAN", "").split(",")):
+        k, _, v = item.partition("=")
+        k = k.strip()
+        if not hasattr(pl, k):
+            raise ValueError(f"DCAD_PLAN: unknown field {k!r}")
+        setattr(pl, k, tuple(int(x) for x in v.split("/")) if "/" in v else int(v))
+    return pl
+
+
 class B200Engine:
     def __init__(self, dims: ModelDims = ModelDims(), batch: int = 16, seq: int = 128, device: int | str = 0,
                  lr: float = 2e-5, betas: Tuple[float, float] = (0.9, 0.999), eps: float = 1e-8, seed: int = 0,
@@ -111,7 +132,7 @@ class B200Engine:
         self.device = torch.device("cuda", device) if not isinstance(device, torch.device) else device
         torch.cuda.set_device(self.device)
         self.lr, self.betas, self.eps = lr, betas, eps
-        self.plan = plan or GemmPlan()
+        self.plan = plan or plan_for(batch * seq)
         self.dp = dp  # parallel.dp.DPGroup when this client spans several GPUs
         # Only the CLS row of the LAST block reaches the classifier (reference client1.py:62), so after the last
         # attention (whose keys/values still need every token) out_lin, both LayerNorms and the FFN are evaluated for

@@ -132,3 +132,37 @@ def test_staged_epoch_matches_iterate_batches_and_dp_slices():
             seen += (ids[:, 0] // S).tolist()
         seen += (p.tail[0][:, 0] // S).tolist()
     assert len(set(seen)) == len(seen) == 70
+
+
+def test_trimming_all_padding_columns_is_exact():
+    """Columns that are padding in every sample can be dropped: same logits from the PyTorch module (the oracle of the
+    engine) on [B, 128] inputs and on the same inputs trimmed to the executed length."""
+    import torch
+
+    from detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200.data.pack import (
+        PackedSplit, executed_seq_len)
+    from detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200.models import (
+        arena as A, distilbert as D)
+
+    assert executed_seq_len(128, 88) == 96 and executed_seq_len(128, 96) == 96 and executed_seq_len(128, 97) == 128
+    assert executed_seq_len(128, 500) == 128 and executed_seq_len(64, 3) == 32
+    g = torch.Generator().manual_seed(0)
+    n, S = 6, 128
+    lens = torch.tensor([88, 80, 79, 85, 12, 83], dtype=torch.int32)
+    ids = torch.randint(5, 900, (n, S), generator=g, dtype=torch.int32)
+    ids[torch.arange(S)[None, :] >= lens[:, None]] = 0
+    split = PackedSplit(ids, lens, torch.zeros(n, dtype=torch.int32))
+    seq = executed_seq_len(S, split.max_len())
+    short = split.trim(seq)
+    assert short.seq_len == 96 and torch.equal(short.input_ids, ids[:, :96])
+    try:
+        split.trim(64)
+        raise AssertionError("trimming below the longest sample must be refused")
+    except ValueError:
+        pass
+    dims = A.ModelDims(vocab_size=1000, max_position=128, dim=64, n_heads=2, hidden_dim=128, n_layers=2)
+    model = D.DDoSClassifier(dims).eval()
+    with torch.no_grad():
+        full = model(split.input_ids.long(), split.attention_mask())
+        cut = model(short.input_ids.long(), short.attention_mask())
+    assert torch.allclose(full, cut, atol=1e-5, rtol=1e-5)

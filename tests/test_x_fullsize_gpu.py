@@ -298,3 +298,35 @@ def test_long_sequence_attention_fallback_dropout_and_engine():
         if it % 10 == 9:
             losses.append(eng.read_loss()[0])
     assert losses[-1] < losses[0], losses
+
+
+def test_engine_at_the_executed_sequence_length_matches_the_padded_run():
+    """The engine run at seq 96 on data whose samples are at most 88 tokens long learns what the engine run at the
+    padded seq 128 learns: same evaluation logits, same parameters after training steps (dropout off; differences are
+    bf16 accumulation order only)."""
+    eng_mod = importlib.import_module(f"{PKG}.models.engine")
+    arena_mod = importlib.import_module(f"{PKG}.models.arena")
+    dims = arena_mod.ModelDims(vocab_size=1000, max_position=128, dim=256, n_layers=2, n_heads=4, hidden_dim=512,
+                               dropout=0.0, attention_dropout=0.0, head_dropout=0.0)
+    B = 8
+    g = torch.Generator().manual_seed(2)
+    lens = torch.randint(70, 89, (B,), generator=g)
+    ids = torch.randint(5, 1000, (B, 128), generator=g)
+    ids[torch.arange(128)[None, :] >= lens[:, None]] = 0
+    labels = (ids[:, 1] % 2)
+    outs = []
+    for S in (128, 96):
+        eng = eng_mod.B200Engine(dims, batch=B, seq=S, init_seed=3, lr=1e-3)
+        eng.set_batch(ids[:, :S].contiguous().int().cuda(), lens.int().cuda(), labels.int().cuda())
+        logits = eng.logits_eval().clone()
+        p0 = eng.arena.flat.clone()
+        for _ in range(3):
+            eng.train_step()
+        torch.cuda.synchronize()
+        outs.append((logits, eng.arena.flat - p0, eng.read_loss()[0]))
+    (l128, u128, loss128), (l96, u96, loss96) = outs
+    assert torch.allclose(l128, l96, atol=2e-2, rtol=2e-2)
+    assert abs(loss128 - loss96) < 2e-2
+    moved = u128.abs() > 0.5e-3
+    cos = torch.nn.functional.cosine_similarity(u128[moved], u96[moved], dim=0).item()
+    assert cos > 0.98, cos
