@@ -660,7 +660,30 @@ class B200Engine:
                 a.bf16[lo:bf_hi] if bf_hi > lo else None, hi - lo, 0, max(bf_hi - lo, 0), 0, 0 if stored else hi - lo,
                 self.lr, self.betas[0], self.betas[1], self.eps, self.rng)
         ticket = self._step_ticket if advance else None  # last launch of the step also advances the step counter
-        if lo <= w0 and w1 <= hi:  # the range holds the word-embedding table: skip rows without optimizer state
+        if (lo <= w0 and w1 <= hi and lo >= a.layout.gemm_end and self.dp is None
+                and os.environ.get("DCAD_ADAM_ROW_KERNEL", "0") != "0"):
+            # Option (off): the word-embedding table through the row-indexed kernel of the data-parallel path (one warp
+            # per row) and the two small dense pieces around it through the flat kernel, instead of ONE flat launch
+            # that scans the table and skips untouched rows.  Measured on one B200: 1.2825 vs 1.2704 ms per step --
+            # the flat kernel's scan of skipped rows is cheaper than two more launches at the end of the step.
+            def dense(d_lo: int, d_hi: int, tk) -> None:
+                if d_hi <= d_lo:
+                    return
+                d_args = (a.flat[d_lo:d_hi], a.grad[d_lo:d_hi], a.exp_avg[d_lo:d_hi], a.exp_avg_sq[d_lo:d_hi], None,
+                          d_hi - d_lo, 0, 0, 0, d_hi - d_lo, self.lr, self.betas[0], self.betas[1], self.eps, self.rng)
+                if tk is not None:
+                    self._k(nv.adam_step_rows, *d_args, None, 0, 0, 4, tk)
+                else:
+                    self._k(nv.adam_step, *d_args)
+
+            self._k(nv.adam_step_dp_rows, a.exp_avg[w0:w1], a.exp_avg_sq[w0:w1], a.grad[w0:w1],
+                    [a.flat.data_ptr() + w0 * 4], [a.grad.data_ptr() + w0 * 4], [self.touched_rows.data_ptr()],
+                    0, self.dims.vocab_size, self.dims.dim, self.lr, self.betas[0], self.betas[1], self.eps, 1.0,
+                    self.rng)
+            last_is_tail = hi > w1
+            dense(lo, w0, None if last_is_tail else ticket)
+            dense(w1, hi, ticket)
+        elif lo <= w0 and w1 <= hi:  # the range holds the word-embedding table: skip rows without optimizer state
             self._k(nv.adam_step_rows, *args, self.touched_rows, w0 - lo, w1 - lo, self.dims.dim, ticket)
         elif advance:
             self._k(nv.adam_step_rows, *args, None, 0, 0, 4, ticket)

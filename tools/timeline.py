@@ -18,8 +18,10 @@ arena_mod = importlib.import_module(f"{PKG}.models.arena")
 synth = importlib.import_module(f"{PKG}.data.synth")
 
 dims = arena_mod.ModelDims()
-eng = eng_mod.B200Engine(dims, batch=16, seq=128, init_seed=0)
+SEQ = int(os.environ.get("SEQ", "96"))
+eng = eng_mod.B200Engine(dims, batch=16, seq=SEQ, init_seed=0)
 ids, lens, labels = synth.synth_token_batch(16, 128, dims.vocab_size, seed=1)
+ids = ids[:, :SEQ].contiguous()
 eng.set_batch(ids.cuda(), lens.cuda(), labels.cuda())
 eng.capture()
 for _ in range(5):
