@@ -163,9 +163,10 @@ def run_client(cfg: FedConfig, transport: Optional[Transport] = None, backend=No
         if cfg.plots and reporter:
             with log.phase("plot generation"):
                 plot_evaluation(local, aggregated, out(f"client{cid}_plots{sfx}"), cid, extra_curves=cfg.extra_curves)
-        if cfg.save_state and reporter and getattr(backend, "dp", None) is None:
+        if cfg.save_state and (reporter or getattr(backend, "dp", None) is not None):
             from ..utils.checkpoint import save_training_state
 
-            save_training_state(state_path, backend, round_idx=rnd + 1, epoch=cfg.local_epochs)
+            # data-parallel client: every GPU of the group joins the merge of the sharded Adam moments, one writes
+            save_training_state(state_path, backend, write=reporter, round_idx=rnd + 1, epoch=cfg.local_epochs)
     log.say("Client shutdown")
     return results

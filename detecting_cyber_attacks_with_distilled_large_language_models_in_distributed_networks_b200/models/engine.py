@@ -299,6 +299,71 @@ class B200Engine:
     def load_state_dict(self, sd) -> None:
         self.arena.load_state_dict(sd)
 
+    def owned_optimizer_ranges(self):
+        """Arena element ranges [lo, hi) whose Adam moments THIS GPU maintains: everything on a single GPU; on a
+        data-parallel client the GEMM weights it owns, its share of the vocabulary rows and (first / last rank) the
+        dense pieces around the word table -- the same split ``_optimizer`` walks."""
+        lay = self.arena.layout
+        if self.dp is None:
+            return [(0, lay.total)]
+        dp = self.dp
+        out = list(dp.gemm_ranges(dp.rank))
+        if self.dp_sparse_emb:
+            w0 = lay.offsets[_WORD_EMB]
+            w1 = w0 + lay.numel(_WORD_EMB)
+            if dp.rank == 0:
+                out.append((lay.gemm_end, w0))
+            if dp.rank == dp.world - 1:
+                out.append((w1, lay.total))
+            row_lo, row_hi = dp.word_rows(dp.rank)
+            out.append((w0 + row_lo * self.dims.dim, w0 + row_hi * self.dims.dim))
+        else:
+            out.append(dp.r2_range(dp.rank))
+        return [(lo, hi) for lo, hi in out if hi > lo]
+
+    def gathered_optimizer_state(self):
+        """``(exp_avg, exp_avg_sq, touched_rows)`` of the whole model.  Single GPU: the arenas themselves.  Data-parallel
+        client: a COLLECTIVE over the client's group -- every rank contributes the ranges it owns (zeros elsewhere),
+        one sum all-reduce per moment and a max all-reduce of the touched-row flags; the result is complete on every
+        rank and has the single-GPU layout, so a snapshot taken on G GPUs resumes on one and vice versa."""
+        a = self.arena
+        if self.dp is None:
+            return a.exp_avg, a.exp_avg_sq, self.touched_rows
+        import torch.distributed as dist
+
+        torch.cuda.synchronize(self.device)
+        out = []
+        for src in (a.exp_avg, a.exp_avg_sq):
+            full = torch.zeros_like(src)
+            for lo, hi in self.owned_optimizer_ranges():
+                full[lo:hi].copy_(src[lo:hi])
+            dist.all_reduce(full, op=dist.ReduceOp.SUM, group=self.dp._dist_group)
+            out.append(full)
+        flags = self.touched_rows.clone()
+        dist.all_reduce(flags, op=dist.ReduceOp.MAX, group=self.dp._dist_group)
+        torch.cuda.synchronize(self.device)
+        return out[0], out[1], flags
+
+    def load_optimizer_state(self, exp_avg, exp_avg_sq, touched_rows, seed: int, step: int) -> None:
+        """Inverse of ``gathered_optimizer_state`` (+ the dropout / Adam step counter).  Every rank of a data-parallel
+        client loads the same full snapshot and keeps the moments of the ranges it owns; the flags become the union
+        over the group (a superset of what this GPU touched: rows are then reduced whose local gradient is zero,
+        which is exact).  The step counter moves, so the cross-GPU barrier words are cleared -- collective."""
+        a = self.arena
+        if exp_avg.numel() != a.exp_avg.numel():
+            raise ValueError("optimizer arena size does not match this model")
+        a.exp_avg.zero_()
+        a.exp_avg_sq.zero_()
+        for lo, hi in self.owned_optimizer_ranges():
+            a.exp_avg[lo:hi].copy_(exp_avg[lo:hi])
+            a.exp_avg_sq[lo:hi].copy_(exp_avg_sq[lo:hi])
+        self.touched_rows.copy_(touched_rows)
+        a.grad.zero_()
+        self.rng.copy_(torch.tensor([seed, step], dtype=torch.int64))
+        torch.cuda.synchronize(self.device)
+        if self.dp is not None:
+            self.dp.reset_barrier_flags()
+
     def refresh_bf16(self) -> None:
         nv.cast_f32_bf16(self.arena.flat[: self.arena.layout.gemm_end], self.arena.bf16)
 

@@ -13,6 +13,11 @@ adds an optional second file that captures everything a bit-faithful resume need
     progress    round / epoch counters and the DataLoader-shuffle generator state, plus free-form ``extra``
 
 ``load_training_state`` restores all of it into a backend built with the same model dimensions.
+
+Data-parallel clients (one client on G GPUs): every GPU holds the Adam moments of the arena ranges it owns only.
+``training_state`` / ``load_training_state`` are then COLLECTIVE over the client's group (every rank calls them; the
+reporter rank writes the file): the moments are merged into the single-GPU layout on save and split again on load, so
+the file does not depend on G.
 """
 from __future__ import annotations
 
@@ -43,9 +48,9 @@ def training_state(backend, round_idx: int = 0, epoch: int = 0, shuffle_generato
     if backend.name == "b200":
         eng = backend.engine
         torch.cuda.synchronize(eng.device)
-        a = eng.arena
-        st["optimizer"] = {"exp_avg": a.exp_avg.to("cpu"), "exp_avg_sq": a.exp_avg_sq.to("cpu"),
-                           "touched_rows": eng.touched_rows.to("cpu"),
+        exp_avg, exp_avg_sq, touched = eng.gathered_optimizer_state()  # collective inside a data-parallel client
+        st["optimizer"] = {"exp_avg": exp_avg.to("cpu"), "exp_avg_sq": exp_avg_sq.to("cpu"),
+                           "touched_rows": touched.to("cpu"),
                            "lr": eng.lr, "betas": tuple(eng.betas), "eps": eng.eps}
         seed, step = (int(x) for x in eng.rng.tolist())
         st["rng"] = {"seed": seed, "step": step}
@@ -56,9 +61,12 @@ def training_state(backend, round_idx: int = 0, epoch: int = 0, shuffle_generato
     return st
 
 
-def save_training_state(path: str, backend, **kw) -> str:
-    """Atomic write (temp file + rename) of ``training_state(backend, **kw)``."""
+def save_training_state(path: str, backend, write: bool = True, **kw) -> str:
+    """Atomic write (temp file + rename) of ``training_state(backend, **kw)``.  ``write=False``: take part in the
+    collectives of a data-parallel client's snapshot without writing the file (every rank but the reporter)."""
     st = training_state(backend, **kw)
+    if not write:
+        return path
     tmp = f"{path}.tmp.{os.getpid()}"
     torch.save(st, tmp)
     os.replace(tmp, path)
@@ -75,16 +83,9 @@ def load_training_state(path_or_state, backend, shuffle_generator: Optional[torc
         raise ValueError(f"snapshot was taken from the {st['backend']!r} backend, not {backend.name!r}")
     backend.load_state_dict(st["model"])
     if backend.name == "b200":
-        eng = backend.engine
-        a, o = eng.arena, st["optimizer"]
-        if o["exp_avg"].numel() != a.exp_avg.numel():
-            raise ValueError("optimizer arena size does not match this model")
-        a.exp_avg.copy_(o["exp_avg"])
-        a.exp_avg_sq.copy_(o["exp_avg_sq"])
-        eng.touched_rows.copy_(o["touched_rows"])
-        a.grad.zero_()
-        eng.rng.copy_(torch.tensor([st["rng"]["seed"], st["rng"]["step"]], dtype=torch.int64))
-        torch.cuda.synchronize(eng.device)
+        o = st["optimizer"]
+        backend.engine.load_optimizer_state(o["exp_avg"], o["exp_avg_sq"], o["touched_rows"], st["rng"]["seed"],
+                                            st["rng"]["step"])
     else:
         backend.opt.load_state_dict(st["optimizer"])
         torch.set_rng_state(st["rng"]["torch_cpu"])

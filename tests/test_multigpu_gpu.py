@@ -85,7 +85,8 @@ def test_multiprocess_ipc_fedavg_and_bench():
 
 def test_intra_client_data_parallel_matches_single_gpu():
     """Fused DP (wgrad TMA reduce-add into the owner's arena, sharded Adam, fused all-gather) on 2 GPUs vs a
-    single-GPU step on the concatenated batch."""
+    single-GPU step on the concatenated batch; the merged optimizer state equals the single-GPU one and a
+    training-state snapshot of the group resumes to the same two steps."""
     _need(2)
     env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
@@ -93,3 +94,4 @@ def test_intra_client_data_parallel_matches_single_gpu():
     r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-3000:])
     assert "DP_OK" in r.stdout
+    assert "DP_CKPT_OK" in r.stdout, r.stdout[-2000:]

@@ -81,6 +81,14 @@ def main():
     print(f"rank {rank}: frac_bad={frac_bad:.4f} cos={cos:.4f} same_mirror={same_mirror} same_r2={same_r2} "
           f"loss_dp(local)={loss_dp:.4f} loss_ref={loss_ref:.4f} owned={[len(grp.gemm_ranges(r)) for r in range(grp.world)]}", flush=True)
     assert ok
+    # merged optimizer state of the sharded Adam == the single-GPU oracle's (same layout; flags exactly: the union of
+    # the rows the GPUs touched is the set of rows of the concatenated batch)
+    m_dp, v_dp, fl_dp = eng.gathered_optimizer_state()
+    assert torch.equal(fl_dp, ref.touched_rows), "touched-row flags differ from the single-GPU run"
+    cos_m = torch.nn.functional.cosine_similarity(m_dp, ref.arena.exp_avg, dim=0).item()
+    cos_v = torch.nn.functional.cosine_similarity(v_dp, ref.arena.exp_avg_sq, dim=0).item()
+    assert cos_m > 0.98 and cos_v > 0.98, (cos_m, cos_v)
+    assert int((m_dp != 0).sum()) > 0.5 * int((ref.arena.exp_avg != 0).sum())
 
     if world // G > 1:
         # inter-client FedAvg over client groups: every GPU must end with mean over clients of the clients' params
@@ -113,7 +121,53 @@ def main():
     t = torch.tensor([e0.elapsed_time(e1) / 20], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     assert grp.error_flag() == 0
+    # ---- training-state checkpoint of a data-parallel client: snapshot, two more steps, restore, the same two steps
+    from detecting_cyber_attacks_with_distilled_large_language_models_in_distributed_networks_b200.utils.checkpoint import (  # noqa: E501
+        load_training_state, training_state)
+
+    class _Backend:
+        name = "b200"
+
+        def __init__(self, engine, dp):
+            self.engine, self.dp = engine, dp
+
+        def state_dict(self):
+            self.dp.allgather_fp32_gemm_params()
+            return self.engine.state_dict()
+
+        def load_state_dict(self, sd):
+            self.engine.load_state_dict(sd)
+
+    shim = _Backend(eng, grp)
+    snap = training_state(shim, round_idx=3)                      # collective; complete on every rank
+    assert snap["optimizer"]["exp_avg"].numel() == lay.total
+    p_snap = eng.arena.flat.clone()
+    step_snap = int(eng.rng[1].item())
+
+    def two_steps():
+        eng.train_step()
+        eng.train_step()
+        torch.cuda.synchronize()
+        dist.barrier()
+        grp.allgather_fp32_gemm_params()
+        return eng.arena.flat.clone(), int(eng.rng[1].item())
+
+    a_params, a_step = two_steps()
+    prog = load_training_state(snap, shim)                        # collective: moments split by ownership again
+    assert prog["round"] == 3 and int(eng.rng[1].item()) == step_snap
+    assert torch.equal(eng.arena.flat, p_snap)
+    own = torch.zeros(lay.total, dtype=torch.bool, device=dev)
+    for lo, hi in eng.owned_optimizer_ranges():
+        own[lo:hi] = True
+    assert int((eng.arena.exp_avg[~own] != 0).sum()) == 0, "moments outside the owned ranges must stay zero"
+    b_params, b_step = two_steps()
+    assert a_step == b_step == step_snap + 2
+    upd_a, upd_b = a_params - p_snap, b_params - p_snap
+    rel = ((upd_a - upd_b).norm() / upd_a.norm().clamp_min(1e-12)).item()
+    assert grp.error_flag() == 0
+    assert rel < 0.02, f"resumed run diverges from the uninterrupted one: rel. update difference {rel:.4f}"
     if rank == 0:
+        print(f"DP_CKPT_OK rel_update_diff={rel:.2e}", flush=True)
         print(f"DP graph step: {t.item():.3f} ms ({world} GPUs x batch {Bl})", flush=True)
         print("DP_OK", flush=True)
     dist.barrier()
