@@ -78,6 +78,8 @@ class GemmPlan:
     # the four weight-gradient GEMMs of a block go out as ONE grouped persistent launch (BLOCK_N 256, the split_k
     # values above) at the end of the block's backward instead of four launches spread through it
     group_wgrad: bool = field(default_factory=lambda: os.environ.get("DCAD_GROUP_WGRAD", "1") != "0")
+    # block 0 (the end of the backward pass): weight gradients + Adam in two halves instead of one group at the very end
+    split_last_wgrad: bool = field(default_factory=lambda: os.environ.get("DCAD_SPLIT_LAST_WGRAD", "1") != "0")
     # last LayerNorm + classifier + cross-entropy (forward and backward) of the pruned tail as one single-CTA launch
     # (dcad_tail_head) instead of three.  Correct and tested, but measured neutral (1.584 vs 1.582 ms per step, same
     # box): one CTA doing three kernels' work serially costs what the two saved launches cost.  Off by default.
@@ -577,6 +579,26 @@ class B200Engine:
             self._k(nv.colsum_bf16, G.wide, P["d_bb1"][l])
             self._k(nv.colsum_bf16, G.qkv, P["d_bqkv"][l])
 
+    def _wgrad_ffn(self, l: int, da2, G) -> None:
+        """First half of a split block: the two FFN weight gradients (and db1) in one grouped launch; side stream."""
+        P, pl = self.p, self.plan
+        if self._count(1, "gemm_group wgrad ffn x2"):
+            nv.gemm_bf16_group([(da2, self.hmid[l], P["d_w2"][l], pl.wgrad_lin2[1]),
+                                (G.wide, self.sa[l], P["d_w1"][l], pl.wgrad_lin1[1])],
+                               block_n=256, reduce_add=self.dp is not None, max_ctas=pl.wgrad_max_ctas)
+        if not pl.fuse_colsum:
+            self._k(nv.colsum_bf16, G.wide, P["d_bb1"][l])
+
+    def _wgrad_attn(self, l: int, G) -> None:
+        """Second half of a split block: the fused-QKV and out_lin weight gradients (and dbqkv); side stream."""
+        P, pl = self.p, self.plan
+        if self._count(1, "gemm_group wgrad attn x2"):
+            nv.gemm_bf16_group([(G.qkv, self.x[l], P["d_wqkv"][l], pl.wgrad_qkv[1]),
+                                (G.a, self.ctx[l], P["d_wo"][l], pl.wgrad_out[1])],
+                               block_n=256, reduce_add=self.dp is not None, max_ctas=pl.wgrad_max_ctas)
+        if not pl.fuse_colsum:
+            self._k(nv.colsum_bf16, G.qkv, P["d_bqkv"][l])
+
     def _backward(self, early_adam: bool = False, head_fused: bool = False) -> None:
         """Backward pass.  With ``early_adam`` (training step, single-GPU client, side stream on) the Adam update of a
         block's GEMM weights is enqueued on the side stream as soon as that block's last data-gradient GEMM has been
@@ -603,6 +625,12 @@ class B200Engine:
             x, qkv, ctx, sa, pre, hmid = self.x[l], self.qkv[l], self.ctx[l], self.sa[l], self.pre[l], self.hmid[l]
             G = self.gset[l % 2]
             self._join(side_done.pop(l + 2, None))  # the side work of layer l+2 read this scratch set
+            # Block 0 is the last one of the backward pass: its weight gradients and its Adam update are what the step
+            # ends with, so they are issued in two halves -- (lin2, lin1) as soon as their inputs exist, with their
+            # Adam behind them, and only (qkv, out_lin) after the attention backward -- instead of one grouped launch
+            # plus one Adam over the whole block after it.
+            split = (l == 0 and top > 0 and pl.group_wgrad and pl.split_last_wgrad and early_adam and self.dp is None)
+            lin1_off = self.arena.layout.offsets[f"distilbert.transformer.layer.{l}.ffn.lin1.weight"]
             if self.prune_last_layer and l == top:
                 # the tail of this block already ran on the CLS rows: dy1 = d(ctx) scattered to all tokens, dy2 = the
                 # residual gradient wrt x (non-zero on the CLS rows only)
@@ -625,8 +653,12 @@ class B200Engine:
                 if not pl.group_wgrad:
                     self._fork(lambda: self._wgrad(G.wide, sa, P["d_w1"][l], pl.wgrad_lin1, G.wide,
                                                    None if pl.fuse_colsum else P["d_bb1"][l]))
+                if split:
+                    self._fork(lambda: self._wgrad_ffn(l, da2, G))
                 dsa = self._gemm_then(G.wide, P["w1"][l], self.T, D, pl.lin1_dgrad, G.b, pl.fuse_ln_partials >= 2,
                                       b_major=MN)
+                if split:  # issued after the lin1 data-gradient GEMM so that the chain's kernel is ahead in the queue
+                    self._fork(lambda: self._adam_range(lin1_off, self.arena.layout.qkv_weight_offset(l + 1)))
                 # sa_layer_norm(attn_out + x): dz1 is the gradient wrt both attn_out and the residual x
                 dz1 = G.a
                 y1, beta1 = self._ln_saved(sa, self.xh1[l], P["b1"][l])
@@ -642,7 +674,9 @@ class B200Engine:
                     p_drop=d.attention_dropout, rng=self.rng, stream_id=_layer_stream(l, 0),
                     dbias=P["d_bqkv"][l] if pl.fuse_colsum else None)
             # QKV: dWqkv = dqkv^T x, dbqkv = colsum(dqkv) (side) ; dx = dqkv Wqkv
-            if pl.group_wgrad and not (self.prune_last_layer and l == top):
+            if split:
+                self._fork(lambda: self._wgrad_attn(l, G))
+            elif pl.group_wgrad and not (self.prune_last_layer and l == top):
                 self._fork(lambda: self._wgrad_block(l, da2, G))  # dz1 of this block is G.a
             else:
                 self._fork(lambda: self._wgrad(G.qkv, x, P["d_wqkv"][l], pl.wgrad_qkv, G.qkv,
@@ -655,7 +689,7 @@ class B200Engine:
                 lo = lay.qkv_weight_offset(l)
                 hi = lay.qkv_weight_offset(l + 1) if l + 1 < d.n_layers else lay.gemm_end
                 if self.dp is None:
-                    self._fork(lambda: self._adam_range(lo, hi))
+                    self._fork(lambda: self._adam_range(lo, lin1_off if split else hi))
                 else:
                     self._fork_opt(lambda: self._adam_block_dp(l, lo, hi))
             side_done[l] = self._side_mark()
