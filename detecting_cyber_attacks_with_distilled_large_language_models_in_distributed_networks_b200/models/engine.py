@@ -762,9 +762,9 @@ class B200Engine:
         if (lo <= w0 and w1 <= hi and lo >= a.layout.gemm_end and self.dp is None
                 and os.environ.get("DCAD_ADAM_ROW_KERNEL", "0") != "0"):
             # Option (off): the word-embedding table through the row-indexed kernel of the data-parallel path (one warp
-            # per row) and the two small dense pieces around it through the flat kernel, instead of ONE flat launch
-            # that scans the table and skips untouched rows.  Measured on one B200: 1.2825 vs 1.2704 ms per step --
-            # the flat kernel's scan of skipped rows is cheaper than two more launches at the end of the step.
+            # per row) and the two small dense pieces around it through the flat kernel, instead of ONE flat launch.
+            # Measured on one B200: 1.2825 vs 1.2704 ms per step (two more launches at the end of the step, and one
+            # warp per row is latency-bound); the flat kernel has since got its own row-group walk (csrc/adam.cu).
             def dense(d_lo: int, d_hi: int, tk) -> None:
                 if d_hi <= d_lo:
                     return

@@ -64,3 +64,14 @@ def test_rejects_foreign_snapshots(tmp_path):
         raise AssertionError("expected a ValueError")
     except ValueError:
         pass
+
+
+def test_non_writing_participant_leaves_no_file(tmp_path):
+    """``write=False`` is what every rank but the reporter of a data-parallel client passes: it takes part in the
+    snapshot (on GPUs: the collectives that merge the sharded Adam moments) and writes nothing."""
+    a = TorchBackend(_dims(), batch=8, seq=16)
+    path = str(tmp_path / "state.pt")
+    assert ck.save_training_state(path, a, write=False, round_idx=1) == path
+    assert list(tmp_path.iterdir()) == []
+    ck.save_training_state(path, a, round_idx=1)
+    assert [p.name for p in tmp_path.iterdir()] == ["state.pt"]   # atomic write: no temp file left behind
