@@ -242,8 +242,11 @@ class B200Engine:
         # ... on a stream of its own: the barrier of block l waits for the SLOWEST GPU's weight gradients and the owner's
         # Adam follows it; on the weight-gradient stream both would sit in front of the next block's wgrad GEMM of
         # every GPU (measured on 4 GPUs: 30-125 us of barrier wait per block, 1.82 ms per step)
+        # Single-GPU option (DCAD_ADAM_STREAM=1): the per-block Adam launches on that third stream as well, so that the
+        # next block's weight-gradient GEMMs do not queue behind a bandwidth-bound Adam on the weight-gradient stream.
+        adam_stream = dp is None and os.environ.get("DCAD_ADAM_STREAM", "0") != "0"
         self._opt_stream = (torch.cuda.Stream(device=dev, priority=int(os.environ.get("DCAD_SIDE_PRIO", "0")))
-                            if (self.dp_early_adam and overlap_wgrad) else None)
+                            if ((self.dp_early_adam or adam_stream) and overlap_wgrad) else None)
         self._step_ticket = torch.zeros(1, device=dev, dtype=torch.int32)
         self.loss_accum = torch.zeros(2, **f32)                       # {sum of batch-mean losses, #batches}
         self.eval_loss_accum = torch.zeros(2, **f32)
@@ -531,14 +534,20 @@ class B200Engine:
                 nv.set_pdl(prev)
 
     def _fork_opt(self, fn) -> None:
-        """Data-parallel client: enqueue ``fn()`` (per-block barrier + sharded Adam) on the optimizer stream, ordered
-        after everything issued on the weight-gradient stream so far."""
+        """Enqueue ``fn()`` (data-parallel client: per-block barrier + sharded Adam; single GPU with DCAD_ADAM_STREAM:
+        the block's Adam) on the optimizer stream, ordered after everything issued so far on the weight-gradient
+        stream and on the current one.  Without an optimizer stream this is ``_fork``."""
         if self._opt_stream is None or self._side is None:
             self._fork(fn)
             return
         ev = torch.cuda.Event()
         ev.record(self._side)
         self._opt_stream.wait_event(ev)
+        # ... and after everything issued on the chain so far: the block's last data-gradient GEMM reads the bf16
+        # weights this update rewrites (it usually ends before the weight gradients do; this makes it an ordering)
+        ev_main = torch.cuda.Event()
+        ev_main.record(torch.cuda.current_stream())
+        self._opt_stream.wait_event(ev_main)
         prev = nv.set_pdl(False)
         try:
             with torch.cuda.stream(self._opt_stream):
@@ -658,7 +667,7 @@ class B200Engine:
                 dsa = self._gemm_then(G.wide, P["w1"][l], self.T, D, pl.lin1_dgrad, G.b, pl.fuse_ln_partials >= 2,
                                       b_major=MN)
                 if split:  # issued after the lin1 data-gradient GEMM so that the chain's kernel is ahead in the queue
-                    self._fork(lambda: self._adam_range(lin1_off, self.arena.layout.qkv_weight_offset(l + 1)))
+                    self._fork_opt(lambda: self._adam_range(lin1_off, self.arena.layout.qkv_weight_offset(l + 1)))
                 # sa_layer_norm(attn_out + x): dz1 is the gradient wrt both attn_out and the residual x
                 dz1 = G.a
                 y1, beta1 = self._ln_saved(sa, self.xh1[l], P["b1"][l])
@@ -689,7 +698,7 @@ class B200Engine:
                 lo = lay.qkv_weight_offset(l)
                 hi = lay.qkv_weight_offset(l + 1) if l + 1 < d.n_layers else lay.gemm_end
                 if self.dp is None:
-                    self._fork(lambda: self._adam_range(lo, lin1_off if split else hi))
+                    self._fork_opt(lambda: self._adam_range(lo, lin1_off if split else hi))
                 else:
                     self._fork_opt(lambda: self._adam_block_dp(l, lo, hi))
             side_done[l] = self._side_mark()
